@@ -1,0 +1,536 @@
+// batch.cu -- the AudioPipeline drop-in: a batch of independent pipelines on one GPU.
+// Host-side orchestration of src/AudioPipeline.zig (pushSamples) and src/AudioPipeline/VAD.zig
+// (collectInputStep -> preAnalyze -> denoiserStep -> fftBufferStep -> fftStep -> stateMachineStep),
+// re-expressed as whole-tile kernel launches over (streams x frames).
+#include "common.cuh"
+#include "frames.cuh"
+#include "rnnoise.cuh"
+#include "stft.cuh"
+#include "vadm.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+using namespace fvad;
+
+struct fvad_batch {
+    fvad_config cfg;
+    std::vector<fvad_vad_machine_config> machine_cfgs;   // [0] main, [1..] alt
+    size_t S = 0, C = 0, rows = 0;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool use_denoiser = true;
+    int fft_size = 2048, frame_len = 480;
+    unsigned trace_flags = 0;
+
+    // tiling
+    size_t tile_frames = 0;        // frames of frame_len per row per tile
+    size_t work_cap = 0;           // floats per work row
+    float *d_work = nullptr;       // [rows][work_cap]: carry + new input of the tile
+    float *d_carry = nullptr;      // [rows][frame_len]
+    size_t carry_len = 0;
+
+    // denoiser path
+    RnnoiseBatch *rn = nullptr;
+    float *d_den = nullptr;        // [rows][den_cap]: carried denoised samples + the tile's output
+    size_t den_cap = 0, den_carry = 0;
+    float *d_den_carry = nullptr;  // [rows][fft_size]
+    static constexpr int kHist480 = 8;
+    float *d_ratio480 = nullptr, *d_vad480 = nullptr;   // [S][kHist480 + tile_frames]
+    size_t stride480 = 0;
+    long long base480 = 0;         // global 480-frame number of slot kHist480
+
+    // STFT + machines
+    const StftTables *tabs = nullptr;
+    StftBands bands{};
+    size_t max_stft = 0;           // STFT frames per row per tile
+    float *d_band = nullptr;       // [n_bands][rows][max_stft]
+    float *d_ratio_stft = nullptr, *d_vad_stft = nullptr;   // [S][max_stft]
+    float *d_spectra = nullptr;    // trace only: [rows][max_stft][1025]
+    int n_machines = 0;
+    VadmParams *d_params = nullptr;
+    VadmState *d_states = nullptr;
+    double *d_rings = nullptr;
+    std::vector<VadmParams> h_params;
+    std::vector<VadmState> h_states0;
+    std::vector<double> h_rings0;
+    size_t rings_per_stream = 0;
+    SegRecord *d_segs = nullptr; unsigned *d_seg_count = nullptr; unsigned seg_cap = 0;
+    EventRecord *d_events = nullptr; unsigned *d_event_count = nullptr; unsigned event_cap = 0;
+    fvad_stft_record *d_trace = nullptr;   // [S][max_stft]
+
+    // progress
+    uint64_t total_write_count = 0, read_count = 0, stft_done = 0;
+
+    // results (host)
+    std::vector<std::vector<fvad_segment>> segs;        // [stream*n_machines + k]
+    std::vector<std::vector<fvad_capture_event>> events;   // [stream]
+    std::vector<std::vector<fvad_stft_record>> tr_records; // [stream]
+    std::vector<std::vector<float>> tr_denoised;        // [row]
+    std::vector<std::vector<float>> tr_vad;             // [stream]
+    std::vector<std::vector<float>> tr_spectra;         // [row]
+    bool dirty = false;
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+template <class T> int dmalloc(T **p, size_t n) {
+    cudaError_t e = cudaMalloc((void **)p, n * sizeof(T) + 16);
+    if (e != cudaSuccess) {
+        *p = nullptr;
+        return set_error(e == cudaErrorMemoryAllocation ? FVAD_EOUT_OF_MEMORY : FVAD_ECUDA, "cudaMalloc(%zu bytes): %s",
+                         n * sizeof(T), cudaGetErrorString(e));
+    }
+    return FVAD_OK;
+}
+
+int freq_to_bin(size_t sample_rate, size_t n_fft, float freq, int *bin) {   // FFT.zig:120-131
+    const float nyq = (float)sample_rate / 2;
+    if (freq > nyq) return set_error(FVAD_EOUT_OF_RANGE, "frequency %g above Nyquist", (double)freq);
+    if (freq < 0) return set_error(FVAD_ENEGATIVE_FREQUENCY, "negative frequency %g", (double)freq);
+    const float bw = (float)sample_rate / (float)n_fft;
+    *bin = (int)roundf(freq / bw);
+    return FVAD_OK;
+}
+
+int upload_machine_state(fvad_batch *b) {
+    FVAD_CUDA_TRY(cudaMemcpyAsync(b->d_states, b->h_states0.data(), sizeof(VadmState) * b->h_states0.size(),
+                                  cudaMemcpyHostToDevice, b->stream));
+    FVAD_CUDA_TRY(cudaMemcpyAsync(b->d_rings, b->h_rings0.data(), sizeof(double) * b->h_rings0.size(),
+                                  cudaMemcpyHostToDevice, b->stream));
+    FVAD_CUDA_TRY(cudaMemsetAsync(b->d_seg_count, 0, sizeof(unsigned), b->stream));
+    FVAD_CUDA_TRY(cudaMemsetAsync(b->d_event_count, 0, sizeof(unsigned), b->stream));
+    return FVAD_OK;
+}
+
+}  // namespace
+
+extern "C" void fvad_batch_destroy(fvad_batch *b) {
+    if (!b) return;
+    {
+        DeviceGuard g(b->device);
+        if (b->stream) cudaStreamSynchronize(b->stream);
+        if (b->rn) rnnoise_batch_destroy(b->rn);
+        cudaFree(b->d_work); cudaFree(b->d_carry); cudaFree(b->d_den); cudaFree(b->d_den_carry);
+        cudaFree(b->d_ratio480); cudaFree(b->d_vad480); cudaFree(b->d_band); cudaFree(b->d_ratio_stft);
+        cudaFree(b->d_vad_stft); cudaFree(b->d_spectra); cudaFree(b->d_params); cudaFree(b->d_states);
+        cudaFree(b->d_rings); cudaFree(b->d_segs); cudaFree(b->d_seg_count); cudaFree(b->d_events);
+        cudaFree(b->d_event_count); cudaFree(b->d_trace);
+        if (b->stream) cudaStreamDestroy(b->stream);
+    }
+    delete b;
+}
+
+extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int device, fvad_batch **out) {
+    if (!cfg || !out || n_streams == 0 || cfg->n_channels == 0)
+        return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_create: null/zero argument");
+    *out = nullptr;
+    if (cfg->sample_rate != 48000)                                             // VAD.zig:101-104
+        return set_error(FVAD_EINVALID_SAMPLE_RATE, "RNNoise can only handle 48 kHz audio (got %zu)", cfg->sample_rate);
+    const size_t n_fft = cfg->vad_config.fft_size;
+    if (n_fft == 0 || (n_fft % 2) != 0)                                        // FFT.zig:29-31
+        return set_error(FVAD_EINVALID_FFT_SIZE, "fft_size %zu must be even and non-zero", n_fft);
+    if (n_fft != (size_t)kFft)
+        return set_error(FVAD_EUNSUPPORTED, "this build's STFT kernel covers fft_size 2048 only (got %zu)", n_fft);
+    if (cfg->n_channels > 64) return set_error(FVAD_EUNSUPPORTED, "more than 64 channels");
+    if (device < 0) {
+        cudaError_t e = cudaGetDevice(&device);
+        if (e != cudaSuccess) return set_error(FVAD_ECUDA, "cudaGetDevice: %s (no CPU fallback exists)", cudaGetErrorString(e));
+    }
+    DeviceGuard g(device);
+    if (!g.ok) return set_error(FVAD_ECUDA, "cannot select CUDA device %d (no CPU fallback exists)", device);
+
+    fvad_batch *b = new (std::nothrow) fvad_batch();
+    if (!b) return set_error(FVAD_EOUT_OF_MEMORY, "host allocation failed");
+    b->cfg = *cfg;
+    b->S = n_streams; b->C = cfg->n_channels; b->rows = b->S * b->C; b->device = device;
+    b->use_denoiser = cfg->vad_config.use_denoiser != 0;
+    b->fft_size = (int)n_fft;
+    b->frame_len = b->use_denoiser ? kRnFrame : b->fft_size;                    // VAD.zig:206-212
+    b->machine_cfgs.push_back(cfg->vad_config.vad_machine_config);
+    for (size_t i = 0; i < cfg->vad_config.n_alt_vad_machine_configs; i++)
+        b->machine_cfgs.push_back(cfg->vad_config.alt_vad_machine_configs[i]);
+    b->cfg.vad_config.alt_vad_machine_configs = nullptr;                        // we own a copy
+    b->n_machines = (int)b->machine_cfgs.size();
+
+    int rc = FVAD_OK;
+    auto fail = [&](int code) { fvad_batch_destroy(b); return code; };
+    if (cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess)
+        return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
+    if ((rc = stft_tables_get(device, &b->tabs)) != FVAD_OK) return fail(rc);
+
+    // machines: params, distinct bands (PipelineFFT.averageVolumeInBand per machine config)
+    b->h_params.resize(b->n_machines);
+    size_t ring_off = 0;
+    for (int k = 0; k < b->n_machines; k++) {
+        size_t nd = 0;
+        if ((rc = vadm_params_from_config(b->machine_cfgs[k], cfg->sample_rate, n_fft, &b->h_params[k], &nd)) != FVAD_OK) return fail(rc);
+        int lo = 0, hi = 0;
+        if ((rc = freq_to_bin(cfg->sample_rate, n_fft, b->machine_cfgs[k].speech_min_freq, &lo)) != FVAD_OK) return fail(rc);
+        if ((rc = freq_to_bin(cfg->sample_rate, n_fft, b->machine_cfgs[k].speech_max_freq, &hi)) != FVAD_OK) return fail(rc);
+        int band = -1;
+        for (int i = 0; i < b->bands.n_bands; i++) if (b->bands.lo[i] == lo && b->bands.hi[i] == hi) band = i;
+        if (band < 0) {
+            if (b->bands.n_bands == kMaxBands) return fail(set_error(FVAD_EUNSUPPORTED, "more than %d distinct speech bands", kMaxBands));
+            band = b->bands.n_bands++;
+            b->bands.lo[band] = lo; b->bands.hi[band] = hi;
+        }
+        b->h_params[k].band = band;
+        b->h_params[k].ring_off = ring_off;
+        ring_off += nd;
+    }
+    b->rings_per_stream = ring_off;
+    b->h_states0.resize(b->S * b->n_machines);
+    b->h_rings0.resize(b->S * ring_off);
+    for (size_t s = 0; s < b->S; s++)
+        for (int k = 0; k < b->n_machines; k++)
+            vadm_init_host(b->h_params[k], &b->h_states0[s * b->n_machines + k], &b->h_rings0[s * ring_off + b->h_params[k].ring_off]);
+
+    // tile geometry
+    const char *env = getenv("FVAD_TILE_FRAMES");
+    size_t tf;
+    if (b->use_denoiser) {
+        tf = 131072 / b->rows;
+        if (tf > 6000) tf = 6000;
+        if (tf < 64) tf = 64;
+    } else {
+        tf = ((size_t)1 << 28) / (b->rows * (size_t)b->fft_size);              // ~1 GiB of f32 per tile
+        if (tf > 4096) tf = 4096;
+        if (tf < 4) tf = 4;
+    }
+    if (env && atol(env) > 0) tf = (size_t)atol(env);
+    b->tile_frames = tf;
+    b->work_cap = tf * b->frame_len + b->frame_len;
+    b->work_cap = (b->work_cap + 3) & ~(size_t)3;
+    if ((rc = dmalloc(&b->d_work, b->rows * b->work_cap)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_carry, b->rows * (size_t)b->frame_len)) != FVAD_OK) return fail(rc);
+    if (b->use_denoiser) {
+        b->den_cap = (tf * kRnFrame + b->fft_size + 3) & ~(size_t)3;
+        b->stride480 = fvad_batch::kHist480 + tf;
+        if ((rc = dmalloc(&b->d_den, b->rows * b->den_cap)) != FVAD_OK) return fail(rc);
+        if ((rc = dmalloc(&b->d_den_carry, b->rows * (size_t)b->fft_size)) != FVAD_OK) return fail(rc);
+        if ((rc = dmalloc(&b->d_ratio480, b->S * b->stride480)) != FVAD_OK) return fail(rc);
+        if ((rc = dmalloc(&b->d_vad480, b->S * b->stride480)) != FVAD_OK) return fail(rc);
+        if ((rc = rnnoise_batch_create(b->S, tf * b->C, device, &b->rn)) != FVAD_OK) return fail(rc);
+        b->max_stft = (tf * kRnFrame + b->fft_size) / b->fft_size + 1;
+    } else {
+        b->max_stft = tf;
+    }
+    if ((rc = dmalloc(&b->d_band, (size_t)b->bands.n_bands * b->rows * b->max_stft)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_ratio_stft, b->S * b->max_stft)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_vad_stft, b->S * b->max_stft)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_params, (size_t)b->n_machines)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_states, b->h_states0.size())) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_rings, b->h_rings0.size())) != FVAD_OK) return fail(rc);
+    b->seg_cap = 1u << 20; b->event_cap = 1u << 21;
+    if ((rc = dmalloc(&b->d_segs, (size_t)b->seg_cap)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_events, (size_t)b->event_cap)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_seg_count, (size_t)1)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_event_count, (size_t)1)) != FVAD_OK) return fail(rc);
+    if (cudaMemcpyAsync(b->d_params, b->h_params.data(), sizeof(VadmParams) * b->n_machines, cudaMemcpyHostToDevice, b->stream) != cudaSuccess)
+        return fail(set_error(FVAD_ECUDA, "upload of machine params failed"));
+    if ((rc = upload_machine_state(b)) != FVAD_OK) return fail(rc);
+    if (b->use_denoiser) {
+        if (cudaMemsetAsync(b->d_ratio480, 0, sizeof(float) * b->S * b->stride480, b->stream) != cudaSuccess ||
+            cudaMemsetAsync(b->d_vad480, 0, sizeof(float) * b->S * b->stride480, b->stream) != cudaSuccess)
+            return fail(set_error(FVAD_ECUDA, "memset failed"));
+    }
+    b->segs.resize(b->S * b->n_machines);
+    b->events.resize(b->S);
+    b->tr_records.resize(b->S); b->tr_vad.resize(b->S);
+    b->tr_denoised.resize(b->rows); b->tr_spectra.resize(b->rows);
+    if (cudaStreamSynchronize(b->stream) != cudaSuccess)
+        return fail(set_error(FVAD_ECUDA, "stream sync after create failed: %s", cudaGetErrorString(cudaGetLastError())));
+    *out = b;
+    return FVAD_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// one tile: d_work rows hold carry_len + m valid samples
+// ------------------------------------------------------------------------------------------
+static int trace_tile(fvad_batch *b, size_t F, size_t J, size_t den_before) {
+    FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    if ((b->trace_flags & FVAD_TRACE_RECORDS) && J) {
+        std::vector<fvad_stft_record> tmp(J);
+        for (size_t s = 0; s < b->S; s++) {
+            FVAD_CUDA_TRY(cudaMemcpy(tmp.data(), b->d_trace + s * b->max_stft, sizeof(fvad_stft_record) * J, cudaMemcpyDeviceToHost));
+            b->tr_records[s].insert(b->tr_records[s].end(), tmp.begin(), tmp.end());
+        }
+    }
+    if ((b->trace_flags & FVAD_TRACE_SPECTRA) && J) {
+        std::vector<float> tmp(J * kBins);
+        for (size_t r = 0; r < b->rows; r++) {
+            FVAD_CUDA_TRY(cudaMemcpy(tmp.data(), b->d_spectra + r * J * kBins, sizeof(float) * J * kBins, cudaMemcpyDeviceToHost));
+            b->tr_spectra[r].insert(b->tr_spectra[r].end(), tmp.begin(), tmp.end());
+        }
+    }
+    if (b->use_denoiser && F) {
+        if (b->trace_flags & FVAD_TRACE_DENOISED) {
+            std::vector<float> tmp(F * kRnFrame);
+            for (size_t r = 0; r < b->rows; r++) {
+                FVAD_CUDA_TRY(cudaMemcpy(tmp.data(), b->d_den + r * b->den_cap + den_before, sizeof(float) * tmp.size(), cudaMemcpyDeviceToHost));
+                b->tr_denoised[r].insert(b->tr_denoised[r].end(), tmp.begin(), tmp.end());
+            }
+        }
+        if (b->trace_flags & FVAD_TRACE_RNN_VAD) {
+            std::vector<float> tmp(F);
+            for (size_t s = 0; s < b->S; s++) {
+                FVAD_CUDA_TRY(cudaMemcpy(tmp.data(), b->d_vad480 + s * b->stride480 + fvad_batch::kHist480, sizeof(float) * F, cudaMemcpyDeviceToHost));
+                b->tr_vad[s].insert(b->tr_vad[s].end(), tmp.begin(), tmp.end());
+            }
+        }
+    }
+    return FVAD_OK;
+}
+
+static int run_machines(fvad_batch *b, const float *d_vad, unsigned long long first_index, size_t J) {
+    VadmIo io{};
+    io.band = b->d_band; io.band_rows = b->rows; io.band_frame_stride = b->max_stft;
+    io.vol_ratio = b->d_ratio_stft; io.vad = d_vad; io.ratio_stride = b->max_stft;
+    io.n_channels = (int)b->C;
+    io.first_index = first_index; io.index_step = (unsigned long long)b->fft_size; io.n_frames = J;
+    io.segs = b->d_segs; io.seg_count = b->d_seg_count; io.seg_cap = b->seg_cap;
+    io.events = b->d_events; io.event_count = b->d_event_count; io.event_cap = b->event_cap;
+    io.trace = (b->trace_flags & FVAD_TRACE_RECORDS) ? b->d_trace : nullptr;
+    io.trace_stride = b->max_stft; io.trace_offset = 0;
+    return vadm_launch(b->d_params, b->d_states, b->d_rings, b->S, b->n_machines, io, b->stream);
+}
+
+static int process_tile(fvad_batch *b, size_t m) {
+    const size_t avail = b->carry_len + m;
+    const size_t F = avail / b->frame_len, used = F * b->frame_len;
+    size_t J = 0, den_before = b->den_carry;
+    if (F > 0 && !b->cfg.skip_processing) {                                   // AudioPipeline.zig:153-157
+        float *spec = (b->trace_flags & FVAD_TRACE_SPECTRA) ? b->d_spectra : nullptr;
+        if (!b->use_denoiser) {
+            J = F;
+            FVAD_TRY(rms_ratio_launch(b->d_work, b->work_cap, b->S, (int)b->C, F, b->fft_size, b->d_ratio_stft, b->max_stft, 0, b->stream));
+            FVAD_TRY(stft_launch(*b->tabs, b->d_work, b->rows, b->work_cap, F, b->fft_size, b->bands, b->d_band, b->max_stft, 0,
+                                 spec, nullptr, 0.f, b->device, b->stream));
+            FVAD_TRY(run_machines(b, nullptr, b->read_count, J));
+        } else {
+            FVAD_TRY(rms_ratio_launch(b->d_work, b->work_cap, b->S, (int)b->C, F, kRnFrame, b->d_ratio480, b->stride480,
+                                      fvad_batch::kHist480, b->stream));
+            FVAD_TRY(rnnoise_batch_process(b->rn, b->d_work, b->work_cap, (int)b->C, F, b->d_den, b->den_cap, b->den_carry,
+                                           b->d_vad480, nullptr, b->stride480, fvad_batch::kHist480, b->stream));
+            const size_t den_avail = b->den_carry + F * kRnFrame;
+            J = den_avail / b->fft_size;
+            if (J > 0) {
+                FVAD_TRY(reframe_launch(b->d_ratio480, b->d_vad480, b->stride480, b->base480, fvad_batch::kHist480, b->S,
+                                        b->stft_done, J, b->fft_size, b->d_ratio_stft, b->d_vad_stft, b->max_stft, b->stream));
+                FVAD_TRY(stft_launch(*b->tabs, b->d_den, b->rows, b->den_cap, J, b->fft_size, b->bands, b->d_band, b->max_stft, 0,
+                                     spec, nullptr, 0.f, b->device, b->stream));
+                FVAD_TRY(run_machines(b, b->d_vad_stft, b->stft_done * (unsigned long long)b->fft_size, J));
+            }
+            if (b->trace_flags) FVAD_TRY(trace_tile(b, F, J, den_before));
+            const size_t tail = den_avail - J * b->fft_size;
+            if (J > 0 && tail > 0) {
+                FVAD_TRY(copy_rows_launch(b->d_den_carry, b->fft_size, 0, b->d_den, b->den_cap, J * b->fft_size, b->rows, tail, b->stream));
+                FVAD_TRY(copy_rows_launch(b->d_den, b->den_cap, 0, b->d_den_carry, b->fft_size, 0, b->rows, tail, b->stream));
+            }
+            b->den_carry = tail;
+            FVAD_TRY(shift_hist_launch(b->d_ratio480, b->stride480, fvad_batch::kHist480, F, b->S, b->stream));
+            FVAD_TRY(shift_hist_launch(b->d_vad480, b->stride480, fvad_batch::kHist480, F, b->S, b->stream));
+            b->base480 += (long long)F;
+        }
+        if (!b->use_denoiser && b->trace_flags) FVAD_TRY(trace_tile(b, F, J, 0));
+        b->stft_done += J;
+        b->dirty = true;
+    }
+    b->read_count += b->cfg.skip_processing ? 0 : used;
+    const size_t consumed = b->cfg.skip_processing ? avail : used;   // skip_processing: samples are only buffered by the reference
+    const size_t tail = avail - consumed;
+    if (consumed > 0 && tail > 0) {
+        FVAD_TRY(copy_rows_launch(b->d_carry, b->frame_len, 0, b->d_work, b->work_cap, consumed, b->rows, tail, b->stream));
+        FVAD_TRY(copy_rows_launch(b->d_work, b->work_cap, 0, b->d_carry, b->frame_len, 0, b->rows, tail, b->stream));
+    }
+    b->carry_len = tail;
+    return FVAD_OK;
+}
+
+static int ensure_trace_buffers(fvad_batch *b) {
+    if ((b->trace_flags & FVAD_TRACE_RECORDS) && !b->d_trace) FVAD_TRY(dmalloc(&b->d_trace, b->S * b->max_stft));
+    if ((b->trace_flags & FVAD_TRACE_SPECTRA) && !b->d_spectra) FVAD_TRY(dmalloc(&b->d_spectra, b->rows * b->max_stft * (size_t)kBins));
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n, uint64_t *first_index) {
+    if (!b || (!pcm && n)) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_push: null argument");
+    DeviceGuard g(b->device);
+    if (!g.ok) return set_error(FVAD_ECUDA, "cannot select device %d", b->device);
+    if (first_index) *first_index = b->total_write_count;
+    FVAD_TRY(ensure_trace_buffers(b));
+    const size_t m_max = b->tile_frames * (size_t)b->frame_len;
+    for (size_t off = 0; off < n;) {
+        const size_t m = std::min(m_max, n - off);
+        for (size_t r = 0; r < b->rows; r++)
+            FVAD_CUDA_TRY(cudaMemcpyAsync(b->d_work + r * b->work_cap + b->carry_len, pcm[r] + off, sizeof(float) * m,
+                                          cudaMemcpyHostToDevice, b->stream));
+        FVAD_TRY(process_tile(b, m));
+        off += m;
+    }
+    b->total_write_count += n;
+    // input is borrowed only until return (AudioPipeline.pushSamples copies into its ring)
+    FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t stream_stride, size_t channel_stride,
+                                      size_t n, uint64_t *first_index) {
+    if (!b || (!d_pcm && n)) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_push_device: null argument");
+    DeviceGuard g(b->device);
+    if (!g.ok) return set_error(FVAD_ECUDA, "cannot select device %d", b->device);
+    if (first_index) *first_index = b->total_write_count;
+    FVAD_TRY(ensure_trace_buffers(b));
+    const size_t m_max = b->tile_frames * (size_t)b->frame_len;
+    for (size_t off = 0; off < n;) {
+        const size_t m = std::min(m_max, n - off);
+        FVAD_TRY(gather_rows_launch(b->d_work, b->work_cap, b->carry_len, d_pcm, stream_stride, channel_stride, off, b->S,
+                                    (int)b->C, m, b->stream));
+        FVAD_TRY(process_tile(b, m));
+        off += m;
+    }
+    b->total_write_count += n;
+    return FVAD_OK;
+}
+
+static int collect(fvad_batch *b) {
+    FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    if (!b->dirty) return FVAD_OK;
+    unsigned ns = 0, ne = 0;
+    FVAD_CUDA_TRY(cudaMemcpy(&ns, b->d_seg_count, sizeof ns, cudaMemcpyDeviceToHost));
+    FVAD_CUDA_TRY(cudaMemcpy(&ne, b->d_event_count, sizeof ne, cudaMemcpyDeviceToHost));
+    if (ns > b->seg_cap || ne > b->event_cap)
+        return set_error(FVAD_EOUT_OF_MEMORY, "segment/event buffer overflow (%u/%u segments, %u/%u events): sync more often", ns, b->seg_cap, ne, b->event_cap);
+    if (ns) {
+        std::vector<SegRecord> tmp(ns);
+        FVAD_CUDA_TRY(cudaMemcpy(tmp.data(), b->d_segs, sizeof(SegRecord) * ns, cudaMemcpyDeviceToHost));
+        std::stable_sort(tmp.begin(), tmp.end(), [](const SegRecord &a, const SegRecord &c) {
+            if (a.stream != c.stream) return a.stream < c.stream;
+            if (a.machine != c.machine) return a.machine < c.machine;
+            return a.seg.sample_to < c.seg.sample_to;      // a machine emits in increasing end time
+        });
+        for (auto &r : tmp) b->segs[(size_t)r.stream * b->n_machines + r.machine].push_back(r.seg);
+        FVAD_CUDA_TRY(cudaMemset(b->d_seg_count, 0, sizeof(unsigned)));
+    }
+    if (ne) {
+        std::vector<EventRecord> tmp(ne);
+        FVAD_CUDA_TRY(cudaMemcpy(tmp.data(), b->d_events, sizeof(EventRecord) * ne, cudaMemcpyDeviceToHost));
+        std::stable_sort(tmp.begin(), tmp.end(), [](const EventRecord &a, const EventRecord &c) {
+            if (a.stream != c.stream) return a.stream < c.stream;
+            return a.ev.at_index < c.ev.at_index;
+        });
+        for (auto &r : tmp) b->events[r.stream].push_back(r.ev);
+        FVAD_CUDA_TRY(cudaMemset(b->d_event_count, 0, sizeof(unsigned)));
+    }
+    b->dirty = false;
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_sync(fvad_batch *b) {
+    if (!b) return set_error(FVAD_EINVALID_ARGUMENT, "null batch");
+    DeviceGuard g(b->device);
+    return collect(b);
+}
+
+extern "C" int fvad_batch_reset(fvad_batch *b) {
+    if (!b) return set_error(FVAD_EINVALID_ARGUMENT, "null batch");
+    DeviceGuard g(b->device);
+    FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    FVAD_TRY(upload_machine_state(b));
+    if (b->use_denoiser) {
+        FVAD_TRY(rnnoise_batch_reset(b->rn, b->stream));
+        FVAD_CUDA_TRY(cudaMemsetAsync(b->d_ratio480, 0, sizeof(float) * b->S * b->stride480, b->stream));
+        FVAD_CUDA_TRY(cudaMemsetAsync(b->d_vad480, 0, sizeof(float) * b->S * b->stride480, b->stream));
+    }
+    b->carry_len = 0; b->den_carry = 0; b->base480 = 0;
+    b->total_write_count = b->read_count = b->stft_done = 0;
+    for (auto &v : b->segs) v.clear();
+    for (auto &v : b->events) v.clear();
+    for (auto &v : b->tr_records) v.clear();
+    for (auto &v : b->tr_denoised) v.clear();
+    for (auto &v : b->tr_vad) v.clear();
+    for (auto &v : b->tr_spectra) v.clear();
+    b->dirty = false;
+    FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_segments(fvad_batch *b, size_t stream, int k, const fvad_segment **segs, size_t *n) {
+    if (!b || !segs || !n || stream >= b->S || k < 0 || k >= b->n_machines)
+        return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_segments: bad argument");
+    FVAD_TRY(fvad_batch_sync(b));
+    auto &v = b->segs[stream * b->n_machines + k];
+    *segs = v.data(); *n = v.size();
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_events(fvad_batch *b, size_t stream, const fvad_capture_event **ev, size_t *n) {
+    if (!b || !ev || !n || stream >= b->S) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_events: bad argument");
+    FVAD_TRY(fvad_batch_sync(b));
+    *ev = b->events[stream].data(); *n = b->events[stream].size();
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_counts(fvad_batch *b, uint64_t *total_write_count, uint64_t *pipeline_read_count) {
+    if (!b) return set_error(FVAD_EINVALID_ARGUMENT, "null batch");
+    if (total_write_count) *total_write_count = b->total_write_count;
+    if (pipeline_read_count) *pipeline_read_count = b->read_count;
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_set_trace(fvad_batch *b, unsigned flags) {
+    if (!b) return set_error(FVAD_EINVALID_ARGUMENT, "null batch");
+    if (b->total_write_count) return set_error(FVAD_EINVALID_ARGUMENT, "set the trace flags before the first push");
+    b->trace_flags = flags;
+    return FVAD_OK;
+}
+
+template <class T> static int copy_out(const std::vector<T> &v, T *out, size_t cap, size_t *n) {
+    if (n) *n = v.size();
+    if (out && cap) memcpy(out, v.data(), sizeof(T) * std::min(cap, v.size()));
+    return FVAD_OK;
+}
+extern "C" int fvad_batch_trace_records(fvad_batch *b, size_t s, fvad_stft_record *out, size_t cap, size_t *n) {
+    if (!b || s >= b->S) return set_error(FVAD_EINVALID_ARGUMENT, "bad argument");
+    FVAD_TRY(fvad_batch_sync(b));
+    return copy_out(b->tr_records[s], out, cap, n);
+}
+extern "C" int fvad_batch_trace_denoised(fvad_batch *b, size_t s, size_t c, float *out, size_t cap, size_t *n) {
+    if (!b || s >= b->S || c >= b->C) return set_error(FVAD_EINVALID_ARGUMENT, "bad argument");
+    FVAD_TRY(fvad_batch_sync(b));
+    return copy_out(b->tr_denoised[s * b->C + c], out, cap, n);
+}
+extern "C" int fvad_batch_trace_rnn_vad(fvad_batch *b, size_t s, float *out, size_t cap, size_t *n) {
+    if (!b || s >= b->S) return set_error(FVAD_EINVALID_ARGUMENT, "bad argument");
+    FVAD_TRY(fvad_batch_sync(b));
+    return copy_out(b->tr_vad[s], out, cap, n);
+}
+extern "C" int fvad_batch_trace_spectra(fvad_batch *b, size_t s, size_t c, float *out, size_t cap, size_t *n) {
+    if (!b || s >= b->S || c >= b->C) return set_error(FVAD_EINVALID_ARGUMENT, "bad argument");
+    FVAD_TRY(fvad_batch_sync(b));
+    return copy_out(b->tr_spectra[s * b->C + c], out, cap, n);
+}
+
+// ---- single pipeline = batch of 1 (AudioPipeline.init / pushSamples / deinit) ---------------
+extern "C" int fvad_pipeline_create(const fvad_config *cfg, fvad_pipeline **out) { return fvad_batch_create(cfg, 1, -1, out); }
+extern "C" int fvad_pipeline_push(fvad_pipeline *p, const float *const *channel_pcm, size_t n, uint64_t *first_index) {
+    return fvad_batch_push(p, channel_pcm, n, first_index);
+}
+extern "C" int fvad_pipeline_segments(fvad_pipeline *p, int k, const fvad_segment **segs, size_t *n) {
+    return fvad_batch_segments(p, 0, k, segs, n);
+}
+extern "C" void fvad_pipeline_destroy(fvad_pipeline *p) { fvad_batch_destroy(p); }

@@ -1,0 +1,97 @@
+// common.cu -- error reporting, launch accounting, misc C-ABI entry points.
+#include "common.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace fvad {
+
+static thread_local char t_err[1024] = "";
+std::atomic<uint64_t> g_launch_count{0};
+
+int set_error(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_err, sizeof t_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int device_sm_count(int device) {
+    static int cache[64];
+    if (device >= 0 && device < 64 && cache[device]) return cache[device];
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || n <= 0) n = 148;
+    if (device >= 0 && device < 64) cache[device] = n;
+    return n;
+}
+
+}  // namespace fvad
+
+extern "C" {
+
+const char *fvad_last_error(void) { return fvad::t_err; }
+
+const char *fvad_status_name(int s) {
+    switch (s) {
+    case FVAD_OK: return "Ok";
+    case FVAD_EINVALID_SAMPLE_RATE: return "InvalidSampleRate";
+    case FVAD_EINVALID_FFT_SIZE: return "InvalidFFTSize";
+    case FVAD_EINVALID_SAMPLES_LEN: return "InvalidSamplesLength";
+    case FVAD_EINVALID_WINDOW_LEN: return "InvalidWindowLength";
+    case FVAD_EINVALID_RESULT_LEN: return "InvalidResultLength";
+    case FVAD_EOUT_OF_RANGE: return "OutOfRange";
+    case FVAD_ENEGATIVE_FREQUENCY: return "NegativeFrequency";
+    case FVAD_EINVALID_FRAME_SIZE: return "InvalidFrameSize";
+    case FVAD_EINVALID_RESULT_SIZE: return "InvalidResultSize";
+    case FVAD_ENOT_INITIALIZED: return "NotInitialized";
+    case FVAD_ECHANNEL_COUNT_MISMATCH: return "ChannelCountMismatch";
+    case FVAD_EOUT_OF_MEMORY: return "OutOfMemory";
+    case FVAD_EINVALID_ARGUMENT: return "InvalidArgument";
+    case FVAD_EUNSUPPORTED: return "Unsupported";
+    case FVAD_ECUDA: return "CudaError";
+    default: return "Unknown";
+    }
+}
+
+const char *fvad_version(void) { return "fvad-b200 0.1 (sm_100a)"; }
+
+int fvad_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return fvad::set_error(FVAD_ECUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e));
+    return n;
+}
+
+uint64_t fvad_launch_count(void) { return fvad::g_launch_count.load(); }
+
+void fvad_default_vad_machine_config(fvad_vad_machine_config *c) {   // VADMachine.zig:18-39
+    memset(c, 0, sizeof *c);
+    c->speech_min_freq = 100;
+    c->speech_max_freq = 1500;
+    c->long_term_speech_avg_sec = 180;
+    c->has_initial_long_term_avg = 1;
+    c->initial_long_term_avg = 0.005;
+    c->short_term_speech_avg_sec = 0.2f;
+    c->speech_threshold_factor = 18;
+    c->channel_vol_ratio_avg_sec = 0.5f;
+    c->channel_vol_ratio_threshold = 0.5f;
+    c->min_consecutive_sec_to_open = 0.2f;
+    c->max_speech_gap_sec = 2;
+    c->min_vad_duration_sec = 0.7f;
+}
+
+void fvad_default_config(fvad_config *c, size_t sample_rate, size_t n_channels) {   // AudioPipeline.zig:20-26, VAD.zig:17-23
+    memset(c, 0, sizeof *c);
+    c->sample_rate = sample_rate;
+    c->n_channels = n_channels;
+    c->buffer_length = 0;
+    c->vad_config.fft_size = 2048;
+    c->vad_config.use_denoiser = 1;
+    fvad_default_vad_machine_config(&c->vad_config.vad_machine_config);
+    c->vad_config.alt_vad_machine_configs = nullptr;
+    c->vad_config.n_alt_vad_machine_configs = 0;
+    c->skip_processing = 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,192 @@
+// leaf_api.cu -- C ABI of the leaf drop-ins: FFT.zig (single transform and batched STFT) and the
+// VADMachine sweep over shared features.
+#include "common.cuh"
+#include "stft.cuh"
+#include "vadm.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <new>
+#include <vector>
+
+using namespace fvad;
+
+struct fvad_fft {
+    size_t n_fft, sample_rate;
+    int device;
+    const StftTables *tabs;
+    float *d_in = nullptr, *d_window = nullptr, *d_out = nullptr, *d_band = nullptr;
+    std::vector<float> h_in, h_window;
+};
+
+extern "C" int fvad_fft_create(size_t n_fft, size_t sample_rate, fvad_fft **out) {
+    if (!out) return set_error(FVAD_EINVALID_ARGUMENT, "null out");
+    *out = nullptr;
+    if (n_fft == 0 || (n_fft % 2) != 0) return set_error(FVAD_EINVALID_FFT_SIZE, "n_fft %zu must be even and non-zero", n_fft);   // FFT.zig:29-31
+    if (n_fft != (size_t)kFft) return set_error(FVAD_EUNSUPPORTED, "this build's FFT kernel covers n_fft 2048 only (got %zu)", n_fft);
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return set_error(FVAD_ECUDA, "cudaGetDevice: %s (no CPU fallback exists)", cudaGetErrorString(e));
+    fvad_fft *f = new (std::nothrow) fvad_fft();
+    if (!f) return set_error(FVAD_EOUT_OF_MEMORY, "host allocation failed");
+    f->n_fft = n_fft; f->sample_rate = sample_rate; f->device = device;
+    int rc = stft_tables_get(device, &f->tabs);
+    if (rc != FVAD_OK) { delete f; return rc; }
+    if (cudaMalloc(&f->d_in, sizeof(float) * n_fft) != cudaSuccess || cudaMalloc(&f->d_window, sizeof(float) * n_fft) != cudaSuccess ||
+        cudaMalloc(&f->d_out, sizeof(float) * (n_fft / 2 + 1)) != cudaSuccess || cudaMalloc(&f->d_band, sizeof(float) * kMaxBands) != cudaSuccess) {
+        fvad_fft_destroy(f);
+        return set_error(FVAD_EOUT_OF_MEMORY, "device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+    }
+    f->h_in.resize(n_fft); f->h_window.resize(n_fft);
+    *out = f;
+    return FVAD_OK;
+}
+
+extern "C" void fvad_fft_destroy(fvad_fft *f) {
+    if (!f) return;
+    cudaFree(f->d_in); cudaFree(f->d_window); cudaFree(f->d_out); cudaFree(f->d_band);
+    delete f;
+}
+
+extern "C" size_t fvad_fft_bin_count(const fvad_fft *f) { return f->n_fft / 2 + 1; }                       // FFT.zig:101-103
+extern "C" float fvad_fft_bin_width(const fvad_fft *f) { return (float)f->sample_rate / (float)f->n_fft; } // FFT.zig:106-111
+extern "C" float fvad_fft_nyquist_freq(const fvad_fft *f) { return (float)f->sample_rate / 2; }            // FFT.zig:114-117
+extern "C" int fvad_fft_freq_to_bin(const fvad_fft *f, float freq, size_t *bin) {                          // FFT.zig:120-131
+    if (freq > fvad_fft_nyquist_freq(f)) return set_error(FVAD_EOUT_OF_RANGE, "frequency above Nyquist");
+    if (freq < 0) return set_error(FVAD_ENEGATIVE_FREQUENCY, "negative frequency");
+    *bin = (size_t)roundf(freq / fvad_fft_bin_width(f));
+    return FVAD_OK;
+}
+extern "C" int fvad_fft_bin_to_freq(const fvad_fft *f, size_t bin, float *freq) {                          // FFT.zig:134-144
+    if (bin > fvad_fft_bin_count(f) - 1) return set_error(FVAD_EOUT_OF_RANGE, "bin out of range");
+    *freq = (float)bin * fvad_fft_bin_width(f);
+    return FVAD_OK;
+}
+extern "C" void fvad_hann_window_periodic(float *w, size_t n) { host_hann_window_periodic(w, n); }
+extern "C" float fvad_window_norm_factor(const float *w, size_t n) { return host_window_norm_factor(w, n); }
+
+// FFT.fft (src/FFT.zig:70-98): host SplitSlice in, normalised magnitudes out.
+extern "C" int fvad_fft_run(fvad_fft *f, const float *first, size_t n_first, const float *second, size_t n_second,
+                            const float *window, size_t n_window, float *result, size_t n_result) {
+    if (!f) return set_error(FVAD_EINVALID_ARGUMENT, "null fft");
+    if (n_first + n_second != f->n_fft) return set_error(FVAD_EINVALID_SAMPLES_LEN, "samples length %zu != n_fft", n_first + n_second);
+    if (n_window != f->n_fft) return set_error(FVAD_EINVALID_WINDOW_LEN, "window length %zu != n_fft", n_window);
+    if (n_result != f->n_fft / 2 + 1) return set_error(FVAD_EINVALID_RESULT_LEN, "result length %zu != bin count", n_result);
+    if (n_first) memcpy(f->h_in.data(), first, sizeof(float) * n_first);
+    if (n_second) memcpy(f->h_in.data() + n_first, second, sizeof(float) * n_second);
+    // window norm factor is recomputed per call as the reference does (FFT.zig:94); in-order f32 sum
+    const float norm = host_window_norm_factor(window, n_window) / (float)(f->n_fft / 2);
+    int prev = 0;
+    FVAD_CUDA_TRY(cudaGetDevice(&prev));
+    FVAD_CUDA_TRY(cudaSetDevice(f->device));
+    FVAD_CUDA_TRY(cudaMemcpyAsync(f->d_in, f->h_in.data(), sizeof(float) * f->n_fft, cudaMemcpyHostToDevice, 0));
+    FVAD_CUDA_TRY(cudaMemcpyAsync(f->d_window, window, sizeof(float) * f->n_fft, cudaMemcpyHostToDevice, 0));
+    StftBands b{}; b.n_bands = 0;
+    FVAD_TRY(stft_launch(*f->tabs, f->d_in, 1, f->n_fft, 1, f->n_fft, b, f->d_band, 1, 0, f->d_out, f->d_window, norm, f->device, 0));
+    FVAD_CUDA_TRY(cudaMemcpy(result, f->d_out, sizeof(float) * n_result, cudaMemcpyDeviceToHost));
+    FVAD_CUDA_TRY(cudaSetDevice(prev));
+    return FVAD_OK;
+}
+
+extern "C" int fvad_stft_batch(fvad_fft *f, const float *d_pcm, size_t n_rows, size_t row_stride, size_t n_frames,
+                               size_t hop, size_t min_bin, size_t max_bin, float *d_band_sum, float *d_spectra,
+                               void *cuda_stream) {
+    if (!f || !d_pcm || !d_band_sum) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_stft_batch: null argument");
+    if (max_bin >= f->n_fft / 2 + 1 || min_bin > max_bin) return set_error(FVAD_EOUT_OF_RANGE, "band %zu..%zu out of range", min_bin, max_bin);
+    StftBands b{}; b.n_bands = 1; b.lo[0] = (int)min_bin; b.hi[0] = (int)max_bin;
+    return stft_launch(*f->tabs, d_pcm, n_rows, row_stride, n_frames, hop, b, d_band_sum, n_frames, 0, d_spectra, nullptr, 0.f,
+                       f->device, (cudaStream_t)cuda_stream);
+}
+
+// ---- VADMachine sweep (BASELINE config 5) --------------------------------------------------
+// One scan per (stream, config) over the same records: VAD.stateMachineStep's alt machines
+// (VAD.zig:375-380) run on "shared features".  Machines are laid out as n_configs machines per stream.
+extern "C" int fvad_vadm_sweep(const fvad_stft_record *records, size_t n_streams, size_t n_records,
+                               const fvad_vad_machine_config *configs, size_t n_configs, size_t sample_rate,
+                               size_t fft_size, int device, fvad_segment *segs, size_t max_segs, uint32_t *counts) {
+    if (!records || !configs || !segs || !counts || !n_streams || !n_configs)
+        return set_error(FVAD_EINVALID_ARGUMENT, "fvad_vadm_sweep: null/zero argument");
+    if (device < 0) FVAD_CUDA_TRY(cudaGetDevice(&device));
+    int prev = 0;
+    FVAD_CUDA_TRY(cudaGetDevice(&prev));
+    FVAD_CUDA_TRY(cudaSetDevice(device));
+    std::vector<VadmParams> params(n_configs);
+    size_t ring_off = 0;
+    for (size_t k = 0; k < n_configs; k++) {
+        size_t nd = 0;
+        FVAD_TRY(vadm_params_from_config(configs[k], sample_rate, fft_size, &params[k], &nd));
+        params[k].band = 0;
+        params[k].ring_off = ring_off;
+        ring_off += nd;
+    }
+    std::vector<VadmState> states(n_streams * n_configs);
+    std::vector<double> rings(n_streams * ring_off);
+    for (size_t s = 0; s < n_streams; s++)
+        for (size_t k = 0; k < n_configs; k++)
+            vadm_init_host(params[k], &states[s * n_configs + k], &rings[s * ring_off + params[k].ring_off]);
+    // split records into the planes the scan kernel reads
+    std::vector<float> minv(n_streams * n_records), ratio(n_streams * n_records), vad(n_streams * n_records);
+    bool any_vad = false;
+    for (size_t i = 0; i < n_streams * n_records; i++) {
+        minv[i] = records[i].min_volume; ratio[i] = records[i].vol_ratio; vad[i] = records[i].rnn_vad;
+        any_vad |= records[i].has_vad != 0.0f;
+    }
+    int rc = FVAD_OK;
+    VadmParams *d_params = nullptr; VadmState *d_states = nullptr; double *d_rings = nullptr;
+    float *d_minv = nullptr, *d_ratio = nullptr, *d_vad = nullptr;
+    SegRecord *d_segs = nullptr; EventRecord *d_events = nullptr; unsigned *d_counts = nullptr;
+    const unsigned seg_cap = (unsigned)std::min<size_t>(n_streams * n_configs * max_segs + 16, (size_t)1 << 26);
+    auto cleanup = [&]() {
+        cudaFree(d_params); cudaFree(d_states); cudaFree(d_rings); cudaFree(d_minv); cudaFree(d_ratio); cudaFree(d_vad);
+        cudaFree(d_segs); cudaFree(d_events); cudaFree(d_counts);
+        cudaSetDevice(prev);
+    };
+#define SWEEP_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { rc = set_error(FVAD_ECUDA, "%s: %s", #x, cudaGetErrorString(e_)); cleanup(); return rc; } } while (0)
+    SWEEP_TRY(cudaMalloc(&d_params, sizeof(VadmParams) * n_configs));
+    SWEEP_TRY(cudaMalloc(&d_states, sizeof(VadmState) * states.size()));
+    SWEEP_TRY(cudaMalloc(&d_rings, sizeof(double) * rings.size()));
+    SWEEP_TRY(cudaMalloc(&d_minv, sizeof(float) * minv.size()));
+    SWEEP_TRY(cudaMalloc(&d_ratio, sizeof(float) * minv.size()));
+    SWEEP_TRY(cudaMalloc(&d_vad, sizeof(float) * minv.size()));
+    SWEEP_TRY(cudaMalloc(&d_segs, sizeof(SegRecord) * seg_cap));
+    SWEEP_TRY(cudaMalloc(&d_events, sizeof(EventRecord) * 16));
+    SWEEP_TRY(cudaMalloc(&d_counts, sizeof(unsigned) * 2));
+    SWEEP_TRY(cudaMemcpy(d_params, params.data(), sizeof(VadmParams) * n_configs, cudaMemcpyHostToDevice));
+    SWEEP_TRY(cudaMemcpy(d_states, states.data(), sizeof(VadmState) * states.size(), cudaMemcpyHostToDevice));
+    SWEEP_TRY(cudaMemcpy(d_rings, rings.data(), sizeof(double) * rings.size(), cudaMemcpyHostToDevice));
+    SWEEP_TRY(cudaMemcpy(d_minv, minv.data(), sizeof(float) * minv.size(), cudaMemcpyHostToDevice));
+    SWEEP_TRY(cudaMemcpy(d_ratio, ratio.data(), sizeof(float) * minv.size(), cudaMemcpyHostToDevice));
+    SWEEP_TRY(cudaMemcpy(d_vad, vad.data(), sizeof(float) * minv.size(), cudaMemcpyHostToDevice));
+    SWEEP_TRY(cudaMemset(d_counts, 0, sizeof(unsigned) * 2));
+    VadmIo io{};
+    io.band = d_minv; io.band_rows = n_streams; io.band_frame_stride = n_records;
+    io.vol_ratio = d_ratio; io.vad = any_vad ? d_vad : nullptr; io.ratio_stride = n_records;
+    io.n_channels = 1;
+    io.first_index = n_records ? records[0].index : 0;
+    io.index_step = fft_size; io.n_frames = n_records;
+    io.segs = d_segs; io.seg_count = d_counts; io.seg_cap = seg_cap;
+    io.events = d_events; io.event_count = d_counts + 1; io.event_cap = 0;
+    io.trace = nullptr;
+    rc = vadm_launch(d_params, d_states, d_rings, n_streams, (int)n_configs, io, 0);
+    if (rc != FVAD_OK) { cleanup(); return rc; }
+    SWEEP_TRY(cudaDeviceSynchronize());
+    unsigned ns = 0;
+    SWEEP_TRY(cudaMemcpy(&ns, d_counts, sizeof ns, cudaMemcpyDeviceToHost));
+    if (ns > seg_cap) { cleanup(); return set_error(FVAD_EOUT_OF_MEMORY, "sweep produced %u segments, buffer holds %u", ns, seg_cap); }
+    std::vector<SegRecord> tmp(ns);
+    if (ns) SWEEP_TRY(cudaMemcpy(tmp.data(), d_segs, sizeof(SegRecord) * ns, cudaMemcpyDeviceToHost));
+    std::stable_sort(tmp.begin(), tmp.end(), [](const SegRecord &a, const SegRecord &c) {
+        if (a.stream != c.stream) return a.stream < c.stream;
+        if (a.machine != c.machine) return a.machine < c.machine;
+        return a.seg.sample_to < c.seg.sample_to;
+    });
+    memset(counts, 0, sizeof(uint32_t) * n_streams * n_configs);
+    for (auto &r : tmp) {
+        const size_t id = (size_t)r.stream * n_configs + r.machine;
+        if (counts[id] < max_segs) segs[id * max_segs + counts[id]] = r.seg;
+        counts[id]++;
+    }
+    cleanup();
+#undef SWEEP_TRY
+    return FVAD_OK;
+}

@@ -1,0 +1,42 @@
+// stft.cuh -- batched windowed real STFT (2048 points) + speech-band reduction.
+// Replaces FFT.fft / PipelineFFT.fft / averageVolumeInBand (src/FFT.zig:70-98,147-177;
+// src/AudioPipeline/PipelineFFT.zig:88-112) over lib/kissfft (kiss_fftr.c:63-117,
+// kiss_fft.c:38-84,235-300) with one kernel over (rows x frames).
+#pragma once
+#include "common.cuh"
+
+namespace fvad {
+
+constexpr int kFft = 2048;          // the size this build's kernel covers (VAD.Config default, VAD.zig:18)
+constexpr int kFftC = kFft / 2;     // complex length handed to kiss_fft
+constexpr int kBins = kFft / 2 + 1;
+constexpr int kMaxBands = 8;
+
+struct StftBands {
+    int n_bands;
+    int lo[kMaxBands], hi[kMaxBands];   // inclusive bin ranges (freqToBin(min), freqToBin(max))
+};
+
+struct StftTables {                  // per device
+    float *d_window = nullptr;       // periodic Hann, 2048 (PipelineFFT.zig:66-68)
+    cpx *d_tw = nullptr;             // 1024 twiddles (kiss_fft.c:357-363)
+    cpx *d_stw = nullptr;            // 512 super twiddles (kiss_fftr.c:53-59)
+    float norm_factor = 0;           // (N / sum(w)) / (N/2)  (FFT.zig:94,165)
+};
+
+// Host-side tables, computed with the same libm the reference's C uses.
+void host_hann_window_periodic(float *w, size_t n);
+float host_window_norm_factor(const float *w, size_t n);
+int stft_tables_get(int device, const StftTables **out);
+
+// frame f of row r = d_pcm[r*row_stride + f*hop ...+2048).  Outputs:
+//   d_band[(band*n_rows + r)*band_frame_stride + band_frame_offset + f]  sum of bins lo..hi
+//   d_spectra (optional) [(r*n_frames + f)*1025]
+// If d_window_override != nullptr it is used instead of the Hann table (FFT.fft takes the
+// window as an argument) with the given norm factor.
+int stft_launch(const StftTables &t, const float *d_pcm, size_t n_rows, size_t row_stride, size_t n_frames,
+                size_t hop, const StftBands &bands, float *d_band, size_t band_frame_stride,
+                size_t band_frame_offset, float *d_spectra, const float *d_window_override,
+                float norm_override, int device, cudaStream_t stream);
+
+}  // namespace fvad

@@ -1,0 +1,235 @@
+/*
+ * fvad.h -- C ABI of libfvad_cuda.so: the B200 (sm_100a) implementation of
+ * Formula-VAD's per-frame AudioPipeline hot path.
+ *
+ * This is the drop-in boundary.  Every entry point names the reference interface
+ * it replaces (file:line under the reference tree).  Signatures use plain
+ * pointers and sizes only.  There is NO CPU fallback: every compute entry point
+ * returns FVAD_ECUDA when no usable CUDA device / kernel image is present.
+ *
+ * The reference processes ONE stream per thread, one 480-sample frame at a time
+ * (src/simulator.zig:217-228).  The GPU is efficient only when many streams x many
+ * frames are submitted at once, so the primary object is a BATCH of independent
+ * pipelines that share one configuration; the single-pipeline API is a batch of 1.
+ *
+ * Threading: a handle is owned by one thread at a time (as a reference pipeline
+ * is, src/simulator/SimulationInstance.zig:134-142); distinct handles may be used
+ * from distinct threads.  Errors: 0 = ok, negative fvad_status; fvad_last_error()
+ * gives a thread-local message.
+ */
+#ifndef FVAD_H
+#define FVAD_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes: the reference's Zig error names ------- */
+typedef enum fvad_status {
+    FVAD_OK = 0,
+    FVAD_EINVALID_SAMPLE_RATE   = -1,   /* VAD.zig:101-104 error.InvalidSampleRate */
+    FVAD_EINVALID_FFT_SIZE      = -2,   /* FFT.zig:29-31 error.InvalidFFTSize (+ sizes this build does not cover) */
+    FVAD_EINVALID_SAMPLES_LEN   = -3,   /* FFT.zig:71-73 error.InvalidSamplesLength */
+    FVAD_EINVALID_WINDOW_LEN    = -4,   /* FFT.zig:75-77 error.InvalidWindowLength */
+    FVAD_EINVALID_RESULT_LEN    = -5,   /* FFT.zig:79-81 error.InvalidResultLength */
+    FVAD_EOUT_OF_RANGE          = -6,   /* FFT.zig:121-123,135-137 error.OutOfRange */
+    FVAD_ENEGATIVE_FREQUENCY    = -7,   /* FFT.zig:125-127 error.NegativeFrequency */
+    FVAD_EINVALID_FRAME_SIZE    = -8,   /* Denoiser.zig:48-50 error.InvalidFrameSize */
+    FVAD_EINVALID_RESULT_SIZE   = -9,   /* Denoiser.zig:52-54 error.InvalidResultSize */
+    FVAD_ENOT_INITIALIZED       = -10,  /* Denoiser.zig:46 error.NotInitialized */
+    FVAD_ECHANNEL_COUNT_MISMATCH= -11,  /* SegmentWriter.zig:63-65 error.ChannelCountMismatch */
+    FVAD_EOUT_OF_MEMORY         = -12,  /* error.OutOfMemory (host or device) */
+    FVAD_EINVALID_ARGUMENT      = -13,  /* null handle, bad index, zero-length ring, ... */
+    FVAD_EUNSUPPORTED           = -14,  /* valid in the reference, not covered by this build */
+    FVAD_ECUDA                  = -15   /* CUDA runtime / driver failure, or no sm_100 device: there is no CPU path */
+} fvad_status;
+
+const char *fvad_last_error(void);
+const char *fvad_status_name(int status);
+const char *fvad_version(void);
+/* Number of CUDA devices visible (<0: FVAD_ECUDA). */
+int fvad_device_count(void);
+/* Kernels launched by this library in this process so far (all handles, all threads). */
+uint64_t fvad_launch_count(void);
+
+/* ---- configuration PODs ---------------------------------------------------------- */
+/* VADMachine.Config, src/AudioPipeline/VADMachine.zig:18-39 (same fields, same defaults
+ * via fvad_default_config). */
+typedef struct fvad_vad_machine_config {
+    float  speech_min_freq;
+    float  speech_max_freq;
+    float  long_term_speech_avg_sec;
+    int32_t has_initial_long_term_avg;      /* the Zig field is ?f64; 0 = null */
+    double initial_long_term_avg;
+    float  short_term_speech_avg_sec;
+    float  speech_threshold_factor;
+    float  channel_vol_ratio_avg_sec;
+    float  channel_vol_ratio_threshold;
+    float  min_consecutive_sec_to_open;
+    float  max_speech_gap_sec;
+    float  min_vad_duration_sec;
+} fvad_vad_machine_config;
+
+/* VAD.Config, src/AudioPipeline/VAD.zig:17-23 */
+typedef struct fvad_vad_config {
+    size_t  fft_size;                                        /* default 2048 */
+    int32_t use_denoiser;                                    /* default 1 */
+    fvad_vad_machine_config vad_machine_config;
+    const fvad_vad_machine_config *alt_vad_machine_configs;  /* may be NULL */
+    size_t  n_alt_vad_machine_configs;
+} fvad_vad_config;
+
+/* AudioPipeline.Config, src/AudioPipeline.zig:20-26 */
+typedef struct fvad_config {
+    size_t  sample_rate;
+    size_t  n_channels;
+    size_t  buffer_length;       /* ?usize; 0 = null (sample_rate*10).  Host ring only: no effect on results */
+    fvad_vad_config vad_config;
+    int32_t skip_processing;
+} fvad_config;
+
+void fvad_default_vad_machine_config(fvad_vad_machine_config *c);
+void fvad_default_config(fvad_config *c, size_t sample_rate, size_t n_channels);
+
+/* VAD.VADSpeechSegment, src/AudioPipeline/VAD.zig:25-30 */
+typedef struct fvad_segment {
+    uint64_t sample_from;
+    uint64_t sample_to;
+    float    debug_rnn_vad;
+    float    debug_avg_speech_vol_ratio;
+} fvad_segment;
+
+/* VAD.VADMachineResult, src/AudioPipeline/VAD.zig:32-42, as emitted by the main machine;
+ * these are what drive AudioPipeline.beginCapture / endCapture (VAD.zig:362-373). */
+typedef enum fvad_recording_state { FVAD_REC_NONE = 0, FVAD_REC_STARTED = 1, FVAD_REC_COMPLETED = 2, FVAD_REC_ABORTED = 3 } fvad_recording_state;
+typedef struct fvad_capture_event {
+    uint64_t at_index;        /* fft_result.index of the STFT frame that produced it */
+    int32_t  recording_state; /* fvad_recording_state */
+    int32_t  _pad;
+    uint64_t sample_number;
+} fvad_capture_event;
+
+/* What VADMachine.run consumes per STFT frame ("shared features", VAD.zig:355-381). */
+typedef struct fvad_stft_record {
+    uint64_t index;        /* fft_result.index */
+    float    min_volume;   /* min over channels of the speech-band sum for the MAIN machine's band */
+    float    vol_ratio;    /* fft_input.volume_ratio */
+    float    rnn_vad;      /* fft_input.vad orelse 0 */
+    float    has_vad;      /* 1.0 if fft_input.vad != null */
+} fvad_stft_record;
+
+/* ---- batch of pipelines (primary API) --------------------------------------------- */
+typedef struct fvad_batch fvad_batch;
+
+/* AudioPipeline.init x n_streams (src/AudioPipeline.zig:39-75, VAD.zig:97-192), all on CUDA
+ * device `device` (-1 = current).  Errors as the reference: sample_rate != 48000 ->
+ * FVAD_EINVALID_SAMPLE_RATE; odd/zero fft_size -> FVAD_EINVALID_FFT_SIZE. */
+int  fvad_batch_create(const fvad_config *cfg, size_t n_streams, int device, fvad_batch **out);
+/* AudioPipeline.deinit */
+void fvad_batch_destroy(fvad_batch *b);
+
+/* AudioPipeline.pushSamples (src/AudioPipeline.zig:86-120) for every stream at once, HOST
+ * buffers: pcm[stream * n_channels + channel] points at n_samples planar f32 in [-1,1].
+ * Input is borrowed until the call returns.  *first_index = total samples written before. */
+int  fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n_samples, uint64_t *first_index);
+/* Same with DEVICE-resident input: sample i of (stream s, channel c) at
+ * d_pcm[s*stream_stride + c*channel_stride + i].  Asynchronous on the batch's CUDA streams;
+ * the input must stay valid until fvad_batch_sync. */
+int  fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t stream_stride, size_t channel_stride,
+                            size_t n_samples, uint64_t *first_index);
+/* Wait for all submitted work; makes segments/events/traces readable. */
+int  fvad_batch_sync(fvad_batch *b);
+/* Back to the state right after create (same config, same device buffers). */
+int  fvad_batch_reset(fvad_batch *b);
+
+/* pipeline.vad.vad_machine.vad_segments (machine_idx 0) / alt_vad_machines[machine_idx-1]
+ * (src/simulator/SimulationInstance.zig:211, VADMachine.zig:63).  The array is owned by the
+ * handle and valid until the next push/reset/destroy.  Implies fvad_batch_sync. */
+int  fvad_batch_segments(fvad_batch *b, size_t stream, int machine_idx, const fvad_segment **segs, size_t *n);
+/* Recording-state results of the main machine, in order (drives the Recorder). */
+int  fvad_batch_events(fvad_batch *b, size_t stream, const fvad_capture_event **events, size_t *n);
+/* Total samples written / consumed by the VAD so far (multi_ring_buffer.total_write_count,
+ * VAD.pipeline_read_count). */
+int  fvad_batch_counts(fvad_batch *b, uint64_t *total_write_count, uint64_t *pipeline_read_count);
+
+/* Optional traces for parity tests and for the config-5 sweep ("shared features").
+ * Bits: 1 = per-STFT-frame records, 2 = denoised PCM, 4 = per-480-frame RNNoise VAD,
+ * 8 = full STFT magnitude spectra.  Set before the first push. */
+enum { FVAD_TRACE_RECORDS = 1, FVAD_TRACE_DENOISED = 2, FVAD_TRACE_RNN_VAD = 4, FVAD_TRACE_SPECTRA = 8 };
+int  fvad_batch_set_trace(fvad_batch *b, unsigned flags);
+/* Copy out (host): returns the number of items available via *n; copies min(cap, *n). */
+int  fvad_batch_trace_records(fvad_batch *b, size_t stream, fvad_stft_record *out, size_t cap, size_t *n);
+int  fvad_batch_trace_denoised(fvad_batch *b, size_t stream, size_t channel, float *out, size_t cap, size_t *n);
+int  fvad_batch_trace_rnn_vad(fvad_batch *b, size_t stream, float *out, size_t cap, size_t *n);
+int  fvad_batch_trace_spectra(fvad_batch *b, size_t stream, size_t channel, float *out, size_t cap_floats, size_t *n_floats);
+
+/* ---- single pipeline = batch of 1 --------------------------------------------------- */
+typedef struct fvad_batch fvad_pipeline;
+int  fvad_pipeline_create(const fvad_config *cfg, fvad_pipeline **out);                 /* AudioPipeline.init */
+int  fvad_pipeline_push(fvad_pipeline *p, const float *const *channel_pcm, size_t n_samples, uint64_t *first_index); /* pushSamples */
+int  fvad_pipeline_segments(fvad_pipeline *p, int machine_idx, const fvad_segment **segs, size_t *n);
+void fvad_pipeline_destroy(fvad_pipeline *p);                                           /* deinit */
+
+/* ---- leaf drop-ins ------------------------------------------------------------------ */
+/* FFT.zig: init/fft/binCount/binWidth/nyquistFreq/freqToBin/binToFreq/deinit (src/FFT.zig:28-144) */
+typedef struct fvad_fft fvad_fft;
+int    fvad_fft_create(size_t n_fft, size_t sample_rate, fvad_fft **out);               /* FFT.init */
+void   fvad_fft_destroy(fvad_fft *f);                                                   /* FFT.deinit */
+/* FFT.fft on a SplitSlice (first,second) of host memory; result = n_fft/2+1 normalised magnitudes. */
+int    fvad_fft_run(fvad_fft *f, const float *first, size_t n_first, const float *second, size_t n_second,
+                    const float *window, size_t n_window, float *result, size_t n_result);
+size_t fvad_fft_bin_count(const fvad_fft *f);
+float  fvad_fft_bin_width(const fvad_fft *f);
+float  fvad_fft_nyquist_freq(const fvad_fft *f);
+int    fvad_fft_freq_to_bin(const fvad_fft *f, float freq, size_t *bin);
+int    fvad_fft_bin_to_freq(const fvad_fft *f, size_t bin, float *freq);
+/* window_fn.hannWindowPeriodic / windowNormFactor (src/audio_utils/window_fn.zig:8-28,51-68), host */
+void   fvad_hann_window_periodic(float *w, size_t n);
+float  fvad_window_norm_factor(const float *w, size_t n);
+
+/* Batched STFT (PipelineFFT.fft + averageVolumeInBand, src/AudioPipeline/PipelineFFT.zig:88-112)
+ * over DEVICE memory: frame f of row r starts at d_pcm[r*row_stride + f*hop]; n_fft samples each;
+ * periodic Hann window.  d_band_sum[r*n_frames+f] = sum of bins min_bin..max_bin (inclusive) of the
+ * normalised magnitudes; d_spectra (may be NULL) gets [r][f][n_fft/2+1] magnitudes. */
+int    fvad_stft_batch(fvad_fft *f, const float *d_pcm, size_t n_rows, size_t row_stride, size_t n_frames,
+                       size_t hop, size_t min_bin, size_t max_bin, float *d_band_sum, float *d_spectra,
+                       void *cuda_stream);
+
+/* Denoiser.zig: init/denoise/getFrameSize/deinit (src/Denoiser.zig:22-70) */
+typedef struct fvad_denoiser fvad_denoiser;
+int    fvad_denoiser_create(fvad_denoiser **out);
+void   fvad_denoiser_destroy(fvad_denoiser *d);
+size_t fvad_denoiser_frame_size(void);                                                   /* 480 */
+/* Denoiser.denoise on a SplitSlice; n_first+n_second must be 480, n_result 480. Host memory. */
+int    fvad_denoiser_denoise(fvad_denoiser *d, const float *first, size_t n_first, const float *second,
+                             size_t n_second, float *result, size_t n_result, float *vad);
+/* Many independent denoisers x many consecutive frames, HOST memory:
+ * pcm[s] -> n_frames*480 normalised samples; out[s] likewise; vad[s] -> n_frames. */
+typedef struct fvad_denoiser_batch fvad_denoiser_batch;
+int    fvad_denoiser_batch_create(size_t n_streams, int device, fvad_denoiser_batch **out);
+void   fvad_denoiser_batch_destroy(fvad_denoiser_batch *d);
+int    fvad_denoiser_batch_run(fvad_denoiser_batch *d, const float *const *pcm, size_t n_frames,
+                               float *const *out, float *const *vad);
+
+/* ---- VADMachine sweep over shared features (BASELINE config 5; VAD.zig:171-183,375-380) - */
+/* records: host [n_streams][n_records]; configs: host [n_configs].  Output: for (stream s,
+ * config k) the segments land at segs[(s*n_configs+k)*max_segs ...] and their count at
+ * counts[s*n_configs+k] (count may exceed max_segs: truncated). */
+int    fvad_vadm_sweep(const fvad_stft_record *records, size_t n_streams, size_t n_records,
+                       const fvad_vad_machine_config *configs, size_t n_configs, size_t sample_rate,
+                       size_t fft_size, int device, fvad_segment *segs, size_t max_segs, uint32_t *counts);
+
+/* ---- seeded synthetic 48 kHz input ------------------------------ */
+/* Bit-identical on host and device.  Sample i of stream `stream_id` (absolute index
+ * first_sample + i).  kind 0 = "onboard": engine bed + radio-speech bursts + gaps. */
+int    fvad_synth_fill_host(float *dst, uint64_t seed, uint64_t stream_id, uint64_t first_sample, size_t n);
+int    fvad_synth_fill_device(float *d_dst, size_t stream_stride, uint64_t seed, uint64_t first_stream_id,
+                              size_t n_streams, uint64_t first_sample, size_t n, void *cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FVAD_H */
