@@ -1,0 +1,841 @@
+// rn_core.cuh -- the arithmetic of RNNoise (lib/rnnoise/src) re-organised for warps.
+//
+// Every routine here is written ONCE as a sequence of lane phases (RN_PHASE ... RN_END).  On the
+// device a phase is the body executed by the 32 lanes of one warp followed by __syncwarp(); on the
+// host (tools/rn_emu, unit tests without a GPU) the same phase is a loop over lane = 0..31.  Values
+// cross phases only through the warp's scratch memory, so the two executions are the same program.
+//
+// Exactness: the library is compiled with -fmad=false / -ffp-contract=off.  Each accumulation below
+// runs in the reference's order on ONE lane (a "chain"); parallelism comes from running independent
+// chains on different lanes and different frames on different warps, never from re-associating a sum.
+#pragma once
+#include "common.cuh"
+#include <math.h>
+
+#if defined(__CUDA_ARCH__)
+#define RN_PHASE { const int lane = threadIdx.x & 31;
+#define RN_END } __syncwarp();
+#else
+#define RN_PHASE for (int lane = 0; lane < 32; lane++) {
+#define RN_END }
+#endif
+#define RN_HD __host__ __device__ inline
+
+namespace fvad {
+namespace rn {
+
+constexpr int kFrame = 480, kWin = 960, kFreq = 481, kNB = 22;
+constexpr int kPBuf = 1728, kPHist = kPBuf - kFrame;      // PITCH_BUF_SIZE, denoise.c:52-55
+constexpr int kPMax = 768, kPMin = 60;
+constexpr int kCeps = 8, kNDelta = 6, kNFeat = 42;
+constexpr int kMaxCand = 15;                              // T0 plus k = 2..15 (pitch.c:460)
+
+struct Tables {                     // pointers valid in the executing address space
+    const float *half_window;       // 480   denoise.c:171-172
+    const float *dct;               // 22x22 denoise.c:173-179
+    const cpx *tw;                  // 960   kiss_fft.c:404-419
+    const short *rev;               // 960   kiss_fft.c:314-343
+    const float *frac, *omf;        // 400: j/band_size and 1 - j/band_size per bin (denoise.c:110-116)
+    const float *tansig;            // 201   tansig_table.h
+    double dct_scale;               // sqrt(2./22), denoise.c:193
+};
+
+__host__ __device__ constexpr int eband(int i) {          // denoise.c:73-76
+    return i == 0 ? 0 : i == 1 ? 1 : i == 2 ? 2 : i == 3 ? 3 : i == 4 ? 4 : i == 5 ? 5 : i == 6 ? 6 : i == 7 ? 7 : i == 8 ? 8
+         : i == 9 ? 10 : i == 10 ? 12 : i == 11 ? 14 : i == 12 ? 16 : i == 13 ? 20 : i == 14 ? 24 : i == 15 ? 28 : i == 16 ? 34
+         : i == 17 ? 40 : i == 18 ? 48 : i == 19 ? 60 : i == 20 ? 78 : 100;
+}
+
+// ------------------------------------------------------------------------------------------
+// 960-point Opus FFT (kiss_fft.c:518-586) on a warp; data in scratch at padded slots
+// ------------------------------------------------------------------------------------------
+RN_HD int s960(int p) { return p + (p >> 4); }            // one pad per 16: every stage is conflict-free
+constexpr int kSlots960 = 960 + 60;
+
+RN_HD void bfly4_tw(cpx &f0, cpx &f1, cpx &f2, cpx &f3, cpx w1, cpx w2, cpx w3) {   // kiss_fft.c:139-160
+    cpx s0 = c_mul(f1, w1), s1 = c_mul(f2, w2), s2 = c_mul(f3, w3);
+    cpx s5 = c_sub(f0, s1);
+    f0 = c_add(f0, s1);
+    cpx s3 = c_add(s0, s2);
+    cpx s4 = c_sub(s0, s2);
+    f2 = c_sub(f0, s3);
+    f0 = c_add(f0, s3);
+    f1.r = s5.r + s4.i; f1.i = s5.i - s4.r;
+    f3.r = s5.r - s4.i; f3.i = s5.i + s4.r;
+}
+RN_HD void bfly4_m1(cpx &f0, cpx &f1, cpx &f2, cpx &f3) {                           // kiss_fft.c:112-131
+    cpx s0 = c_sub(f0, f2);
+    f0 = c_add(f0, f2);
+    cpx s1 = c_add(f1, f3);
+    f2 = c_sub(f0, s1);
+    f0 = c_add(f0, s1);
+    s1 = c_sub(f1, f3);
+    f1.r = s0.r + s1.i; f1.i = s0.i - s1.r;
+    f3.r = s0.r - s1.i; f3.i = s0.i + s1.r;
+}
+
+// The input must already sit at buf[s960(rev[i])] = (1/960) * in[i]  (kiss_fft.c:579-584).
+RN_HD void fft960_warp(cpx *buf, const cpx *tw) {
+    RN_PHASE   // radix-4 m=1 and radix-4 m=4 (N=60, mm=16, fstride 60) on the same 16 points
+        for (int b = lane; b < 60; b += 32) {
+            cpx a[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) a[i] = buf[s960(16 * b + i)];
+#pragma unroll
+            for (int g = 0; g < 4; g++) bfly4_m1(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3]);
+#pragma unroll
+            for (int j = 0; j < 4; j++) bfly4_tw(a[j], a[j + 4], a[j + 8], a[j + 12], tw[j * 60], tw[j * 120], tw[j * 180]);
+#pragma unroll
+            for (int i = 0; i < 16; i++) buf[s960(16 * b + i)] = a[i];
+        }
+    RN_END
+    RN_PHASE   // radix-4 m=16, N=15, mm=64, fstride 15
+        for (int u = lane; u < 240; u += 32) {
+            const int j = u & 15, base = 64 * (u >> 4) + j;
+            cpx f0 = buf[s960(base)], f1 = buf[s960(base + 16)], f2 = buf[s960(base + 32)], f3 = buf[s960(base + 48)];
+            bfly4_tw(f0, f1, f2, f3, tw[j * 15], tw[j * 30], tw[j * 45]);
+            buf[s960(base)] = f0; buf[s960(base + 16)] = f1; buf[s960(base + 32)] = f2; buf[s960(base + 48)] = f3;
+        }
+    RN_END
+    RN_PHASE   // radix-3 m=64, N=5, mm=192, fstride 5 (kf_bfly3, kiss_fft.c:174-226)
+        const float epi3_i = tw[5 * 64].i;
+        for (int u = lane; u < 320; u += 32) {
+            const int k = u & 63, base = 192 * (u >> 6) + k;
+            cpx f0 = buf[s960(base)], f1 = buf[s960(base + 64)], f2 = buf[s960(base + 128)];
+            cpx s1 = c_mul(f1, tw[k * 5]), s2 = c_mul(f2, tw[k * 10]);
+            cpx s3 = c_add(s1, s2), s0 = c_sub(s1, s2);
+            f1.r = f0.r - s3.r * .5f;
+            f1.i = f0.i - s3.i * .5f;
+            s0.r *= epi3_i; s0.i *= epi3_i;
+            f0 = c_add(f0, s3);
+            f2.r = f1.r + s0.i;
+            f2.i = f1.i - s0.r;
+            f1.r = f1.r - s0.i;
+            f1.i = f1.i + s0.r;
+            buf[s960(base)] = f0; buf[s960(base + 64)] = f1; buf[s960(base + 128)] = f2;
+        }
+    RN_END
+    RN_PHASE   // radix-5 m=192, N=1, fstride 1 (kf_bfly5, kiss_fft.c:230-305)
+        const cpx ya = tw[192], yb = tw[384];
+        for (int u = lane; u < 192; u += 32) {
+            cpx s0 = buf[s960(u)];
+            cpx s1 = c_mul(buf[s960(u + 192)], tw[u]);
+            cpx s2 = c_mul(buf[s960(u + 384)], tw[2 * u]);
+            cpx s3 = c_mul(buf[s960(u + 576)], tw[3 * u]);
+            cpx s4 = c_mul(buf[s960(u + 768)], tw[4 * u]);
+            cpx s7 = c_add(s1, s4), s10 = c_sub(s1, s4), s8 = c_add(s2, s3), s9 = c_sub(s2, s3);
+            cpx o0, s5, s6, s11, s12;
+            o0.r = s0.r + (s7.r + s8.r);
+            o0.i = s0.i + (s7.i + s8.i);
+            s5.r = s0.r + (s7.r * ya.r + s8.r * yb.r);
+            s5.i = s0.i + (s7.i * ya.r + s8.i * yb.r);
+            s6.r = s10.i * ya.i + s9.i * yb.i;
+            s6.i = -(s10.r * ya.i + s9.r * yb.i);
+            s11.r = s0.r + (s7.r * yb.r + s8.r * ya.r);
+            s11.i = s0.i + (s7.i * yb.r + s8.i * ya.r);
+            s12.r = s9.i * ya.i - s10.i * yb.i;
+            s12.i = s10.r * yb.i - s9.r * ya.i;
+            buf[s960(u)] = o0;
+            buf[s960(u + 192)] = c_sub(s5, s6);
+            buf[s960(u + 768)] = c_add(s5, s6);
+            buf[s960(u + 384)] = c_add(s11, s12);
+            buf[s960(u + 576)] = c_sub(s11, s12);
+        }
+    RN_END
+}
+
+// ------------------------------------------------------------------------------------------
+// band chains: compute_band_energy / compute_band_corr (denoise.c:100-148).  One lane per band;
+// sum[b] receives band b-1's `frac` terms first, then band b's `1-frac` terms, in bin order.
+// ------------------------------------------------------------------------------------------
+struct SlotSpec { const cpx *b; RN_HD cpx operator[](int k) const { return b[s960(k)]; } };
+struct LinSpec { const cpx *b; RN_HD cpx operator[](int k) const { return b[k]; } };
+
+template <class SX, class SP, bool CORR>
+RN_HD float band_chain(const Tables &t, SX X, SP P, int b) {
+    float s = 0;
+    if (b > 0) {
+        const int lo = eband(b - 1) << 2, hi = eband(b) << 2;
+        for (int k = lo; k < hi; k++) {
+            cpx x = X[k];
+            float tmp;
+            if (CORR) { cpx p = P[k]; tmp = x.r * p.r; tmp += x.i * p.i; }
+            else { tmp = x.r * x.r; tmp += x.i * x.i; }
+            s += t.frac[k] * tmp;
+        }
+    }
+    if (b < kNB - 1) {
+        const int lo = eband(b) << 2, hi = eband(b + 1) << 2;
+        for (int k = lo; k < hi; k++) {
+            cpx x = X[k];
+            float tmp;
+            if (CORR) { cpx p = P[k]; tmp = x.r * p.r; tmp += x.i * p.i; }
+            else { tmp = x.r * x.r; tmp += x.i * x.i; }
+            s += t.omf[k] * tmp;
+        }
+    }
+    if (b == 0 || b == kNB - 1) s *= 2;
+    return s;
+}
+
+// interp_band_gain (denoise.c:150-163) for one bin < 400
+RN_HD int band_of_bin(int k) {          // band index i with 4*eband[i] <= k < 4*eband[i+1]
+    const int e = k >> 2;
+    int i = 0;
+#pragma unroll
+    for (int j = 1; j < kNB - 1; j++) i += (e >= eband(j)) ? 1 : 0;
+    return i;
+}
+RN_HD float band_interp_bin(const Tables &t, const float *bandE, int k) {
+    const int i = band_of_bin(k);
+    return t.omf[k] * bandE[i] + t.frac[k] * bandE[i + 1];
+}
+
+RN_HD float dct_out(const Tables &t, const float *in, int i) {   // dct, denoise.c:184-195
+    float sum = 0;
+    for (int j = 0; j < kNB; j++) sum += in[j] * t.dct[j * kNB + i];
+    return (float)(sum * t.dct_scale);
+}
+
+// window + bit-reversed scatter of a real 960-sample frame: apply_window + forward_transform's load
+// (denoise.c:247-254, 212-220; kiss_fft.c:579-584).  src(i) returns sample i.
+template <class SRC>
+RN_HD void load_windowed(const Tables &t, cpx *buf, SRC src) {
+    RN_PHASE
+        const float scale = 1.f / kWin;
+        for (int i = lane; i < kWin; i += 32) {
+            const float w = t.half_window[i < kFrame ? i : kWin - 1 - i];
+            float x = src(i);
+            x *= w;
+            cpx v; v.r = scale * x; v.i = scale * 0.0f;
+            buf[s960(t.rev[i])] = v;
+        }
+    RN_END
+}
+
+
+// ------------------------------------------------------------------------------------------
+// Warp scratch layouts (floats).  The FFT buffer is reused by analysis / P-spectrum / synthesis.
+// ------------------------------------------------------------------------------------------
+constexpr int kScrFft = 2 * kSlots960;                     // cpx buf[1020]
+constexpr int kScrAna = kScrFft + 96;                      // + misc
+constexpr int kScrSyn = kScrFft + 2 * kFreq + 2 + 96;      // + linear X[481] + misc
+constexpr int kScrPitch = 864 + 296 + 388 + 388 + 64 + 64; // xlp, xc, yyl, ip, list, misc
+
+// frame_analysis + the energy half of compute_frame_features (denoise.c:295-308, 349-362, 363-365):
+// X, Ex, E<0.04 silence flag and the cepstrum dct(Ly) with its -12/-4 offsets.
+// hpb = this state's high-passed signal with kPHist samples of history in front; frame q starts at
+// hpb[kPHist + q*480].
+RN_HD void analysis_warp(const Tables &t, const float *hpb, int q, cpx *Xq, float *Exq, float *cepsq, int *silq,
+                         float *scr) {
+    cpx *buf = reinterpret_cast<cpx *>(scr);
+    float *misc = scr + kScrFft;                           // [0..21] Ex, [32..53] Ly, [60] E
+    const float *x0 = hpb + (kPHist - kFrame) + (size_t)q * kFrame;   // analysis_mem | in
+    load_windowed(t, buf, [&](int i) { return x0[i]; });
+    fft960_warp(buf, t.tw);
+    RN_PHASE
+        for (int k = lane; k < kFreq; k += 32) Xq[k] = buf[s960(k)];
+        if (lane < kNB) misc[lane] = band_chain<SlotSpec, SlotSpec, false>(t, SlotSpec{buf}, SlotSpec{buf}, lane);
+    RN_END
+    RN_PHASE
+        if (lane < kNB) Exq[lane] = misc[lane];
+        if (lane == 0) {
+            float logMax = -2, follow = -2, E = 0;
+            for (int i = 0; i < kNB; i++) {                // denoise.c:351-357
+                float ly = (float)log10(1e-2 + misc[i]);
+                double a = follow - 1.5;
+                double inner_max = a > ly ? a : (double)ly;
+                float lm7 = logMax - 7;
+                ly = (float)(lm7 > inner_max ? (double)lm7 : inner_max);
+                logMax = logMax > ly ? logMax : ly;
+                a = follow - 1.5;
+                follow = (float)(a > ly ? a : (double)ly);
+                E += misc[i];
+                misc[32 + i] = ly;
+            }
+            *silq = (E < 0.04) ? 1 : 0;                     // denoise.c:358 (float < double literal)
+        }
+    RN_END
+    RN_PHASE
+        if (lane < kNB) {
+            float c = dct_out(t, misc + 32, lane);
+            if (lane == 0) c -= 12;
+            if (lane == 1) c -= 4;
+            cepsq[lane] = c;
+        }
+    RN_END
+}
+
+// ------------------------------------------------------------------------------------------
+// pitch analysis: pitch_downsample + pitch_search + everything of remove_doubling that does not
+// depend on the previous frame (pitch.c:148-216, 283-385, 423-458; celt_lpc.c:37-88, 198-279).
+// Output: the candidate table the sequential decision (pitch_decide) walks.
+// ------------------------------------------------------------------------------------------
+struct PitchCand {                 // per frame
+    int n;                         // candidates: index 0 is T0, index c is k = c+1
+    short T[kMaxCand];
+    signed char off[kMaxCand];     // pseudo-interpolation offset if this candidate wins (pitch.c:511-517)
+    float g[kMaxCand], xy[kMaxCand], yy[kMaxCand];
+};
+
+template <class YF>
+RN_HD void best_pitch2(const float *xcorr, YF y, int len, int max_pitch, int *best) {   // find_best_pitch, pitch.c:46-104
+    float Syy = 1;
+    float best_num0 = -1, best_num1 = -1, best_den0 = 0, best_den1 = 0;
+    best[0] = 0; best[1] = 1;
+    for (int j = 0; j < len; j++) Syy = Syy + y(j) * y(j);
+    for (int i = 0; i < max_pitch; i++) {
+        if (xcorr[i] > 0) {
+            float x16 = xcorr[i];
+            x16 *= 1e-12f;
+            const float num = x16 * x16;
+            if (num * best_den1 > best_num1 * Syy) {
+                if (num * best_den0 > best_num0 * Syy) {
+                    best_num1 = best_num0; best_den1 = best_den0; best[1] = best[0];
+                    best_num0 = num; best_den0 = Syy; best[0] = i;
+                } else {
+                    best_num1 = num; best_den1 = Syy; best[1] = i;
+                }
+            }
+        }
+        Syy += y(i + len) * y(i + len) - y(i) * y(i);
+        Syy = Syy < 1 ? 1 : Syy;
+    }
+}
+
+RN_HD float pitch_gain(float xy, float xx, float yy) {     // compute_pitch_gain, pitch.c:416-419
+    return (float)(xy / sqrt((double)(1 + xx * yy)));
+}
+
+RN_HD void pitch_warp(const Tables &t, const float *hpb, int q, PitchCand *out, float *scr) {
+    float *xlp = scr, *xc = scr + 864, *yyl = xc + 296, *ip = yyl + 388;
+    int *list = reinterpret_cast<int *>(ip + 388);
+    float *misc = reinterpret_cast<float *>(list + 64);    // [0..4] ac, [8..12] num, ints below
+    int *imisc = reinterpret_cast<int *>(misc + 16);       // [0] best0 [1] best1 [2] T0 [3] nlist [4] ncand; [5..] candT, candTb
+    const float *x = hpb + (size_t)q * kFrame;             // pitch_buf of frame q (1728 samples)
+    (void)t;
+    RN_PHASE   // pitch_downsample, pitch.c:171-173
+        for (int i = lane; i < 864; i += 32)
+            xlp[i] = (i == 0) ? .5f * (.5f * x[1] + x[0]) : .5f * (.5f * (x[2 * i - 1] + x[2 * i + 1]) + x[2 * i]);
+    RN_END
+    RN_PHASE   // _celt_autocorr lag 0..4: fastN = 860 in-order chain, then the tail (celt_lpc.c:261-267)
+        if (lane < 5) {
+            const int k = lane;
+            float a = 0;
+            for (int j = 0; j < 860; j++) a = a + xlp[j] * xlp[j + k];
+            float d = 0;
+            for (int i = k + 860; i < 864; i++) d = d + xlp[i] * xlp[i - k];
+            misc[k] = a + d;
+        }
+    RN_END
+    RN_PHASE
+        if (lane == 0) {
+            float ac[5];
+            for (int i = 0; i < 5; i++) ac[i] = misc[i];
+            ac[0] *= 1.0001f;                              // pitch.c:187
+            for (int i = 1; i <= 4; i++) ac[i] -= ac[i] * (.008f * i) * (.008f * i);   // pitch.c:196
+            float lpc[4] = {0, 0, 0, 0};
+            float error = ac[0];
+            if (ac[0] != 0) {                              // _celt_lpc, celt_lpc.c:55-82
+                for (int i = 0; i < 4; i++) {
+                    float rr = 0;
+                    for (int j = 0; j < i; j++) rr += lpc[j] * ac[i - j];
+                    rr += ac[i + 1];
+                    const float r = -rr / error;
+                    lpc[i] = r;
+                    for (int j = 0; j < (i + 1) >> 1; j++) {
+                        const float t1 = lpc[j], t2 = lpc[i - 1 - j];
+                        lpc[j] = t1 + r * t2;
+                        lpc[i - 1 - j] = t2 + r * t1;
+                    }
+                    error = error - (r * r) * error;
+                    if (error < .001f * ac[0]) break;
+                }
+            }
+            float tmp = 1.0f;
+            for (int i = 0; i < 4; i++) { tmp = .9f * tmp; lpc[i] = lpc[i] * tmp; }   // pitch.c:201-205
+            const float c1 = .8f;
+            misc[8] = lpc[0] + .8f;
+            misc[9] = lpc[1] + c1 * lpc[0];
+            misc[10] = lpc[2] + c1 * lpc[1];
+            misc[11] = lpc[3] + c1 * lpc[2];
+            misc[12] = c1 * lpc[3];
+        }
+    RN_END
+    // celt_fir5 (pitch.c:106-145) in place: taps read the ORIGINAL x_lp, so compute all, then store.
+#if defined(__CUDA_ARCH__)
+    float yv[27];
+#define RN_YV(r) yv[r]
+#else
+    static thread_local float yv_all[32][27];
+#define RN_YV(r) yv_all[lane][r]
+#endif
+    RN_PHASE
+        const float n0 = misc[8], n1 = misc[9], n2 = misc[10], n3 = misc[11], n4 = misc[12];
+#pragma unroll
+        for (int r = 0; r < 27; r++) {
+            const int i = lane + 32 * r;
+            float sum = xlp[i];
+            sum = sum + n0 * (i >= 1 ? xlp[i - 1] : 0.0f);
+            sum = sum + n1 * (i >= 2 ? xlp[i - 2] : 0.0f);
+            sum = sum + n2 * (i >= 3 ? xlp[i - 3] : 0.0f);
+            sum = sum + n3 * (i >= 4 ? xlp[i - 4] : 0.0f);
+            sum = sum + n4 * (i >= 5 ? xlp[i - 5] : 0.0f);
+            RN_YV(r) = sum;
+        }
+    RN_END
+    RN_PHASE
+#pragma unroll
+        for (int r = 0; r < 27; r++) xlp[lane + 32 * r] = RN_YV(r);
+    RN_END
+#undef RN_YV
+    RN_PHASE   // coarse search, 4x decimation: celt_pitch_xcorr(x_lp4, y_lp4, xcorr, 240, 147) (pitch.c:335)
+        for (int i = lane; i < 147; i += 32) {
+            float s = 0;
+            for (int j = 0; j < 240; j++) s = s + xlp[384 + 2 * j] * xlp[2 * (i + j)];
+            xc[i] = s;
+        }
+    RN_END
+    RN_PHASE
+        if (lane == 0) {
+            int best[2];
+            best_pitch2(xc, [&](int j) { return xlp[2 * j]; }, 240, 147, best);
+            imisc[0] = best[0]; imisc[1] = best[1];
+        }
+    RN_END
+    RN_PHASE
+        for (int i = lane; i < 294; i += 32) xc[i] = 0;    // pitch.c:352
+    RN_END
+    RN_PHASE   // fine search, 2x decimation (pitch.c:349-366): only lags within 2 of a coarse best
+        if (lane < 10) {
+            const int b0 = imisc[0], b1 = imisc[1];
+            const int i = lane < 5 ? 2 * b0 + lane - 2 : 2 * b1 + lane - 7;
+            if (i >= 0 && i < 294) {
+                float s = 0;
+                for (int j = 0; j < 480; j++) s = s + xlp[384 + j] * xlp[i + j];
+                xc[i] = s < -1 ? -1 : s;
+            }
+        }
+    RN_END
+    RN_PHASE
+        if (lane == 0) {
+            int best[2] = {imisc[0], imisc[1]};
+            best_pitch2(xc, [&](int j) { return xlp[j]; }, 480, 294, best);
+            int offset = 0;
+            if (best[0] > 0 && best[0] < 294 - 1) {        // pitch.c:371-384
+                const float a = xc[best[0] - 1], b = xc[best[0]], c = xc[best[0] + 1];
+                if ((c - a) > .7f * (b - a)) offset = 1;
+                else if ((a - c) > .7f * (b - c)) offset = -1;
+            }
+            int pitch_index = kPMax - (2 * best[0] - offset);   // denoise.c:330
+            // remove_doubling's frame-local part (pitch.c:436-445, 460-478)
+            int T0 = pitch_index / 2;
+            if (T0 >= 384) T0 = 383;
+            imisc[2] = T0;
+            unsigned need[13];
+            for (int w = 0; w < 13; w++) need[w] = 0;
+            auto mark = [&](int lag) { need[lag >> 5] |= 1u << (lag & 31); };
+            mark(T0 - 1); mark(T0); mark(T0 + 1);
+            int nc = 1;
+            const int second_check[16] = {0, 0, 3, 2, 3, 2, 5, 2, 3, 2, 3, 2, 5, 2, 3, 2};
+            for (int k = 2; k <= 15; k++) {
+                const int T1 = (2 * T0 + k) / (2 * k);
+                if (T1 < 30) break;
+                int T1b;
+                if (k == 2) T1b = (T1 + T0 > 384) ? T0 : T0 + T1;
+                else T1b = (2 * second_check[k] * T0 + k) / (2 * k);
+                imisc[5 + 2 * nc] = T1; imisc[6 + 2 * nc] = T1b;
+                mark(T1 - 1); mark(T1); mark(T1 + 1); mark(T1b);
+                nc++;
+            }
+            imisc[4] = nc;
+            int nl = 0;
+            for (int lag = 1; lag <= 384; lag++)
+                if (need[lag >> 5] & (1u << (lag & 31))) list[nl++] = lag;
+            imisc[3] = nl;
+        }
+    RN_END
+    RN_PHASE   // inner products by lag: ip[lag] = sum_i x[i]*x[i-lag], x = x_lp + 384, N = 480
+        if (lane == 0) {
+            float xx = 0;                                  // dual_inner_prod's xx, pitch.c:446
+            for (int i = 0; i < 480; i++) xx = xx + xlp[384 + i] * xlp[384 + i];
+            ip[0] = xx;
+            yyl[0] = xx;
+            float yy = xx;
+            for (int i = 1; i <= 384; i++) {               // pitch.c:449-453
+                yy = yy + xlp[384 - i] * xlp[384 - i] - xlp[384 + 480 - i] * xlp[384 + 480 - i];
+                yyl[i] = yy < 0 ? 0 : yy;
+            }
+        } else {
+            const int nl = imisc[3];
+            for (int idx = lane - 1; idx < nl; idx += 31) {
+                const int lag = list[idx];
+                float s = 0;
+                for (int i = 0; i < 480; i++) s = s + xlp[384 + i] * xlp[384 + i - lag];
+                ip[lag] = s;
+            }
+        }
+    RN_END
+    RN_PHASE
+        const int nc = imisc[4];
+        if (lane < nc) {
+            const int T0 = imisc[2];
+            const float xx = ip[0];
+            int T; float xy, yy;
+            if (lane == 0) { T = T0; xy = ip[T0]; yy = yyl[T0]; }
+            else {
+                const int T1 = imisc[5 + 2 * lane], T1b = imisc[6 + 2 * lane];
+                T = T1;
+                xy = .5f * (ip[T1] + ip[T1b]);             // pitch.c:479-480
+                yy = .5f * (yyl[T1] + yyl[T1b]);
+            }
+            out->T[lane] = (short)T;
+            out->xy[lane] = xy; out->yy[lane] = yy;
+            out->g[lane] = pitch_gain(xy, xx, yy);
+            const float x0 = ip[T - 1], x1 = ip[T], x2 = ip[T + 1];       // pitch.c:509-517
+            int off;
+            if ((x2 - x0) > .7f * (x1 - x0)) off = 1;
+            else if ((x0 - x2) > .7f * (x1 - x2)) off = -1;
+            else off = 0;
+            out->off[lane] = (signed char)off;
+        }
+        if (lane == 0) out->n = nc;
+    RN_END
+}
+
+// The sequential part of remove_doubling (pitch.c:459-525): walks the candidate table with the
+// previous frame's period and gain.  Returns the pitch index; *gain_out is the new last_gain.
+RN_HD int pitch_decide(const PitchCand &c, int prev_period, float prev_gain, float *gain_out) {
+    const int T0 = c.T[0];
+    const float g0 = c.g[0];
+    int T = T0, off = c.off[0];
+    float g = g0, best_xy = c.xy[0], best_yy = c.yy[0];
+    prev_period /= 2;
+    for (int i = 1; i < c.n; i++) {
+        const int k = i + 1, T1 = c.T[i];
+        const float g1 = c.g[i];
+        float cont;
+        const int d = T1 - prev_period, ad = d < 0 ? -d : d;
+        if (ad <= 1) cont = prev_gain;
+        else if (ad <= 2 && 5 * k * k < T0) cont = .5f * prev_gain;
+        else cont = 0;
+        float a = .7f * g0 - cont;
+        float thresh = .3f > a ? .3f : a;
+        if (T1 < 90) { a = .85f * g0 - cont; thresh = .4f > a ? .4f : a; }
+        if (g1 > thresh) { best_xy = c.xy[i]; best_yy = c.yy[i]; T = T1; g = g1; off = c.off[i]; }
+    }
+    best_xy = best_xy < 0 ? 0 : best_xy;
+    float pg;
+    if (best_yy <= best_xy) pg = 1.0f;
+    else pg = best_xy / (best_yy + 1);
+    if (pg > g) pg = g;
+    int idx = 2 * T + off;
+    if (idx < kPMin) idx = kPMin;
+    *gain_out = pg;
+    return idx;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// pitch-lagged spectrum and the pitch-correlation features (denoise.c:337-348)
+// featB[0..5] = features[34..39], featB[6] = features[40]
+// ------------------------------------------------------------------------------------------
+RN_HD void pfeat_warp(const Tables &t, const float *hpb, int q, int pitch_index, const cpx *Xq, const float *Exq,
+                      cpx *Pq, float *Epq, float *Expq, float *featB, float *scr) {
+    cpx *buf = reinterpret_cast<cpx *>(scr);
+    float *misc = scr + kScrFft;                           // [0..21] Ep, [32..53] Exp
+    const float *p0 = hpb + (size_t)q * kFrame + (kPBuf - kWin - pitch_index);   // denoise.c:337-338
+    load_windowed(t, buf, [&](int i) { return p0[i]; });
+    fft960_warp(buf, t.tw);
+    RN_PHASE
+        for (int k = lane; k < kFreq; k += 32) Pq[k] = buf[s960(k)];
+        if (lane < kNB) {
+            const float ep = band_chain<SlotSpec, SlotSpec, false>(t, SlotSpec{buf}, SlotSpec{buf}, lane);
+            float exp_ = band_chain<LinSpec, SlotSpec, true>(t, LinSpec{Xq}, SlotSpec{buf}, lane);
+            exp_ = (float)(exp_ / sqrt(.001 + Exq[lane] * ep));        // denoise.c:343
+            misc[lane] = ep; misc[32 + lane] = exp_;
+            Epq[lane] = ep; Expq[lane] = exp_;
+        }
+    RN_END
+    RN_PHASE
+        if (lane < kNDelta) {
+            float v = dct_out(t, misc + 32, lane);                     // denoise.c:344-347
+            if (lane == 0) v = (float)(v - 1.3);
+            if (lane == 1) v = (float)(v - 0.9);
+            featB[lane] = v;
+        }
+        if (lane == 6) featB[6] = (float)(.01 * (pitch_index - 300));   // denoise.c:348
+    RN_END
+}
+
+// ------------------------------------------------------------------------------------------
+// cepstral ring features (denoise.c:366-398) for the non-silent frame whose global rank among
+// non-silent frames is `rank`; cc points at its own entry of the compacted cepstrum list, so that
+// cc - k*22 is the cepstrum k non-silent frames earlier (zeros before the first).
+// ------------------------------------------------------------------------------------------
+RN_HD void cepsfeat_warp(const float *cc, long long rank, const float *featB, float *feat, float *scr) {
+    float *dist = scr;            // 64
+    float *mind = scr + 64;       // 8
+    const int memid = (int)(rank & 7);
+    RN_PHASE
+        for (int p = lane; p < 64; p += 32) {
+            const int i = p >> 3, j = p & 7;
+            const float *ci = cc - ((memid - i + 8) & 7) * kNB;        // slot i holds rank - ((memid-i) mod 8)
+            const float *cj = cc - ((memid - j + 8) & 7) * kNB;
+            float d = 0;
+            for (int k = 0; k < kNB; k++) {
+                const float tmp = ci[k] - cj[k];
+                d += tmp * tmp;
+            }
+            dist[p] = d;
+        }
+    RN_END
+    RN_PHASE
+        if (lane < kCeps) {
+            float m = 1e15f;
+            for (int j = 0; j < kCeps; j++)
+                if (j != lane) m = m < dist[lane * 8 + j] ? m : dist[lane * 8 + j];
+            mind[lane] = m;
+        }
+        const float *c0 = cc, *c1 = cc - kNB, *c2 = cc - 2 * kNB;
+        if (lane < kNB) {
+            if (lane < kNDelta) {
+                feat[lane] = c0[lane] + c1[lane] + c2[lane];
+                feat[kNB + lane] = c0[lane] - c2[lane];
+                feat[kNB + kNDelta + lane] = c0[lane] - 2 * c1[lane] + c2[lane];
+            } else {
+                feat[lane] = c0[lane];
+            }
+        }
+        if (lane < 7) feat[kNB + 2 * kNDelta + lane] = featB[lane];
+    RN_END
+    RN_PHASE
+        if (lane == 0) {
+            float sv = 0;
+            for (int i = 0; i < kCeps; i++) sv += mind[i];
+            feat[kNB + 3 * kNDelta + 1] = (float)(sv / kCeps - 2.1);
+        }
+    RN_END
+}
+
+// ------------------------------------------------------------------------------------------
+// pitch_filter + gains + frame_synthesis (denoise.c:422-456, 475-490, 401-408, 227-245).
+// g_rnn = the RNN's band gains, g_sm = after the 0.6*lastg floor (computed by the gain scan).
+// head = first 480 windowed samples, tail = last 480 (the next frame's synthesis_mem).
+// ------------------------------------------------------------------------------------------
+RN_HD void synth_warp(const Tables &t, const cpx *Xq, const cpx *Pq, const float *Exq, const float *Epq,
+                      const float *Expq, const float *g_rnn, const float *g_sm, int silence, float *head,
+                      float *tail, float *scr) {
+    cpx *buf = reinterpret_cast<cpx *>(scr);
+    cpx *X = reinterpret_cast<cpx *>(scr + kScrFft);
+    float *misc = scr + kScrFft + 2 * kFreq + 2;           // [0..21] r, [32..53] norm, [64..85] g_sm copy
+    RN_PHASE
+        for (int k = lane; k < kFreq; k += 32) X[k] = Xq[k];
+        if (!silence && lane < kNB) {
+            const float e = Expq[lane], g = g_rnn[lane];
+            float r;
+            if (e > g) r = 1;
+            else r = (float)((e * e) * (1 - (g * g)) / (.001 + (g * g) * (1 - (e * e))));
+            float c = 0 > r ? 0 : r;
+            c = 1 < c ? 1 : c;
+            r = (float)sqrt((double)c);
+            r = (float)(r * sqrt(Exq[lane] / (1e-8 + Epq[lane])));
+            misc[lane] = r;
+            misc[64 + lane] = g_sm[lane];
+        }
+    RN_END
+    if (!silence) {
+        RN_PHASE
+            for (int k = lane; k < kFreq; k += 32) {
+                const float rf = k < 400 ? band_interp_bin(t, misc, k) : 0.0f;
+                const cpx p = Pq[k];
+                X[k].r += rf * p.r;
+                X[k].i += rf * p.i;
+            }
+        RN_END
+        RN_PHASE
+            if (lane < kNB) {
+                const float ne = band_chain<LinSpec, LinSpec, false>(t, LinSpec{X}, LinSpec{X}, lane);
+                misc[32 + lane] = (float)sqrt(Exq[lane] / (1e-8 + ne));
+            }
+        RN_END
+        RN_PHASE
+            for (int k = lane; k < kFreq; k += 32) {
+                const float nf = k < 400 ? band_interp_bin(t, misc + 32, k) : 0.0f;
+                const float gf = k < 400 ? band_interp_bin(t, misc + 64, k) : 0.0f;
+                X[k].r *= nf; X[k].i *= nf;
+                X[k].r *= gf; X[k].i *= gf;
+            }
+        RN_END
+    }
+    RN_PHASE   // inverse_transform's Hermitian extension + the forward FFT's scaled bit-reversed load
+        const float scale = 1.f / kWin;
+        for (int i = lane; i < kWin; i += 32) {
+            cpx v;
+            if (i < kFreq) v = X[i];
+            else { v.r = X[kWin - i].r; v.i = -X[kWin - i].i; }
+            cpx o; o.r = scale * v.r; o.i = scale * v.i;
+            buf[s960(t.rev[i])] = o;
+        }
+    RN_END
+    fft960_warp(buf, t.tw);
+    RN_PHASE
+        for (int i = lane; i < kWin; i += 32) {
+            float v = kWin * buf[s960(i == 0 ? 0 : kWin - i)].r;        // denoise.c:240-244
+            v *= t.half_window[i < kFrame ? i : kWin - 1 - i];
+            if (i < kFrame) head[i] = v; else tail[i - kFrame] = v;
+        }
+    RN_END
+}
+
+// ------------------------------------------------------------------------------------------
+// activations (rnn.c:41-72)
+// ------------------------------------------------------------------------------------------
+RN_HD float tansig_approx(const float *table, float x) {
+    float y, dy, sign = 1;
+    if (!(x < 8)) return 1;
+    if (!(x > -8)) return -1;
+    if (x != x) return 0;
+    if (x < 0) { x = -x; sign = -1; }
+    const int i = (int)floor((double)(.5f + 25 * x));
+    x -= .04f * i;
+    y = table[i];
+    dy = 1 - y * y;
+    y = y + x * dy * (1 - y * x);
+    return sign * y;
+}
+RN_HD float sigmoid_approx(const float *table, float x) {
+    return (float)(.5 + .5 * tansig_approx(table, (float)(.5 * x)));
+}
+
+
+// ------------------------------------------------------------------------------------------
+// compute_rnn (rnn.c:160-178) for one state, executed by a CTA of kRnnThreads threads.
+// Weights: per layer one matrix W[j][col] (bf16 bit patterns: every int8 weight is exact in bf16),
+// j running over the layer's inputs and then, for a GRU, its recurrent inputs -- the order in which
+// compute_gru accumulates (rnn.c:122-127).  Columns: z | r | h gates.
+// ------------------------------------------------------------------------------------------
+#if defined(__CUDA_ARCH__)
+#define RN_CTA_PHASE { const int tid = threadIdx.x;
+#define RN_CTA_END } __syncthreads();
+#else
+#define RN_CTA_PHASE for (int tid = 0; tid < ::fvad::rn::kRnnThreads; tid++) {
+#define RN_CTA_END }
+#endif
+
+constexpr int kRnnThreads = 288;
+struct RnnLayer { int J, M, cols, w_off, b_off; };        // J = chain length, M = inputs before the recurrent part
+constexpr int kL_in = 0, kL_vad = 1, kL_vout = 2, kL_noise = 3, kL_den = 4, kL_out = 5;
+__host__ __device__ constexpr RnnLayer rnn_layer(int l) {
+    return l == 0 ? RnnLayer{42, 42, 24, 0, 0}
+         : l == 1 ? RnnLayer{48, 24, 72, 1008, 24}
+         : l == 2 ? RnnLayer{24, 24, 1, 4464, 96}
+         : l == 3 ? RnnLayer{138, 90, 144, 4488, 97}
+         : l == 4 ? RnnLayer{210, 114, 288, 24360, 241}
+         :          RnnLayer{96, 96, 22, 84840, 529};
+}
+constexpr int kRnnWeights = 86952, kRnnBiases = 551;
+// scratch floats of the CTA, after the weights: vectors
+constexpr int kRv_feat = 0, kRv_v1 = 48, kRv_v3 = 96, kRv_v4 = 240, kRv_zr = 456, kRv_hp = 648, kRv_hn = 744, kRv_end = 840;
+
+RN_HD float bf16_to_f32(unsigned short b) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(((unsigned)b) << 16);
+#else
+    union { unsigned u; float f; } c; c.u = ((unsigned)b) << 16; return c.f;
+#endif
+}
+
+// bias + sum_{j in [j0,j1)} W[j][col]*v[j]   continuing from `sum`
+RN_HD float rnn_chain(const unsigned short *W, int cols, int col, const float *v, int j0, int j1, float sum) {
+    for (int j = j0; j < j1; j++) sum += bf16_to_f32(W[j * cols + col]) * v[j];
+    return sum;
+}
+// recurrent part of the candidate gate: sum += (W[j][col]*state[j-M])*r[j-M]  (rnn.c:147)
+RN_HD float rnn_chain_r(const unsigned short *W, int cols, int col, const float *v, const float *r, int M, int J, float sum) {
+    for (int j = M; j < J; j++) sum += bf16_to_f32(W[j * cols + col]) * v[j] * r[j - M];
+    return sum;
+}
+
+constexpr float kWScale = 1.f / 256;
+
+// One GRU layer: v = [inputs(M) | state(N)], zr/hp/hn scratch.  Three CTA phases.
+RN_HD void rnn_gru_cta(const unsigned short *W, const float *bias, const float *tansig, int layer, float *v,
+                       float *zr, float *hp, float *hn) {
+    const RnnLayer L = rnn_layer(layer);
+    const int N = L.cols / 3;
+    const unsigned short *Wl = W + L.w_off;
+    const float *bl = bias + L.b_off;
+    RN_CTA_PHASE
+        if (tid < 2 * N) {                                   // update and reset gates (rnn.c:119-139)
+            const float s = rnn_chain(Wl, L.cols, tid, v, 0, L.J, bl[tid]);
+            zr[tid] = sigmoid_approx(tansig, kWScale * s);
+        } else if (tid < 3 * N) {                            // candidate: input part (rnn.c:143-145)
+            hp[tid - 2 * N] = rnn_chain(Wl, L.cols, tid, v, 0, L.M, bl[tid]);
+        }
+    RN_CTA_END
+    RN_CTA_PHASE
+        if (tid < N) {                                       // candidate: recurrent part, ReLU, blend (rnn.c:146-152)
+            float s = rnn_chain_r(Wl, L.cols, 2 * N + tid, v, zr + N, L.M, L.J, hp[tid]);
+            s = kWScale * s;
+            s = s < 0 ? 0 : s;
+            const float z = zr[tid];
+            hn[tid] = z * v[L.M + tid] + (1 - z) * s;
+        }
+    RN_CTA_END
+}
+
+// Whole network for one frame.  scr = vectors (kRv_* offsets); feat already at scr[kRv_feat..+42).
+RN_HD void rnn_frame_cta(const unsigned short *W, const float *bias, const float *tansig, float *scr, float *gains_out,
+                         float *vad_out) {
+    float *feat = scr + kRv_feat, *v1 = scr + kRv_v1, *v3 = scr + kRv_v3, *v4 = scr + kRv_v4;
+    float *zr = scr + kRv_zr, *hp = scr + kRv_hp, *hn = scr + kRv_hn;
+    RN_CTA_PHASE
+        if (tid < 24) {                                      // input_dense, tanh (rnn.c:79-107)
+            const RnnLayer L = rnn_layer(kL_in);
+            const float s = rnn_chain(W + L.w_off, L.cols, tid, feat, 0, L.J, bias[L.b_off + tid]);
+            v1[tid] = tansig_approx(tansig, kWScale * s);
+        }
+    RN_CTA_END
+    rnn_gru_cta(W, bias, tansig, kL_vad, v1, zr, hp, hn);
+    RN_CTA_PHASE
+        if (tid < 24) { v1[24 + tid] = hn[tid]; v3[24 + tid] = hn[tid]; v4[tid] = hn[tid]; }   // vad_gru_state
+        else if (tid < 48) v3[tid - 24] = v1[tid - 24];                                      // dense_out
+        else if (tid < 90) { v3[48 + tid - 48] = feat[tid - 48]; v4[72 + tid - 48] = feat[tid - 48]; }
+    RN_CTA_END
+    RN_CTA_PHASE
+        if (tid == kRnnThreads - 1) {                        // vad_output, sigmoid (rnn.c:166)
+            const RnnLayer L = rnn_layer(kL_vout);
+            const float s = rnn_chain(W + L.w_off, L.cols, 0, v1 + 24, 0, L.J, bias[L.b_off]);
+            *vad_out = sigmoid_approx(tansig, kWScale * s);
+        }
+    RN_CTA_END
+    rnn_gru_cta(W, bias, tansig, kL_noise, v3, zr, hp, hn);
+    RN_CTA_PHASE
+        if (tid < 48) { v3[90 + tid] = hn[tid]; v4[24 + tid] = hn[tid]; }                    // noise_gru_state
+    RN_CTA_END
+    rnn_gru_cta(W, bias, tansig, kL_den, v4, zr, hp, hn);
+    RN_CTA_PHASE
+        if (tid < 96) v4[114 + tid] = hn[tid];                                               // denoise_gru_state
+    RN_CTA_END
+    RN_CTA_PHASE
+        if (tid < 22) {                                      // denoise_output, sigmoid (rnn.c:177)
+            const RnnLayer L = rnn_layer(kL_out);
+            const float s = rnn_chain(W + L.w_off, L.cols, tid, v4 + 114, 0, L.J, bias[L.b_off + tid]);
+            gains_out[tid] = sigmoid_approx(tansig, kWScale * s);
+        }
+    RN_CTA_END
+}
+
+// biquad (denoise.c:410-420) with the Denoiser's x32767 input scaling (Denoiser.zig:72-82)
+RN_HD float biquad_step(float in_norm, float &m0, float &m1) {
+    const float a0 = -1.99599f, a1 = 0.99600f, b0 = -2.f, b1 = 1.f;     // denoise.c:470-471
+    const float xi = in_norm * 32767.0f;
+    const float yi = xi + m0;
+    m0 = (float)(m1 + (b0 * (double)xi - a0 * (double)yi));
+    m1 = (float)(b1 * (double)xi - a1 * (double)yi);
+    return yi;
+}
+
+}  // namespace rn
+}  // namespace fvad

@@ -1,0 +1,534 @@
+// rnnoise.cu -- batched RNNoise on the GPU: kernels + tile orchestration (see rnnoise.cuh).
+//
+// What is sequential in rnnoise_process_frame (denoise.c:458-494) and what is not:
+//   sample-sequential : biquad (denoise.c:410-420)                          -> k_rn_biquad, one lane per state
+//   frame-sequential  : remove_doubling's prev_period/prev_gain decision      -> k_rn_pitch_seq (tiny)
+//                       cepstral ring position (only non-silent frames count) -> k_rn_compact (prefix count)
+//                       the three GRUs (rnn.c:109-156)                        -> k_rn_rnn, one CTA per state
+//                       lastg floor (denoise.c:478-482)                       -> k_rn_gain_scan
+//   frame-parallel    : everything else (3 FFTs, band energies, pitch correlations, DCTs, synthesis)
+//                                                                             -> warp-per-frame kernels
+// All arithmetic lives in rn_core.cuh and runs in the reference's operation order.
+#include "rnnoise.cuh"
+#include "rn_core.cuh"
+#include "rn_tables.cuh"
+#include <algorithm>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+namespace fvad {
+using namespace rn;
+
+struct RnPersist {                 // per state, lives across tiles (DenoiseState, denoise.c:86-98)
+    float biq[2];
+    int last_period;
+    float last_gain;
+    long long nz_total;            // non-silent frames so far: cepstral ring position = nz_total & 7
+    int nz_tile;                   // non-silent frames of the current tile
+    int _pad;
+    float lastg[kNB];
+    float rnn_vec[kRv_end];        // RNN vectors incl. the three GRU states
+};
+
+struct RnDevTables {
+    Tables t{};
+    unsigned short *weights = nullptr;
+    float *bias = nullptr;
+};
+
+struct RnnoiseBatch {
+    int device = 0;
+    size_t N = 0, Qcap = 0;
+    RnDevTables tab;
+    RnPersist *persist = nullptr;
+    // tile arrays, [state][frame] major
+    float *hp = nullptr;           // [N][kPHist + Qcap*480]
+    cpx *X = nullptr, *P = nullptr;          // [N][Qcap][481]
+    float *Ex = nullptr, *Ep = nullptr, *Exp = nullptr, *ceps = nullptr, *gains = nullptr, *gsm = nullptr;   // [N][Qcap][22]
+    float *featB = nullptr;        // [N][Qcap][8]
+    float *feat = nullptr;         // [N][Qcap][42]
+    float *vad = nullptr;          // [N][Qcap]
+    int *sil = nullptr, *pidx = nullptr, *nzlist = nullptr;   // [N][Qcap]
+    long long *rank = nullptr;     // [N][Qcap]
+    PitchCand *cand = nullptr;     // [N][Qcap]
+    float *cepsc = nullptr;        // [N][8 + Qcap][22]
+    float *head = nullptr;         // [N][Qcap][480]
+    float *tail = nullptr;         // [N][1 + Qcap][480]
+    std::vector<void *> allocs;
+    size_t hp_stride() const { return kPHist + Qcap * kFrame; }
+};
+
+// ------------------------------------------------------------------------------------------
+// tables per device
+// ------------------------------------------------------------------------------------------
+static std::mutex g_rn_mu;
+static RnDevTables g_rn_tab[64];
+static bool g_rn_ready[64];
+
+template <class T> static int up(T **dst, const std::vector<T> &src) {
+    FVAD_CUDA_TRY(cudaMalloc((void **)dst, sizeof(T) * src.size()));
+    FVAD_CUDA_TRY(cudaMemcpy(*dst, src.data(), sizeof(T) * src.size(), cudaMemcpyHostToDevice));
+    return FVAD_OK;
+}
+
+static int rn_tables_get(int device, RnDevTables *out) {
+    std::lock_guard<std::mutex> lk(g_rn_mu);
+    if (!g_rn_ready[device]) {
+        HostTables h;
+        FVAD_TRY(host_tables_build(&h, nullptr));
+        RnDevTables d;
+        float *hw, *dct, *frac, *omf, *ts; cpx *tw; short *rev;
+        FVAD_TRY(up(&hw, h.half_window)); FVAD_TRY(up(&dct, h.dct)); FVAD_TRY(up(&frac, h.frac)); FVAD_TRY(up(&omf, h.omf));
+        FVAD_TRY(up(&ts, h.tansig)); FVAD_TRY(up(&tw, h.tw)); FVAD_TRY(up(&rev, h.rev));
+        FVAD_TRY(up(&d.weights, h.weights)); FVAD_TRY(up(&d.bias, h.bias));
+        d.t.half_window = hw; d.t.dct = dct; d.t.frac = frac; d.t.omf = omf; d.t.tansig = ts; d.t.tw = tw; d.t.rev = rev;
+        d.t.dct_scale = h.dct_scale;
+        g_rn_tab[device] = d;
+        g_rn_ready[device] = true;
+    }
+    *out = g_rn_tab[device];
+    return FVAD_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// kernels
+// ------------------------------------------------------------------------------------------
+// One warp per state; lane 0 walks the samples, the warp stages frames through shared memory so
+// that global traffic is coalesced and off the dependent chain.
+__global__ void __launch_bounds__(32) k_rn_biquad(const float *__restrict__ in, size_t in_stride, int C, int Q,
+                                                  RnPersist *persist, float *__restrict__ hp, size_t hp_stride, size_t N) {
+    const size_t n = blockIdx.x;
+    if (n >= N) return;
+    __shared__ float sx[2][kFrame];
+    __shared__ float sy[kFrame];
+    const int lane = threadIdx.x;
+    float m0 = persist[n].biq[0], m1 = persist[n].biq[1];
+    float *dst = hp + n * hp_stride + kPHist;
+    auto src = [&](int q) { return in + (n * C + (q % C)) * in_stride + (size_t)(q / C) * kFrame; };
+    if (Q > 0) for (int i = lane; i < kFrame; i += 32) sx[0][i] = src(0)[i];
+    __syncwarp();
+    for (int q = 0; q < Q; q++) {
+        const int cur = q & 1;
+        if (q + 1 < Q) { const float *s = src(q + 1); for (int i = lane; i < kFrame; i += 32) sx[cur ^ 1][i] = s[i]; }
+        if (lane == 0) {
+#pragma unroll 8
+            for (int i = 0; i < kFrame; i++) sy[i] = biquad_step(sx[cur][i], m0, m1);
+        }
+        __syncwarp();
+        for (int i = lane; i < kFrame; i += 32) dst[(size_t)q * kFrame + i] = sy[i];
+        __syncwarp();
+    }
+    if (lane == 0) { persist[n].biq[0] = m0; persist[n].biq[1] = m1; }
+}
+
+constexpr int kWarpsPerCta = 8;
+
+__global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_analysis(Tables t, const float *__restrict__ hp, size_t hp_stride,
+                                                                   size_t N, int Q, size_t Qcap, cpx *X, float *Ex,
+                                                                   float *ceps, int *sil) {
+    extern __shared__ float smem[];
+    const int w = threadIdx.x >> 5;
+    const size_t id = (size_t)blockIdx.x * kWarpsPerCta + w;
+    if (id >= N * (size_t)Q) return;
+    const size_t n = id / Q; const int q = (int)(id - n * Q);
+    const size_t f = n * Qcap + q;
+    analysis_warp(t, hp + n * hp_stride, q, X + f * kFreq, Ex + f * kNB, ceps + f * kNB, sil + f, smem + (size_t)w * kScrAna);
+}
+
+__global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_pitch(Tables t, const float *__restrict__ hp, size_t hp_stride, size_t N,
+                                                                int Q, size_t Qcap, PitchCand *cand) {
+    extern __shared__ float smem[];
+    const int w = threadIdx.x >> 5;
+    const size_t id = (size_t)blockIdx.x * kWarpsPerCta + w;
+    if (id >= N * (size_t)Q) return;
+    const size_t n = id / Q; const int q = (int)(id - n * Q);
+    pitch_warp(t, hp + n * hp_stride, q, cand + n * Qcap + q, smem + (size_t)w * kScrPitch);
+}
+
+__global__ void k_rn_pitch_seq(const PitchCand *__restrict__ cand, size_t N, int Q, size_t Qcap, RnPersist *persist, int *pidx) {
+    const size_t n = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    int lp = persist[n].last_period; float lg = persist[n].last_gain;
+    for (int q = 0; q < Q; q++) {
+        float g;
+        const int idx = pitch_decide(cand[n * Qcap + q], lp, lg, &g);
+        lp = idx; lg = g;                                     // denoise.c:334-335
+        pidx[n * Qcap + q] = idx;
+    }
+    persist[n].last_period = lp; persist[n].last_gain = lg;
+}
+
+__global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_pfeat(Tables t, const float *__restrict__ hp, size_t hp_stride, size_t N,
+                                                                int Q, size_t Qcap, const int *pidx, const cpx *X, const float *Ex,
+                                                                cpx *P, float *Ep, float *Exp, float *featB) {
+    extern __shared__ float smem[];
+    const int w = threadIdx.x >> 5;
+    const size_t id = (size_t)blockIdx.x * kWarpsPerCta + w;
+    if (id >= N * (size_t)Q) return;
+    const size_t n = id / Q; const int q = (int)(id - n * Q);
+    const size_t f = n * Qcap + q;
+    pfeat_warp(t, hp + n * hp_stride, q, pidx[f], X + f * kFreq, Ex + f * kNB, P + f * kFreq, Ep + f * kNB, Exp + f * kNB,
+               featB + f * 8, smem + (size_t)w * kScrAna);
+}
+
+// ranks of non-silent frames: the cepstral ring advances only on them (denoise.c:358-369)
+__global__ void k_rn_compact(const int *__restrict__ sil, size_t N, int Q, size_t Qcap, RnPersist *persist, long long *rank,
+                             int *nzlist) {
+    const size_t n = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const long long base = persist[n].nz_total;
+    int j = 0;
+    for (int q = 0; q < Q; q++) {
+        if (!sil[n * Qcap + q]) { rank[n * Qcap + q] = base + j; nzlist[n * Qcap + j] = q; j++; }
+        else rank[n * Qcap + q] = -1;
+    }
+    persist[n].nz_tile = j;
+}
+
+__global__ void k_rn_compact_copy(const float *__restrict__ ceps, const int *__restrict__ nzlist, const RnPersist *persist,
+                                  size_t N, int Q, size_t Qcap, float *cepsc) {
+    const size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;      // one thread per (state, j, coefficient)
+    const size_t per = (size_t)Q * kNB;
+    if (id >= N * per) return;
+    const size_t n = id / per; const size_t r = id - n * per;
+    const int j = (int)(r / kNB), k = (int)(r - (size_t)j * kNB);
+    if (j >= persist[n].nz_tile) return;
+    const int q = nzlist[n * Qcap + j];
+    cepsc[(n * (8 + Qcap) + 8 + j) * kNB + k] = ceps[(n * Qcap + q) * kNB + k];
+}
+
+__global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_cepsfeat(const float *__restrict__ cepsc, const int *__restrict__ nzlist,
+                                                                   const long long *__restrict__ rank, const RnPersist *persist,
+                                                                   const float *featB, size_t N, int Q, size_t Qcap, float *feat) {
+    __shared__ float smem[kWarpsPerCta * 80];
+    const int w = threadIdx.x >> 5;
+    const size_t id = (size_t)blockIdx.x * kWarpsPerCta + w;
+    if (id >= N * (size_t)Q) return;
+    const size_t n = id / Q; const int j = (int)(id - n * Q);
+    if (j >= persist[n].nz_tile) return;
+    const int q = nzlist[n * Qcap + j];
+    const size_t f = n * Qcap + q;
+    cepsfeat_warp(cepsc + (n * (8 + Qcap) + 8 + j) * kNB, rank[f], featB + f * 8, feat + f * kNFeat, smem + w * 80);
+}
+
+// One CTA per state walks its non-silent frames in order.  Weights (bf16, 174 KB) stay in shared memory.
+__global__ void __launch_bounds__(kRnnThreads) k_rn_rnn(const unsigned short *__restrict__ weights, const float *__restrict__ bias,
+                                                        const float *__restrict__ tansig, const float *__restrict__ feat,
+                                                        const int *__restrict__ nzlist, RnPersist *persist, size_t Qcap,
+                                                        float *gains, float *vad) {
+    extern __shared__ __align__(16) unsigned char smraw[];
+    unsigned short *W = reinterpret_cast<unsigned short *>(smraw);
+    float *b = reinterpret_cast<float *>(smraw + ((kRnnWeights * 2 + 15) & ~15));
+    float *ts = b + 560;
+    float *scr = ts + 208;
+    const size_t n = blockIdx.x;
+    for (int i = threadIdx.x; i < kRnnWeights / 2; i += kRnnThreads)
+        reinterpret_cast<unsigned *>(W)[i] = reinterpret_cast<const unsigned *>(weights)[i];
+    for (int i = threadIdx.x; i < kRnnBiases; i += kRnnThreads) b[i] = bias[i];
+    for (int i = threadIdx.x; i < 201; i += kRnnThreads) ts[i] = tansig[i];
+    for (int i = threadIdx.x; i < kRv_end; i += kRnnThreads) scr[i] = persist[n].rnn_vec[i];
+    __syncthreads();
+    const int nz = persist[n].nz_tile;
+    for (int j = 0; j < nz; j++) {
+        const int q = nzlist[n * Qcap + j];
+        const size_t f = n * Qcap + q;
+        if (threadIdx.x < kNFeat) scr[kRv_feat + threadIdx.x] = feat[f * kNFeat + threadIdx.x];
+        __syncthreads();
+        rnn_frame_cta(W, b, ts, scr, gains + f * kNB, vad + f);
+    }
+    for (int i = threadIdx.x; i < kRv_end; i += kRnnThreads) persist[n].rnn_vec[i] = scr[i];
+}
+
+// lastg floor (denoise.c:478-482): one thread per (state, band); also zeroes vad/gains bookkeeping of silent frames
+__global__ void k_rn_gain_scan(const float *__restrict__ gains, const int *__restrict__ sil, size_t N, int Q, size_t Qcap,
+                               RnPersist *persist, float *gsm, float *vad) {
+    const size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= N * kNB) return;
+    const size_t n = id / kNB; const int b = (int)(id - n * kNB);
+    float lastg = persist[n].lastg[b];
+    for (int q = 0; q < Q; q++) {
+        const size_t f = n * Qcap + q;
+        if (!sil[f]) {
+            const float a = .6f * lastg;
+            float g = gains[f * kNB + b];
+            g = g > a ? g : a;
+            lastg = g;
+            gsm[f * kNB + b] = g;
+        } else if (b == 0) vad[f] = 0.0f;                     // vad_prob stays 0 on silent frames (denoise.c:468)
+    }
+    persist[n].lastg[b] = lastg;
+}
+
+__global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_synth(Tables t, size_t N, int Q, size_t Qcap, const cpx *X, const cpx *P,
+                                                                const float *Ex, const float *Ep, const float *Exp,
+                                                                const float *gains, const float *gsm, const int *sil,
+                                                                float *head, float *tail) {
+    extern __shared__ float smem[];
+    const int w = threadIdx.x >> 5;
+    const size_t id = (size_t)blockIdx.x * kWarpsPerCta + w;
+    if (id >= N * (size_t)Q) return;
+    const size_t n = id / Q; const int q = (int)(id - n * Q);
+    const size_t f = n * Qcap + q;
+    synth_warp(t, X + f * kFreq, P + f * kFreq, Ex + f * kNB, Ep + f * kNB, Exp + f * kNB, gains + f * kNB, gsm + f * kNB, sil[f],
+               head + f * kFrame, tail + (n * (1 + Qcap) + 1 + q) * kFrame, smem + (size_t)w * kScrSyn);
+}
+
+// overlap-add with the previous frame's tail, back to normalised PCM, channel rows (denoise.c:405-407, Denoiser.zig:88-94)
+__global__ void k_rn_out(const float *__restrict__ head, const float *__restrict__ tail, size_t N, int C, int Q, size_t Qcap,
+                         float *out, size_t out_stride, size_t out_off) {
+    const size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t per = (size_t)Q * kFrame;
+    if (id >= N * per) return;
+    const size_t n = id / per; const size_t r = id - n * per;
+    const int q = (int)(r / kFrame), i = (int)(r - (size_t)q * kFrame);
+    float v = head[(n * Qcap + q) * kFrame + i] + tail[(n * (1 + Qcap) + q) * kFrame + i];
+    v *= (1.0f / 32767.0f);
+    const int tt = q / C, c = q % C;
+    out[(n * C + c) * out_stride + out_off + (size_t)tt * kFrame + i] = v;
+}
+
+// min over channels of the frame's VAD, start value 1 (VAD.zig:284-293)
+__global__ void k_rn_vadmin(const float *__restrict__ vad, size_t N, int C, int Tn, size_t Qcap, float *vad_min, float *vad_all,
+                            size_t vad_stride, size_t vad_off) {
+    const size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= N * (size_t)Tn) return;
+    const size_t n = id / Tn; const int tt = (int)(id - n * Tn);
+    float lo = 1.0f;
+    for (int c = 0; c < C; c++) {
+        const float v = vad[n * Qcap + (size_t)tt * C + c];
+        if (v < lo) lo = v;
+        if (vad_all) vad_all[(n * C + c) * vad_stride + vad_off + tt] = v;
+    }
+    if (vad_min) vad_min[n * vad_stride + vad_off + tt] = lo;
+}
+
+// carries to the next tile: pitch/analysis history of hp, the cepstral history, the synthesis tail
+__global__ void __launch_bounds__(256) k_rn_carry(float *hp, size_t hp_stride, float *cepsc, float *tail, RnPersist *persist,
+                                                  int Q, size_t Qcap) {
+    const size_t n = blockIdx.x;
+    __shared__ float tmp[kPHist];
+    float *h = hp + n * hp_stride;
+    for (int i = threadIdx.x; i < kPHist; i += blockDim.x) tmp[i] = h[(size_t)Q * kFrame + i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < kPHist; i += blockDim.x) h[i] = tmp[i];
+    __syncthreads();
+    const int nz = persist[n].nz_tile;
+    float *cc = cepsc + n * (8 + Qcap) * kNB;
+    for (int i = threadIdx.x; i < 8 * kNB; i += blockDim.x) tmp[i] = cc[(size_t)nz * kNB + i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < 8 * kNB; i += blockDim.x) cc[i] = tmp[i];
+    float *tl = tail + n * (1 + Qcap) * kFrame;
+    for (int i = threadIdx.x; i < kFrame; i += blockDim.x) tl[i] = tl[(size_t)Q * kFrame + i];
+    if (threadIdx.x == 0) { persist[n].nz_total += nz; persist[n].nz_tile = 0; }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+constexpr size_t kSmemAna = (size_t)kWarpsPerCta * kScrAna * sizeof(float);
+constexpr size_t kSmemPitch = (size_t)kWarpsPerCta * kScrPitch * sizeof(float);
+constexpr size_t kSmemSyn = (size_t)kWarpsPerCta * kScrSyn * sizeof(float);
+constexpr size_t kSmemRnn = ((kRnnWeights * 2 + 15) & ~15) + (560 + 208 + kRv_end) * sizeof(float);
+
+template <class T> static int rn_alloc(RnnoiseBatch *r, T **p, size_t n) {
+    void *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, n * sizeof(T) + 256);
+    if (e != cudaSuccess)
+        return set_error(e == cudaErrorMemoryAllocation ? FVAD_EOUT_OF_MEMORY : FVAD_ECUDA, "cudaMalloc(%zu): %s", n * sizeof(T),
+                         cudaGetErrorString(e));
+    r->allocs.push_back(q);
+    *p = (T *)q;
+    return FVAD_OK;
+}
+
+void rnnoise_batch_destroy(RnnoiseBatch *r) {
+    if (!r) return;
+    int prev = -1;
+    cudaGetDevice(&prev);
+    cudaSetDevice(r->device);
+    for (void *p : r->allocs) cudaFree(p);
+    if (prev >= 0) cudaSetDevice(prev);
+    delete r;
+}
+
+int rnnoise_batch_reset(RnnoiseBatch *r, cudaStream_t stream) {
+    FVAD_CUDA_TRY(cudaMemsetAsync(r->persist, 0, sizeof(RnPersist) * r->N, stream));
+    FVAD_CUDA_TRY(cudaMemsetAsync(r->hp, 0, sizeof(float) * r->N * r->hp_stride(), stream));
+    FVAD_CUDA_TRY(cudaMemsetAsync(r->cepsc, 0, sizeof(float) * r->N * (8 + r->Qcap) * kNB, stream));
+    FVAD_CUDA_TRY(cudaMemsetAsync(r->tail, 0, sizeof(float) * r->N * (1 + r->Qcap) * kFrame, stream));
+    return FVAD_OK;
+}
+
+int rnnoise_batch_create(size_t n_states, size_t max_frames, int device, RnnoiseBatch **out) {
+    *out = nullptr;
+    if (!n_states || !max_frames) return set_error(FVAD_EINVALID_ARGUMENT, "rnnoise_batch_create: zero size");
+    int prev = 0;
+    FVAD_CUDA_TRY(cudaGetDevice(&prev));
+    FVAD_CUDA_TRY(cudaSetDevice(device));
+    RnnoiseBatch *r = new (std::nothrow) RnnoiseBatch();
+    if (!r) return set_error(FVAD_EOUT_OF_MEMORY, "host allocation failed");
+    r->device = device; r->N = n_states; r->Qcap = max_frames;
+    int rc = rn_tables_get(device, &r->tab);
+    const size_t NQ = r->N * r->Qcap;
+#define RN_A(p, n) if (rc == FVAD_OK) rc = rn_alloc(r, &r->p, (n))
+    RN_A(persist, r->N);
+    RN_A(hp, r->N * r->hp_stride());
+    RN_A(X, NQ * kFreq); RN_A(P, NQ * kFreq);
+    RN_A(Ex, NQ * kNB); RN_A(Ep, NQ * kNB); RN_A(Exp, NQ * kNB); RN_A(ceps, NQ * kNB); RN_A(gains, NQ * kNB); RN_A(gsm, NQ * kNB);
+    RN_A(featB, NQ * 8); RN_A(feat, NQ * kNFeat); RN_A(vad, NQ);
+    RN_A(sil, NQ); RN_A(pidx, NQ); RN_A(nzlist, NQ); RN_A(rank, NQ); RN_A(cand, NQ);
+    RN_A(cepsc, r->N * (8 + r->Qcap) * kNB);
+    RN_A(head, NQ * kFrame); RN_A(tail, r->N * (1 + r->Qcap) * kFrame);
+#undef RN_A
+    if (rc == FVAD_OK) {
+        cudaError_t e = cudaFuncSetAttribute(k_rn_analysis, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemAna);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_pfeat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemAna);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_pitch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemPitch);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_synth, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemSyn);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemRnn);
+        if (e != cudaSuccess) rc = set_error(FVAD_ECUDA, "cudaFuncSetAttribute: %s (is this an sm_100 device?)", cudaGetErrorString(e));
+    }
+    if (rc == FVAD_OK) rc = rnnoise_batch_reset(r, 0);
+    if (rc == FVAD_OK && cudaDeviceSynchronize() != cudaSuccess) rc = set_error(FVAD_ECUDA, "sync failed: %s", cudaGetErrorString(cudaGetLastError()));
+    cudaSetDevice(prev);
+    if (rc != FVAD_OK) { rnnoise_batch_destroy(r); return rc; }
+    *out = r;
+    return FVAD_OK;
+}
+
+int rnnoise_batch_process(RnnoiseBatch *r, const float *d_in, size_t in_stride, int C, size_t Tn, float *d_out,
+                          size_t out_stride, size_t out_off, float *d_vad_min, float *d_vad_all, size_t vad_stride,
+                          size_t vad_off, cudaStream_t st) {
+    if (!r) return set_error(FVAD_ENOT_INITIALIZED, "denoiser not initialised");
+    const size_t Qs = Tn * (size_t)C;
+    if (Qs == 0) return FVAD_OK;
+    if (Qs > r->Qcap) return set_error(FVAD_EINVALID_ARGUMENT, "rnnoise_batch_process: %zu frames exceed capacity %zu", Qs, r->Qcap);
+    const int Q = (int)Qs;
+    const size_t N = r->N, Qcap = r->Qcap, NQ = N * Qs;
+    const Tables &t = r->tab.t;
+    const unsigned warp_grid = (unsigned)ceil_div(NQ, kWarpsPerCta);
+    FVAD_LAUNCH(k_rn_biquad, (unsigned)N, 32, 0, st, d_in, in_stride, C, Q, r->persist, r->hp, r->hp_stride(), N);
+    FVAD_LAUNCH(k_rn_analysis, warp_grid, 32 * kWarpsPerCta, kSmemAna, st, t, r->hp, r->hp_stride(), N, Q, Qcap, r->X, r->Ex, r->ceps, r->sil);
+    FVAD_LAUNCH(k_rn_pitch, warp_grid, 32 * kWarpsPerCta, kSmemPitch, st, t, r->hp, r->hp_stride(), N, Q, Qcap, r->cand);
+    FVAD_LAUNCH(k_rn_pitch_seq, (unsigned)ceil_div(N, 32), 32, 0, st, r->cand, N, Q, Qcap, r->persist, r->pidx);
+    FVAD_LAUNCH(k_rn_pfeat, warp_grid, 32 * kWarpsPerCta, kSmemAna, st, t, r->hp, r->hp_stride(), N, Q, Qcap, r->pidx, r->X, r->Ex, r->P,
+                r->Ep, r->Exp, r->featB);
+    FVAD_LAUNCH(k_rn_compact, (unsigned)ceil_div(N, 32), 32, 0, st, r->sil, N, Q, Qcap, r->persist, r->rank, r->nzlist);
+    FVAD_LAUNCH(k_rn_compact_copy, (unsigned)ceil_div(NQ * kNB, 256), 256, 0, st, r->ceps, r->nzlist, r->persist, N, Q, Qcap, r->cepsc);
+    FVAD_LAUNCH(k_rn_cepsfeat, warp_grid, 32 * kWarpsPerCta, 0, st, r->cepsc, r->nzlist, r->rank, r->persist, r->featB, N, Q, Qcap, r->feat);
+    FVAD_LAUNCH(k_rn_rnn, (unsigned)N, kRnnThreads, kSmemRnn, st, r->tab.weights, r->tab.bias, t.tansig, r->feat, r->nzlist, r->persist,
+                Qcap, r->gains, r->vad);
+    FVAD_LAUNCH(k_rn_gain_scan, (unsigned)ceil_div(N * kNB, 64), 64, 0, st, r->gains, r->sil, N, Q, Qcap, r->persist, r->gsm, r->vad);
+    FVAD_LAUNCH(k_rn_synth, warp_grid, 32 * kWarpsPerCta, kSmemSyn, st, t, N, Q, Qcap, r->X, r->P, r->Ex, r->Ep, r->Exp, r->gains, r->gsm,
+                r->sil, r->head, r->tail);
+    FVAD_LAUNCH(k_rn_out, (unsigned)ceil_div(NQ * kFrame, 256), 256, 0, st, r->head, r->tail, N, C, Q, Qcap, d_out, out_stride, out_off);
+    if (d_vad_min || d_vad_all)
+        FVAD_LAUNCH(k_rn_vadmin, (unsigned)ceil_div(N * Tn, 128), 128, 0, st, r->vad, N, C, (int)Tn, Qcap, d_vad_min, d_vad_all, vad_stride, vad_off);
+    FVAD_LAUNCH(k_rn_carry, (unsigned)N, 256, 0, st, r->hp, r->hp_stride(), r->cepsc, r->tail, r->persist, Q, Qcap);
+    FVAD_CUDA_TRY(cudaGetLastError());
+    return FVAD_OK;
+}
+
+}  // namespace fvad
+
+// ------------------------------------------------------------------------------------------
+// C ABI: Denoiser.zig drop-ins
+// ------------------------------------------------------------------------------------------
+using namespace fvad;
+
+struct fvad_denoiser_batch {
+    RnnoiseBatch *rn = nullptr;
+    size_t N = 0, Qcap = 0;
+    int device = 0;
+    float *d_in = nullptr, *d_out = nullptr, *d_vad = nullptr;
+};
+struct fvad_denoiser { fvad_denoiser_batch *b; float in[480]; };
+
+extern "C" size_t fvad_denoiser_frame_size(void) { return 480; }       // Denoiser.zig:68-70
+
+extern "C" void fvad_denoiser_batch_destroy(fvad_denoiser_batch *d) {
+    if (!d) return;
+    int prev = -1; cudaGetDevice(&prev); cudaSetDevice(d->device);
+    rnnoise_batch_destroy(d->rn);
+    cudaFree(d->d_in); cudaFree(d->d_out); cudaFree(d->d_vad);
+    if (prev >= 0) cudaSetDevice(prev);
+    delete d;
+}
+
+extern "C" int fvad_denoiser_batch_create(size_t n_streams, int device, fvad_denoiser_batch **out) {
+    if (!out || !n_streams) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_denoiser_batch_create: bad argument");
+    *out = nullptr;
+    if (device < 0) {
+        cudaError_t e = cudaGetDevice(&device);
+        if (e != cudaSuccess) return set_error(FVAD_ECUDA, "cudaGetDevice: %s (no CPU fallback exists)", cudaGetErrorString(e));
+    }
+    fvad_denoiser_batch *d = new (std::nothrow) fvad_denoiser_batch();
+    if (!d) return set_error(FVAD_EOUT_OF_MEMORY, "host allocation failed");
+    d->N = n_streams; d->device = device;
+    d->Qcap = std::max<size_t>(1, std::min<size_t>(4096, 65536 / n_streams));
+    int rc = rnnoise_batch_create(n_streams, d->Qcap, device, &d->rn);
+    int prev = 0; cudaGetDevice(&prev); cudaSetDevice(device);
+    if (rc == FVAD_OK && (cudaMalloc(&d->d_in, sizeof(float) * d->N * d->Qcap * 480) != cudaSuccess ||
+                          cudaMalloc(&d->d_out, sizeof(float) * d->N * d->Qcap * 480) != cudaSuccess ||
+                          cudaMalloc(&d->d_vad, sizeof(float) * d->N * d->Qcap) != cudaSuccess))
+        rc = set_error(FVAD_EOUT_OF_MEMORY, "device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+    cudaSetDevice(prev);
+    if (rc != FVAD_OK) { fvad_denoiser_batch_destroy(d); return rc; }
+    *out = d;
+    return FVAD_OK;
+}
+
+extern "C" int fvad_denoiser_batch_run(fvad_denoiser_batch *d, const float *const *pcm, size_t n_frames, float *const *out,
+                                       float *const *vad) {
+    if (!d || !pcm || !out) return set_error(FVAD_ENOT_INITIALIZED, "denoiser not initialised");
+    int prev = 0;
+    FVAD_CUDA_TRY(cudaGetDevice(&prev));
+    FVAD_CUDA_TRY(cudaSetDevice(d->device));
+    const size_t stride = d->Qcap * 480;
+    for (size_t f0 = 0; f0 < n_frames; f0 += d->Qcap) {
+        const size_t nf = std::min(d->Qcap, n_frames - f0);
+        for (size_t s = 0; s < d->N; s++)
+            FVAD_CUDA_TRY(cudaMemcpyAsync(d->d_in + s * stride, pcm[s] + f0 * 480, sizeof(float) * nf * 480, cudaMemcpyHostToDevice, 0));
+        FVAD_TRY(rnnoise_batch_process(d->rn, d->d_in, stride, 1, nf, d->d_out, stride, 0, d->d_vad, nullptr, d->Qcap, 0, 0));
+        for (size_t s = 0; s < d->N; s++) {
+            FVAD_CUDA_TRY(cudaMemcpyAsync(out[s] + f0 * 480, d->d_out + s * stride, sizeof(float) * nf * 480, cudaMemcpyDeviceToHost, 0));
+            if (vad) FVAD_CUDA_TRY(cudaMemcpyAsync(vad[s] + f0, d->d_vad + s * d->Qcap, sizeof(float) * nf, cudaMemcpyDeviceToHost, 0));
+        }
+        FVAD_CUDA_TRY(cudaStreamSynchronize(0));
+    }
+    FVAD_CUDA_TRY(cudaSetDevice(prev));
+    return FVAD_OK;
+}
+
+extern "C" int fvad_denoiser_create(fvad_denoiser **out) {              // Denoiser.init, Denoiser.zig:22-31
+    if (!out) return set_error(FVAD_EINVALID_ARGUMENT, "null out");
+    *out = nullptr;
+    fvad_denoiser_batch *b = nullptr;
+    FVAD_TRY(fvad_denoiser_batch_create(1, -1, &b));
+    fvad_denoiser *d = new (std::nothrow) fvad_denoiser();
+    if (!d) { fvad_denoiser_batch_destroy(b); return set_error(FVAD_EOUT_OF_MEMORY, "host allocation failed"); }
+    d->b = b;
+    *out = d;
+    return FVAD_OK;
+}
+extern "C" void fvad_denoiser_destroy(fvad_denoiser *d) {               // Denoiser.deinit, Denoiser.zig:33-39
+    if (!d) return;
+    fvad_denoiser_batch_destroy(d->b);
+    delete d;
+}
+extern "C" int fvad_denoiser_denoise(fvad_denoiser *d, const float *first, size_t n_first, const float *second, size_t n_second,
+                                     float *result, size_t n_result, float *vad) {   // Denoiser.denoise, Denoiser.zig:45-66
+    if (!d || !d->b) return set_error(FVAD_ENOT_INITIALIZED, "denoiser not initialised");
+    if (n_first + n_second != 480) return set_error(FVAD_EINVALID_FRAME_SIZE, "frame of %zu samples, expected 480", n_first + n_second);
+    if (n_result != 480) return set_error(FVAD_EINVALID_RESULT_SIZE, "result of %zu samples, expected 480", n_result);
+    if (n_first) memcpy(d->in, first, sizeof(float) * n_first);
+    if (n_second) memcpy(d->in + n_first, second, sizeof(float) * n_second);
+    const float *pin = d->in;
+    float v = 0;
+    float *pv = &v;
+    FVAD_TRY(fvad_denoiser_batch_run(d->b, &pin, 1, &result, &pv));
+    if (vad) *vad = v;
+    return FVAD_OK;
+}

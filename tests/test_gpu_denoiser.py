@@ -1,0 +1,80 @@
+"""GPU parity: batched RNNoise (Denoiser.zig / lib/rnnoise) and the full AudioPipeline path
+against the oracle: bit-exact denoised PCM, VAD probabilities, STFT records, segments, events."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import synth, assert_segments_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def test_denoiser_batch_bit_exact(fv, checker):
+    S, secs = 4, 8
+    pcm = np.stack([synth(fv, 20 + s, secs) for s in range(S)])
+    d = fv.DenoiserBatch(S)
+    out, vad = d.run(pcm)
+    # a second call continues from the carried state
+    pcm2 = np.stack([synth(fv, 20 + s, 2, first=secs * 48000) for s in range(S)])
+    out2, vad2 = d.run(pcm2)
+    silent = voiced = 0
+    for s in range(S):
+        wo, wv = checker.denoise_stream(np.concatenate([pcm[s], pcm2[s]]))
+        go, gv = np.concatenate([out[s], out2[s]]), np.concatenate([vad[s], vad2[s]])
+        assert np.array_equal(gv, wv), (s, np.abs(gv - wv).max(), np.nonzero(gv != wv)[0][:5])
+        assert np.array_equal(go, wo), (s, np.abs(go - wo).max())
+        silent += int((wv == 0).sum()); voiced += int((wv > 0.5).sum())
+    assert silent > 0 and voiced > 0, "input must exercise silent and voiced frames"
+
+
+def test_denoiser_single_frame_api(fv, checker):
+    x = synth(fv, 33, 1.0)
+    d = fv.Denoiser()
+    assert d.get_frame_size() == 480
+    want_o, want_v = checker.denoise_stream(x[:480 * 20])
+    for q in range(20):
+        fr = x[q * 480:(q + 1) * 480]
+        o, v = d.denoise(fr[:100], second=fr[100:])       # SplitSlice
+        assert v == want_v[q] and np.array_equal(o, want_o[q * 480:(q + 1) * 480])
+    with pytest.raises(fv.FvadError) as e:
+        d.denoise(np.zeros(479, np.float32))
+    assert e.value.name == "InvalidFrameSize"
+    with pytest.raises(fv.FvadError) as e:
+        d.denoise(np.zeros(480, np.float32), result_len=100)
+    assert e.value.name == "InvalidResultSize"
+
+
+@pytest.mark.parametrize("n_channels,tile", [(1, None), (1, 37), (2, 53)])
+def test_full_pipeline_bit_exact(fv, checker, n_channels, tile, monkeypatch):
+    if tile:
+        monkeypatch.setenv("FVAD_TILE_FRAMES", str(tile))
+    S, secs = 3, 50
+    pcm = np.stack([np.stack([synth(fv, 200 + 5 * s + c, secs) * np.float32(1.0 if c == 0 else 0.7)
+                              for c in range(n_channels)]) for s in range(S)])
+    alt = fv.default_machine_config(speech_threshold_factor=9.0, min_vad_duration_sec=0.3, max_speech_gap_sec=1.0)
+    flags = fv.TRACE_RECORDS | fv.TRACE_DENOISED | fv.TRACE_RNN_VAD
+    with fv.PipelineBatch(S, n_channels=n_channels, alt_vad_machine_configs=[alt], trace=flags) as b:
+        off = 0
+        for n in (48000, 1, 479, 481, 2048 * 3 + 5):
+            b.push_samples(pcm[:, :, off:off + n]); off += n
+        b.push_samples(pcm[:, :, off:])
+        oalt = checker.default_config(speech_threshold_factor=9.0, min_vad_duration_sec=0.3, max_speech_gap_sec=1.0)
+        total = 0
+        for s in range(S):
+            want = checker.run_pipeline(list(pcm[s]), alt_cfgs=[oalt], trace=True)
+            assert np.array_equal(b.trace_rnn_vad(s), want["rnn_vad"])
+            for c in range(n_channels):
+                got = b.trace_denoised(s, c)
+                assert np.array_equal(got, want["denoised"][c]), np.abs(got - want["denoised"][c]).max()
+            rec = b.trace_records(s)
+            for k in ("index", "min_volume", "vol_ratio", "rnn_vad"):
+                assert np.array_equal(rec[k], want["records"][k]), k
+            for k in range(2):
+                assert_segments_equal(b.segments(s, k), want["segments"][k])
+                gs, ws = b.segments(s, k), want["segments"][k]
+                assert np.array_equal(gs["rnn_vad"], ws["rnn_vad"]) and np.array_equal(gs["vol_ratio"], ws["vol_ratio"])
+                total += len(ws)
+            ev = b.events(s)
+            assert [(int(e["at_index"]), int(e["recording_state"]), int(e["sample_number"])) for e in ev] == want["events"]
+        assert total > 0, "test input produced no segments"
