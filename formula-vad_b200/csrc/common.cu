@@ -3,6 +3,10 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
 
 namespace fvad {
 
@@ -15,6 +19,24 @@ int set_error(int code, const char *fmt, ...) {
     vsnprintf(t_err, sizeof t_err, fmt, ap);
     va_end(ap);
     return code;
+}
+
+std::atomic<int> g_profile_on{0};
+namespace {
+struct ProfRec { std::string name; cudaEvent_t a, b; };
+std::mutex g_prof_mu;
+std::vector<ProfRec> g_prof;
+}
+void profile_begin(const char *name, cudaStream_t stream) {
+    ProfRec r; r.name = name;
+    if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess) return;
+    cudaEventRecord(r.a, stream);
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    g_prof.push_back(r);
+}
+void profile_end(cudaStream_t stream) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (!g_prof.empty()) cudaEventRecord(g_prof.back().b, stream);
 }
 
 int device_sm_count(int device) {
@@ -64,6 +86,34 @@ int fvad_device_count(void) {
 }
 
 uint64_t fvad_launch_count(void) { return fvad::g_launch_count.load(); }
+
+void fvad_profile_enable(int on) { fvad::g_profile_on.store(on ? 1 : 0); }
+
+// JSON: {"kernel": {"launches": n, "total_ms": t}, ...} for everything recorded since the last report.
+int fvad_profile_report(char *buf, size_t cap) {
+    using namespace fvad;
+    cudaDeviceSynchronize();
+    std::map<std::string, std::pair<long, double>> agg;
+    {
+        std::lock_guard<std::mutex> lk(g_prof_mu);
+        for (auto &r : g_prof) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) { agg[r.name].first++; agg[r.name].second += ms; }
+            cudaEventDestroy(r.a); cudaEventDestroy(r.b);
+        }
+        g_prof.clear();
+    }
+    std::string out = "{";
+    bool first = true;
+    for (auto &kv : agg) {
+        char tmp[256];
+        snprintf(tmp, sizeof tmp, "%s\"%s\": {\"launches\": %ld, \"total_ms\": %.6f}", first ? "" : ", ", kv.first.c_str(), kv.second.first, kv.second.second);
+        out += tmp; first = false;
+    }
+    out += "}";
+    if (buf && cap) { snprintf(buf, cap, "%s", out.c_str()); }
+    return (int)out.size();
+}
 
 void fvad_default_vad_machine_config(fvad_vad_machine_config *c) {   // VADMachine.zig:18-39
     memset(c, 0, sizeof *c);

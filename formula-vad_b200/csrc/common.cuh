@@ -28,10 +28,19 @@ extern std::atomic<uint64_t> g_launch_count;
         if (rc__ != FVAD_OK) return rc__; \
     } while (0)
 
+// Optional per-kernel timing (fvad_profile_enable): CUDA events recorded on the launching stream
+// around every launch, aggregated by kernel name in fvad_profile_report.
+extern std::atomic<int> g_profile_on;
+void profile_begin(const char *name, cudaStream_t stream);
+void profile_end(cudaStream_t stream);
+
 // Every kernel launch of the library goes through this so that fvad_launch_count() is honest.
 #define FVAD_LAUNCH(kernel, grid, block, smem, stream, ...)                 \
     do {                                                                    \
+        const bool prof__ = ::fvad::g_profile_on.load(std::memory_order_relaxed) != 0; \
+        if (prof__) ::fvad::profile_begin(#kernel, (stream));               \
         kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);         \
+        if (prof__) ::fvad::profile_end((stream));                          \
         ::fvad::g_launch_count.fetch_add(1, std::memory_order_relaxed);     \
     } while (0)
 

@@ -69,6 +69,7 @@ def lib():
     sig = {
         "fvad_last_error": (C.c_char_p, []), "fvad_status_name": (C.c_char_p, [C.c_int]),
         "fvad_version": (C.c_char_p, []), "fvad_device_count": (C.c_int, []), "fvad_launch_count": (C.c_uint64, []),
+        "fvad_profile_enable": (None, [C.c_int]), "fvad_profile_report": (C.c_int, [C.c_char_p, sz]),
         "fvad_default_vad_machine_config": (None, [C.POINTER(VadMachineConfig)]),
         "fvad_default_config": (None, [C.POINTER(Config), sz, sz]),
         "fvad_batch_create": (C.c_int, [C.POINTER(Config), sz, C.c_int, C.POINTER(vp)]),
@@ -138,6 +139,18 @@ def default_machine_config(**kw):
 
 def launch_count():
     return int(lib().fvad_launch_count())
+
+
+def profile_enable(on=True):
+    lib().fvad_profile_enable(int(on))
+
+
+def profile_report():
+    import json
+    n = lib().fvad_profile_report(None, 0)
+    buf = C.create_string_buffer(n + 16)
+    lib().fvad_profile_report(buf, n + 16)   # second call reports nothing new: keep the first result
+    return json.loads(buf.value.decode() or "{}")
 
 
 class PipelineBatch:

@@ -54,6 +54,11 @@ const char *fvad_version(void);
 int fvad_device_count(void);
 /* Kernels launched by this library in this process so far (all handles, all threads). */
 uint64_t fvad_launch_count(void);
+/* Per-kernel timing for bench.py: when enabled, every launch is bracketed by CUDA events on its own
+ * stream; fvad_profile_report writes {"kernel": {"launches": n, "total_ms": t}, ...} (JSON) for
+ * everything recorded since the previous report and returns the length needed. */
+void fvad_profile_enable(int on);
+int  fvad_profile_report(char *buf, size_t cap);
 
 /* ---- configuration PODs ---------------------------------------------------------- */
 /* VADMachine.Config, src/AudioPipeline/VADMachine.zig:18-39 (same fields, same defaults
