@@ -492,6 +492,8 @@ extern "C" int fvad_batch_counts(fvad_batch *b, uint64_t *total_write_count, uin
     return FVAD_OK;
 }
 
+extern "C" void *fvad_batch_cuda_stream(fvad_batch *b) { return b ? (void *)b->stream : nullptr; }
+
 extern "C" int fvad_batch_set_trace(fvad_batch *b, unsigned flags) {
     if (!b) return set_error(FVAD_EINVALID_ARGUMENT, "null batch");
     if (b->total_write_count) return set_error(FVAD_EINVALID_ARGUMENT, "set the trace flags before the first push");

@@ -99,9 +99,9 @@ int fvad_profile_report(char *buf, size_t cap) {
         for (auto &r : g_prof) {
             float ms = 0;
             if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) { agg[r.name].first++; agg[r.name].second += ms; }
-            cudaEventDestroy(r.a); cudaEventDestroy(r.b);
+            if (buf && cap) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         }
-        g_prof.clear();
+        if (buf && cap) g_prof.clear();      // a size query (buf == NULL) leaves the records in place
     }
     std::string out = "{";
     bool first = true;

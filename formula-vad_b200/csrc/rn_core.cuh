@@ -832,8 +832,12 @@ RN_HD float biquad_step(float in_norm, float &m0, float &m1) {
     const float a0 = -1.99599f, a1 = 0.99600f, b0 = -2.f, b1 = 1.f;     // denoise.c:470-471
     const float xi = in_norm * 32767.0f;
     const float yi = xi + m0;
-    m0 = (float)(m1 + (b0 * (double)xi - a0 * (double)yi));
-    m1 = (float)(b1 * (double)xi - a1 * (double)yi);
+    // a0*yi and a1*yi are products of two floats: exact in double, so DMUL+DADD == one DFMA bit for bit
+    // (b0*xi = -2*xi and b1*xi = xi are exact as well).  Shortens the dependent chain by one DADD.
+    const double xd = (double)xi, yd = (double)yi;
+    (void)b0; (void)b1;
+    m0 = (float)((double)m1 + fma(-(double)a0, yd, -2.0 * xd));
+    m1 = (float)fma(-(double)a1, yd, xd);
     return yi;
 }
 

@@ -80,6 +80,7 @@ def lib():
         "fvad_batch_segments": (C.c_int, [vp, sz, C.c_int, C.POINTER(vp), szp]),
         "fvad_batch_events": (C.c_int, [vp, sz, C.POINTER(vp), szp]),
         "fvad_batch_counts": (C.c_int, [vp, u64p, u64p]),
+        "fvad_batch_cuda_stream": (vp, [vp]),
         "fvad_batch_set_trace": (C.c_int, [vp, C.c_uint]),
         "fvad_batch_trace_records": (C.c_int, [vp, sz, vp, sz, szp]),
         "fvad_batch_trace_denoised": (C.c_int, [vp, sz, sz, _fp, sz, szp]),
@@ -149,7 +150,7 @@ def profile_report():
     import json
     n = lib().fvad_profile_report(None, 0)
     buf = C.create_string_buffer(n + 16)
-    lib().fvad_profile_report(buf, n + 16)   # second call reports nothing new: keep the first result
+    lib().fvad_profile_report(buf, n + 16)   # the size query above leaves the records in place
     return json.loads(buf.value.decode() or "{}")
 
 
@@ -227,6 +228,10 @@ class PipelineBatch:
 
     def sync(self):
         _check(lib().fvad_batch_sync(self._h))
+
+    def cuda_stream(self):
+        """Address of the batch's main cudaStream_t (for torch.cuda.ExternalStream / event timing)."""
+        return int(lib().fvad_batch_cuda_stream(self._h) or 0)
 
     def reset(self):
         _check(lib().fvad_batch_reset(self._h))

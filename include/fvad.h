@@ -159,6 +159,9 @@ int  fvad_batch_events(fvad_batch *b, size_t stream, const fvad_capture_event **
 /* Total samples written / consumed by the VAD so far (multi_ring_buffer.total_write_count,
  * VAD.pipeline_read_count). */
 int  fvad_batch_counts(fvad_batch *b, uint64_t *total_write_count, uint64_t *pipeline_read_count);
+/* The batch's main CUDA stream (a cudaStream_t): everything a push submits is ordered before work later
+ * enqueued on it, so callers can bracket pushes with their own CUDA events (bench.py does). */
+void *fvad_batch_cuda_stream(fvad_batch *b);
 
 /* Optional traces for parity tests and for the config-5 sweep ("shared features").
  * Bits: 1 = per-STFT-frame records, 2 = denoised PCM, 4 = per-480-frame RNNoise VAD,

@@ -1,5 +1,6 @@
-"""Quick timing probe (not the bench): S streams x secs through the full pipeline, device-resident input."""
-import sys, os, time
+"""Quick timing probe (not the bench): S streams x secs through the full pipeline, device-resident input.
+usage: perf_probe.py [S=20] [secs=120] [reps=2] [use_denoiser=1] [profile=0]"""
+import sys, os, time, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "formula-vad_b200"))
 import torch, fvad
@@ -7,6 +8,7 @@ S = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 secs = int(sys.argv[2]) if len(sys.argv) > 2 else 120
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
 use_dn = int(sys.argv[4]) if len(sys.argv) > 4 else 1
+prof = int(sys.argv[5]) if len(sys.argv) > 5 else 0
 n = secs * 48000
 x = torch.empty(S, n, dtype=torch.float32, device="cuda")
 fvad.synth_device(x.data_ptr(), n, 0xF1AD5EED00000000, 0, S, 0, n)
@@ -14,9 +16,16 @@ torch.cuda.synchronize()
 b = fvad.PipelineBatch(S, use_denoiser=bool(use_dn))
 for r in range(reps):
     b.reset()
+    if prof and r == reps - 1:
+        fvad.profile_enable(True)
     t0 = time.time()
     b.push_device(x.data_ptr(), n, n, n)
     b.sync()
     dt = time.time() - t0
     nseg = sum(len(b.segments(s)) for s in range(S))
-    print(f"rep {r}: {dt*1e3:.1f} ms  -> {S*secs/dt:.0f} x real-time, segments {nseg}", flush=True)
+    print(f"S={S} secs={secs} dn={use_dn} rep {r}: {dt*1e3:.1f} ms  -> {S*secs/dt:.0f} x real-time, segments {nseg}", flush=True)
+if prof:
+    rep = fvad.profile_report()
+    tot = sum(v["total_ms"] for v in rep.values())
+    for k, v in sorted(rep.items(), key=lambda kv: -kv[1]["total_ms"]):
+        print(f"  {k:24s} {v['launches']:6d} launches {v['total_ms']:10.2f} ms {100*v['total_ms']/tot:5.1f}%")
