@@ -21,7 +21,14 @@ struct fvad_batch {
     std::vector<fvad_vad_machine_config> machine_cfgs;   // [0] main, [1..] alt
     size_t S = 0, C = 0, rows = 0;
     int device = 0;
-    cudaStream_t stream = nullptr;
+    // Four stage streams (wavefront over tiles): sA biquad, sB analysis/pitch/features, sC RNN, stream (= stage D)
+    // synthesis + STFT + VADMachine.  `stream` is the batch's main stream: results become visible in its order.
+    cudaStream_t stream = nullptr, sA = nullptr, sB = nullptr, sC = nullptr;
+    static constexpr int kMaxSlots = 8;
+    int n_slots = 1;
+    cudaEvent_t evA[kMaxSlots] = {}, evB[kMaxSlots] = {}, evC[kMaxSlots] = {}, evD[kMaxSlots] = {};
+    unsigned long long tile_no = 0;
+    float *d_ratio_slot[kMaxSlots] = {};   // [S][tile_frames] channel-volume ratio per 480-frame, stage A -> D
     bool use_denoiser = true;
     int fft_size = 2048, frame_len = 480;
     unsigned trace_flags = 0;
@@ -122,14 +129,18 @@ extern "C" void fvad_batch_destroy(fvad_batch *b) {
     if (!b) return;
     {
         DeviceGuard g(b->device);
-        if (b->stream) cudaStreamSynchronize(b->stream);
+        for (cudaStream_t st : {b->sA, b->sB, b->sC, b->stream}) if (st) cudaStreamSynchronize(st);
         if (b->rn) rnnoise_batch_destroy(b->rn);
+        for (int i = 0; i < fvad_batch::kMaxSlots; i++) {
+            cudaFree(b->d_ratio_slot[i]);
+            for (cudaEvent_t e : {b->evA[i], b->evB[i], b->evC[i], b->evD[i]}) if (e) cudaEventDestroy(e);
+        }
         cudaFree(b->d_work); cudaFree(b->d_carry); cudaFree(b->d_den); cudaFree(b->d_den_carry);
         cudaFree(b->d_ratio480); cudaFree(b->d_vad480); cudaFree(b->d_band); cudaFree(b->d_ratio_stft);
         cudaFree(b->d_vad_stft); cudaFree(b->d_spectra); cudaFree(b->d_params); cudaFree(b->d_states);
         cudaFree(b->d_rings); cudaFree(b->d_segs); cudaFree(b->d_seg_count); cudaFree(b->d_events);
         cudaFree(b->d_event_count); cudaFree(b->d_trace);
-        if (b->stream) cudaStreamDestroy(b->stream);
+        for (cudaStream_t st : {b->sA, b->sB, b->sC, b->stream}) if (st) cudaStreamDestroy(st);
     }
     delete b;
 }
@@ -168,8 +179,20 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
 
     int rc = FVAD_OK;
     auto fail = [&](int code) { fvad_batch_destroy(b); return code; };
-    if (cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess)
+    if (cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&b->sA, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&b->sB, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&b->sC, cudaStreamNonBlocking) != cudaSuccess)
         return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
+    {
+        const char *es = getenv("FVAD_SLOTS");
+        int ns = es ? atoi(es) : 3;
+        b->n_slots = ns < 1 ? 1 : ns > fvad_batch::kMaxSlots ? fvad_batch::kMaxSlots : ns;
+        for (int i = 0; i < b->n_slots; i++)
+            for (cudaEvent_t *e : {&b->evA[i], &b->evB[i], &b->evC[i], &b->evD[i]})
+                if (cudaEventCreateWithFlags(e, cudaEventDisableTiming) != cudaSuccess)
+                    return fail(set_error(FVAD_ECUDA, "cudaEventCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
+    }
     if ((rc = stft_tables_get(device, &b->tabs)) != FVAD_OK) return fail(rc);
 
     // machines: params, distinct bands (PipelineFFT.averageVolumeInBand per machine config)
@@ -224,7 +247,9 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
         if ((rc = dmalloc(&b->d_den_carry, b->rows * (size_t)b->fft_size)) != FVAD_OK) return fail(rc);
         if ((rc = dmalloc(&b->d_ratio480, b->S * b->stride480)) != FVAD_OK) return fail(rc);
         if ((rc = dmalloc(&b->d_vad480, b->S * b->stride480)) != FVAD_OK) return fail(rc);
-        if ((rc = rnnoise_batch_create(b->S, tf * b->C, device, &b->rn)) != FVAD_OK) return fail(rc);
+        if ((rc = rnnoise_batch_create(b->S, tf * b->C, b->n_slots, device, &b->rn)) != FVAD_OK) return fail(rc);
+        for (int i = 0; i < b->n_slots; i++)
+            if ((rc = dmalloc(&b->d_ratio_slot[i], b->S * tf)) != FVAD_OK) return fail(rc);
         b->max_stft = (tf * kRnFrame + b->fft_size) / b->fft_size + 1;
     } else {
         b->max_stft = tf;
@@ -313,38 +338,59 @@ static int process_tile(fvad_batch *b, size_t m) {
     const size_t avail = b->carry_len + m;
     const size_t F = avail / b->frame_len, used = F * b->frame_len;
     size_t J = 0, den_before = b->den_carry;
+    cudaStream_t sA = b->use_denoiser ? b->sA : b->stream, sD = b->stream;   // the input side lives on sA
     if (F > 0 && !b->cfg.skip_processing) {                                   // AudioPipeline.zig:153-157
         float *spec = (b->trace_flags & FVAD_TRACE_SPECTRA) ? b->d_spectra : nullptr;
         if (!b->use_denoiser) {
             J = F;
-            FVAD_TRY(rms_ratio_launch(b->d_work, b->work_cap, b->S, (int)b->C, F, b->fft_size, b->d_ratio_stft, b->max_stft, 0, b->stream));
+            FVAD_TRY(rms_ratio_launch(b->d_work, b->work_cap, b->S, (int)b->C, F, b->fft_size, b->d_ratio_stft, b->max_stft, 0, sD));
             FVAD_TRY(stft_launch(*b->tabs, b->d_work, b->rows, b->work_cap, F, b->fft_size, b->bands, b->d_band, b->max_stft, 0,
-                                 spec, nullptr, 0.f, b->device, b->stream));
+                                 spec, nullptr, 0.f, b->device, sD));
             FVAD_TRY(run_machines(b, nullptr, b->read_count, J));
         } else {
-            FVAD_TRY(rms_ratio_launch(b->d_work, b->work_cap, b->S, (int)b->C, F, kRnFrame, b->d_ratio480, b->stride480,
-                                      fvad_batch::kHist480, b->stream));
-            FVAD_TRY(rnnoise_batch_process(b->rn, b->d_work, b->work_cap, (int)b->C, F, b->d_den, b->den_cap, b->den_carry,
-                                           b->d_vad480, nullptr, b->stride480, fvad_batch::kHist480, b->stream));
+            // ---- wavefront: stage X of this tile follows stage X of the previous tile (stream order) and
+            // stage X-1 of this tile (event); a slot is reused only after its previous tile left stage D.
+            const int slot = (int)(b->tile_no % (unsigned)b->n_slots);
+            b->tile_no++;
+            // stage A (sA): channel RMS ratio + biquad; the tile's PCM is already in d_work (same stream)
+            FVAD_CUDA_TRY(cudaStreamWaitEvent(sA, b->evD[slot], 0));
+            FVAD_TRY(rms_ratio_launch(b->d_work, b->work_cap, b->S, (int)b->C, F, kRnFrame, b->d_ratio_slot[slot], b->tile_frames, 0, sA));
+            FVAD_TRY(rnnoise_stage_a(b->rn, slot, b->d_work, b->work_cap, (int)b->C, F, sA));
+            FVAD_CUDA_TRY(cudaEventRecord(b->evA[slot], sA));
+            // stage B (sB)
+            FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sB, b->evA[slot], 0));
+            FVAD_TRY(rnnoise_stage_b(b->rn, slot, F * b->C, b->sB));
+            FVAD_CUDA_TRY(cudaEventRecord(b->evB[slot], b->sB));
+            // stage C (sC)
+            FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sC, b->evB[slot], 0));
+            FVAD_TRY(rnnoise_stage_c(b->rn, slot, F * b->C, b->sC));
+            FVAD_CUDA_TRY(cudaEventRecord(b->evC[slot], b->sC));
+            // stage D (main stream)
+            FVAD_CUDA_TRY(cudaStreamWaitEvent(sD, b->evC[slot], 0));
+            FVAD_TRY(copy_rows_launch(b->d_ratio480, b->stride480, fvad_batch::kHist480, b->d_ratio_slot[slot], b->tile_frames, 0,
+                                      b->S, F, sD));
+            FVAD_TRY(rnnoise_stage_d(b->rn, slot, (int)b->C, F, b->d_den, b->den_cap, b->den_carry, b->d_vad480, nullptr,
+                                     b->stride480, fvad_batch::kHist480, sD));
             const size_t den_avail = b->den_carry + F * kRnFrame;
             J = den_avail / b->fft_size;
             if (J > 0) {
                 FVAD_TRY(reframe_launch(b->d_ratio480, b->d_vad480, b->stride480, b->base480, fvad_batch::kHist480, b->S,
-                                        b->stft_done, J, b->fft_size, b->d_ratio_stft, b->d_vad_stft, b->max_stft, b->stream));
+                                        b->stft_done, J, b->fft_size, b->d_ratio_stft, b->d_vad_stft, b->max_stft, sD));
                 FVAD_TRY(stft_launch(*b->tabs, b->d_den, b->rows, b->den_cap, J, b->fft_size, b->bands, b->d_band, b->max_stft, 0,
-                                     spec, nullptr, 0.f, b->device, b->stream));
+                                     spec, nullptr, 0.f, b->device, sD));
                 FVAD_TRY(run_machines(b, b->d_vad_stft, b->stft_done * (unsigned long long)b->fft_size, J));
             }
             if (b->trace_flags) FVAD_TRY(trace_tile(b, F, J, den_before));
             const size_t tail = den_avail - J * b->fft_size;
             if (J > 0 && tail > 0) {
-                FVAD_TRY(copy_rows_launch(b->d_den_carry, b->fft_size, 0, b->d_den, b->den_cap, J * b->fft_size, b->rows, tail, b->stream));
-                FVAD_TRY(copy_rows_launch(b->d_den, b->den_cap, 0, b->d_den_carry, b->fft_size, 0, b->rows, tail, b->stream));
+                FVAD_TRY(copy_rows_launch(b->d_den_carry, b->fft_size, 0, b->d_den, b->den_cap, J * b->fft_size, b->rows, tail, sD));
+                FVAD_TRY(copy_rows_launch(b->d_den, b->den_cap, 0, b->d_den_carry, b->fft_size, 0, b->rows, tail, sD));
             }
             b->den_carry = tail;
-            FVAD_TRY(shift_hist_launch(b->d_ratio480, b->stride480, fvad_batch::kHist480, F, b->S, b->stream));
-            FVAD_TRY(shift_hist_launch(b->d_vad480, b->stride480, fvad_batch::kHist480, F, b->S, b->stream));
+            FVAD_TRY(shift_hist_launch(b->d_ratio480, b->stride480, fvad_batch::kHist480, F, b->S, sD));
+            FVAD_TRY(shift_hist_launch(b->d_vad480, b->stride480, fvad_batch::kHist480, F, b->S, sD));
             b->base480 += (long long)F;
+            FVAD_CUDA_TRY(cudaEventRecord(b->evD[slot], sD));
         }
         if (!b->use_denoiser && b->trace_flags) FVAD_TRY(trace_tile(b, F, J, 0));
         b->stft_done += J;
@@ -354,8 +400,8 @@ static int process_tile(fvad_batch *b, size_t m) {
     const size_t consumed = b->cfg.skip_processing ? avail : used;   // skip_processing: samples are only buffered by the reference
     const size_t tail = avail - consumed;
     if (consumed > 0 && tail > 0) {
-        FVAD_TRY(copy_rows_launch(b->d_carry, b->frame_len, 0, b->d_work, b->work_cap, consumed, b->rows, tail, b->stream));
-        FVAD_TRY(copy_rows_launch(b->d_work, b->work_cap, 0, b->d_carry, b->frame_len, 0, b->rows, tail, b->stream));
+        FVAD_TRY(copy_rows_launch(b->d_carry, b->frame_len, 0, b->d_work, b->work_cap, consumed, b->rows, tail, sA));
+        FVAD_TRY(copy_rows_launch(b->d_work, b->work_cap, 0, b->d_carry, b->frame_len, 0, b->rows, tail, sA));
     }
     b->carry_len = tail;
     return FVAD_OK;
@@ -378,13 +424,14 @@ extern "C" int fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n,
         const size_t m = std::min(m_max, n - off);
         for (size_t r = 0; r < b->rows; r++)
             FVAD_CUDA_TRY(cudaMemcpyAsync(b->d_work + r * b->work_cap + b->carry_len, pcm[r] + off, sizeof(float) * m,
-                                          cudaMemcpyHostToDevice, b->stream));
+                                          cudaMemcpyHostToDevice, b->use_denoiser ? b->sA : b->stream));
         FVAD_TRY(process_tile(b, m));
         off += m;
     }
     b->total_write_count += n;
-    // input is borrowed only until return (AudioPipeline.pushSamples copies into its ring)
-    FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    // input is borrowed only until return (AudioPipeline.pushSamples copies into its ring): wait for the
+    // input-side stream only; the later stages keep running behind the caller's back until fvad_batch_sync
+    FVAD_CUDA_TRY(cudaStreamSynchronize(b->use_denoiser ? b->sA : b->stream));
     return FVAD_OK;
 }
 
@@ -399,7 +446,7 @@ extern "C" int fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t 
     for (size_t off = 0; off < n;) {
         const size_t m = std::min(m_max, n - off);
         FVAD_TRY(gather_rows_launch(b->d_work, b->work_cap, b->carry_len, d_pcm, stream_stride, channel_stride, off, b->S,
-                                    (int)b->C, m, b->stream));
+                                    (int)b->C, m, b->use_denoiser ? b->sA : b->stream));
         FVAD_TRY(process_tile(b, m));
         off += m;
     }
@@ -449,14 +496,14 @@ extern "C" int fvad_batch_sync(fvad_batch *b) {
 extern "C" int fvad_batch_reset(fvad_batch *b) {
     if (!b) return set_error(FVAD_EINVALID_ARGUMENT, "null batch");
     DeviceGuard g(b->device);
-    FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    for (cudaStream_t st : {b->sA, b->sB, b->sC, b->stream}) FVAD_CUDA_TRY(cudaStreamSynchronize(st));
     FVAD_TRY(upload_machine_state(b));
     if (b->use_denoiser) {
         FVAD_TRY(rnnoise_batch_reset(b->rn, b->stream));
         FVAD_CUDA_TRY(cudaMemsetAsync(b->d_ratio480, 0, sizeof(float) * b->S * b->stride480, b->stream));
         FVAD_CUDA_TRY(cudaMemsetAsync(b->d_vad480, 0, sizeof(float) * b->S * b->stride480, b->stream));
     }
-    b->carry_len = 0; b->den_carry = 0; b->base480 = 0;
+    b->carry_len = 0; b->den_carry = 0; b->base480 = 0; b->tile_no = 0;
     b->total_write_count = b->read_count = b->stft_done = 0;
     for (auto &v : b->segs) v.clear();
     for (auto &v : b->events) v.clear();

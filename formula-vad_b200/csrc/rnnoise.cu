@@ -26,8 +26,6 @@ struct RnPersist {                 // per state, lives across tiles (DenoiseStat
     int last_period;
     float last_gain;
     long long nz_total;            // non-silent frames so far: cepstral ring position = nz_total & 7
-    int nz_tile;                   // non-silent frames of the current tile
-    int _pad;
     float lastg[kNB];
     float rnn_vec[kRv_end];        // RNN vectors incl. the three GRU states
 };
@@ -38,24 +36,32 @@ struct RnDevTables {
     float *bias = nullptr;
 };
 
+// Tile arrays that cross a stage boundary exist once per SLOT so that stage X of tile t+1 can run while
+// stage X+1 of tile t still reads tile t's arrays (batch.cu runs the four stages on four CUDA streams).
+struct RnSlot {
+    float *hp = nullptr;           // [N][kPHist + Qcap*480]   A -> B
+    cpx *X = nullptr, *P = nullptr;          // [N][Qcap][481]  B -> D
+    float *Ex = nullptr, *Ep = nullptr, *Exp = nullptr, *ceps = nullptr, *gains = nullptr, *gsm = nullptr;   // [N][Qcap][22]
+    float *featB = nullptr;        // [N][Qcap][8]
+    float *feat = nullptr;         // [N][Qcap][42]            B -> C
+    float *vad = nullptr;          // [N][Qcap]                C -> D
+    int *sil = nullptr, *pidx = nullptr, *nzlist = nullptr;   // [N][Qcap]
+    int *nz_tile = nullptr;        // [N] non-silent frames of the tile
+    long long *rank = nullptr;     // [N][Qcap]
+    PitchCand *cand = nullptr;     // [N][Qcap]
+};
+
 struct RnnoiseBatch {
     int device = 0;
     size_t N = 0, Qcap = 0;
     RnDevTables tab;
     RnPersist *persist = nullptr;
-    // tile arrays, [state][frame] major
-    float *hp = nullptr;           // [N][kPHist + Qcap*480]
-    cpx *X = nullptr, *P = nullptr;          // [N][Qcap][481]
-    float *Ex = nullptr, *Ep = nullptr, *Exp = nullptr, *ceps = nullptr, *gains = nullptr, *gsm = nullptr;   // [N][Qcap][22]
-    float *featB = nullptr;        // [N][Qcap][8]
-    float *feat = nullptr;         // [N][Qcap][42]
-    float *vad = nullptr;          // [N][Qcap]
-    int *sil = nullptr, *pidx = nullptr, *nzlist = nullptr;   // [N][Qcap]
-    long long *rank = nullptr;     // [N][Qcap]
-    PitchCand *cand = nullptr;     // [N][Qcap]
-    float *cepsc = nullptr;        // [N][8 + Qcap][22]
-    float *head = nullptr;         // [N][Qcap][480]
-    float *tail = nullptr;         // [N][1 + Qcap][480]
+    std::vector<RnSlot> slots;
+    // single-stage arrays (carried in place)
+    float *hp_hist = nullptr;      // [N][kPHist]   stage A: pitch/analysis history between tiles
+    float *cepsc = nullptr;        // [N][8 + Qcap][22]  stage B
+    float *head = nullptr;         // [N][Qcap][480]     stage D
+    float *tail = nullptr;         // [N][1 + Qcap][480] stage D
     std::vector<void *> allocs;
     size_t hp_stride() const { return kPHist + Qcap * kFrame; }
 };
@@ -175,7 +181,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_pfeat(Tables t, const 
 
 // ranks of non-silent frames: the cepstral ring advances only on them (denoise.c:358-369)
 __global__ void k_rn_compact(const int *__restrict__ sil, size_t N, int Q, size_t Qcap, RnPersist *persist, long long *rank,
-                             int *nzlist) {
+                             int *nzlist, int *nz_tile) {
     const size_t n = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
     const long long base = persist[n].nz_total;
@@ -184,30 +190,31 @@ __global__ void k_rn_compact(const int *__restrict__ sil, size_t N, int Q, size_
         if (!sil[n * Qcap + q]) { rank[n * Qcap + q] = base + j; nzlist[n * Qcap + j] = q; j++; }
         else rank[n * Qcap + q] = -1;
     }
-    persist[n].nz_tile = j;
+    nz_tile[n] = j;
+    persist[n].nz_total = base + j;
 }
 
-__global__ void k_rn_compact_copy(const float *__restrict__ ceps, const int *__restrict__ nzlist, const RnPersist *persist,
+__global__ void k_rn_compact_copy(const float *__restrict__ ceps, const int *__restrict__ nzlist, const int *__restrict__ nz_tile,
                                   size_t N, int Q, size_t Qcap, float *cepsc) {
     const size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;      // one thread per (state, j, coefficient)
     const size_t per = (size_t)Q * kNB;
     if (id >= N * per) return;
     const size_t n = id / per; const size_t r = id - n * per;
     const int j = (int)(r / kNB), k = (int)(r - (size_t)j * kNB);
-    if (j >= persist[n].nz_tile) return;
+    if (j >= nz_tile[n]) return;
     const int q = nzlist[n * Qcap + j];
     cepsc[(n * (8 + Qcap) + 8 + j) * kNB + k] = ceps[(n * Qcap + q) * kNB + k];
 }
 
 __global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_cepsfeat(const float *__restrict__ cepsc, const int *__restrict__ nzlist,
-                                                                   const long long *__restrict__ rank, const RnPersist *persist,
+                                                                   const long long *__restrict__ rank, const int *__restrict__ nz_tile,
                                                                    const float *featB, size_t N, int Q, size_t Qcap, float *feat) {
     __shared__ float smem[kWarpsPerCta * 80];
     const int w = threadIdx.x >> 5;
     const size_t id = (size_t)blockIdx.x * kWarpsPerCta + w;
     if (id >= N * (size_t)Q) return;
     const size_t n = id / Q; const int j = (int)(id - n * Q);
-    if (j >= persist[n].nz_tile) return;
+    if (j >= nz_tile[n]) return;
     const int q = nzlist[n * Qcap + j];
     const size_t f = n * Qcap + q;
     cepsfeat_warp(cepsc + (n * (8 + Qcap) + 8 + j) * kNB, rank[f], featB + f * 8, feat + f * kNFeat, smem + w * 80);
@@ -216,8 +223,8 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_cepsfeat(const float *
 // One CTA per state walks its non-silent frames in order.  Weights (bf16, 174 KB) stay in shared memory.
 __global__ void __launch_bounds__(kRnnThreads) k_rn_rnn(const unsigned short *__restrict__ weights, const float *__restrict__ bias,
                                                         const float *__restrict__ tansig, const float *__restrict__ feat,
-                                                        const int *__restrict__ nzlist, RnPersist *persist, size_t Qcap,
-                                                        float *gains, float *vad) {
+                                                        const int *__restrict__ nzlist, const int *__restrict__ nz_tile,
+                                                        RnPersist *persist, size_t Qcap, float *gains, float *vad) {
     extern __shared__ __align__(16) unsigned char smraw[];
     unsigned short *W = reinterpret_cast<unsigned short *>(smraw);
     float *b = reinterpret_cast<float *>(smraw + ((kRnnWeights * 2 + 15) & ~15));
@@ -230,7 +237,7 @@ __global__ void __launch_bounds__(kRnnThreads) k_rn_rnn(const unsigned short *__
     for (int i = threadIdx.x; i < 201; i += kRnnThreads) ts[i] = tansig[i];
     for (int i = threadIdx.x; i < kRv_end; i += kRnnThreads) scr[i] = persist[n].rnn_vec[i];
     __syncthreads();
-    const int nz = persist[n].nz_tile;
+    const int nz = nz_tile[n];
     for (int j = 0; j < nz; j++) {
         const int q = nzlist[n * Qcap + j];
         const size_t f = n * Qcap + q;
@@ -304,24 +311,31 @@ __global__ void k_rn_vadmin(const float *__restrict__ vad, size_t N, int C, int 
     if (vad_min) vad_min[n * vad_stride + vad_off + tt] = lo;
 }
 
-// carries to the next tile: pitch/analysis history of hp, the cepstral history, the synthesis tail
-__global__ void __launch_bounds__(256) k_rn_carry(float *hp, size_t hp_stride, float *cepsc, float *tail, RnPersist *persist,
-                                                  int Q, size_t Qcap) {
+// Carries between tiles, one per stage so that the stages of different tiles can overlap.
+// stage A: the last kPHist high-passed samples are the next tile's pitch/analysis history
+__global__ void __launch_bounds__(256) k_rn_hp_save(const float *__restrict__ hp, size_t hp_stride, float *__restrict__ hist, int Q) {
     const size_t n = blockIdx.x;
-    __shared__ float tmp[kPHist];
-    float *h = hp + n * hp_stride;
-    for (int i = threadIdx.x; i < kPHist; i += blockDim.x) tmp[i] = h[(size_t)Q * kFrame + i];
-    __syncthreads();
-    for (int i = threadIdx.x; i < kPHist; i += blockDim.x) h[i] = tmp[i];
-    __syncthreads();
-    const int nz = persist[n].nz_tile;
+    for (int i = threadIdx.x; i < kPHist; i += blockDim.x) hist[n * kPHist + i] = hp[n * hp_stride + (size_t)Q * kFrame + i];
+}
+__global__ void __launch_bounds__(256) k_rn_hp_load(float *__restrict__ hp, size_t hp_stride, const float *__restrict__ hist) {
+    const size_t n = blockIdx.x;
+    for (int i = threadIdx.x; i < kPHist; i += blockDim.x) hp[n * hp_stride + i] = hist[n * kPHist + i];
+}
+// stage B: the last 8 compacted cepstra move to the front (cepstral_mem, denoise.c:366-377)
+__global__ void __launch_bounds__(256) k_rn_ceps_carry(float *cepsc, const int *__restrict__ nz_tile, size_t Qcap) {
+    const size_t n = blockIdx.x;
+    __shared__ float tmp[8 * kNB];
+    const int nz = nz_tile[n];
     float *cc = cepsc + n * (8 + Qcap) * kNB;
     for (int i = threadIdx.x; i < 8 * kNB; i += blockDim.x) tmp[i] = cc[(size_t)nz * kNB + i];
     __syncthreads();
     for (int i = threadIdx.x; i < 8 * kNB; i += blockDim.x) cc[i] = tmp[i];
+}
+// stage D: the last frame's second half is the next tile's synthesis_mem (denoise.c:405-407)
+__global__ void __launch_bounds__(256) k_rn_tail_carry(float *tail, int Q, size_t Qcap) {
+    const size_t n = blockIdx.x;
     float *tl = tail + n * (1 + Qcap) * kFrame;
     for (int i = threadIdx.x; i < kFrame; i += blockDim.x) tl[i] = tl[(size_t)Q * kFrame + i];
-    if (threadIdx.x == 0) { persist[n].nz_total += nz; persist[n].nz_tile = 0; }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -355,15 +369,15 @@ void rnnoise_batch_destroy(RnnoiseBatch *r) {
 
 int rnnoise_batch_reset(RnnoiseBatch *r, cudaStream_t stream) {
     FVAD_CUDA_TRY(cudaMemsetAsync(r->persist, 0, sizeof(RnPersist) * r->N, stream));
-    FVAD_CUDA_TRY(cudaMemsetAsync(r->hp, 0, sizeof(float) * r->N * r->hp_stride(), stream));
+    FVAD_CUDA_TRY(cudaMemsetAsync(r->hp_hist, 0, sizeof(float) * r->N * kPHist, stream));
     FVAD_CUDA_TRY(cudaMemsetAsync(r->cepsc, 0, sizeof(float) * r->N * (8 + r->Qcap) * kNB, stream));
     FVAD_CUDA_TRY(cudaMemsetAsync(r->tail, 0, sizeof(float) * r->N * (1 + r->Qcap) * kFrame, stream));
     return FVAD_OK;
 }
 
-int rnnoise_batch_create(size_t n_states, size_t max_frames, int device, RnnoiseBatch **out) {
+int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int device, RnnoiseBatch **out) {
     *out = nullptr;
-    if (!n_states || !max_frames) return set_error(FVAD_EINVALID_ARGUMENT, "rnnoise_batch_create: zero size");
+    if (!n_states || !max_frames || n_slots < 1) return set_error(FVAD_EINVALID_ARGUMENT, "rnnoise_batch_create: zero size");
     int prev = 0;
     FVAD_CUDA_TRY(cudaGetDevice(&prev));
     FVAD_CUDA_TRY(cudaSetDevice(device));
@@ -372,15 +386,19 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int device, Rnnoise
     r->device = device; r->N = n_states; r->Qcap = max_frames;
     int rc = rn_tables_get(device, &r->tab);
     const size_t NQ = r->N * r->Qcap;
-#define RN_A(p, n) if (rc == FVAD_OK) rc = rn_alloc(r, &r->p, (n))
-    RN_A(persist, r->N);
-    RN_A(hp, r->N * r->hp_stride());
-    RN_A(X, NQ * kFreq); RN_A(P, NQ * kFreq);
-    RN_A(Ex, NQ * kNB); RN_A(Ep, NQ * kNB); RN_A(Exp, NQ * kNB); RN_A(ceps, NQ * kNB); RN_A(gains, NQ * kNB); RN_A(gsm, NQ * kNB);
-    RN_A(featB, NQ * 8); RN_A(feat, NQ * kNFeat); RN_A(vad, NQ);
-    RN_A(sil, NQ); RN_A(pidx, NQ); RN_A(nzlist, NQ); RN_A(rank, NQ); RN_A(cand, NQ);
-    RN_A(cepsc, r->N * (8 + r->Qcap) * kNB);
-    RN_A(head, NQ * kFrame); RN_A(tail, r->N * (1 + r->Qcap) * kFrame);
+    r->slots.resize(n_slots);
+#define RN_A(p, n) if (rc == FVAD_OK) rc = rn_alloc(r, &p, (n))
+    RN_A(r->persist, r->N);
+    RN_A(r->hp_hist, r->N * kPHist);
+    RN_A(r->cepsc, r->N * (8 + r->Qcap) * kNB);
+    RN_A(r->head, NQ * kFrame); RN_A(r->tail, r->N * (1 + r->Qcap) * kFrame);
+    for (RnSlot &s : r->slots) {
+        RN_A(s.hp, r->N * r->hp_stride());
+        RN_A(s.X, NQ * kFreq); RN_A(s.P, NQ * kFreq);
+        RN_A(s.Ex, NQ * kNB); RN_A(s.Ep, NQ * kNB); RN_A(s.Exp, NQ * kNB); RN_A(s.ceps, NQ * kNB); RN_A(s.gains, NQ * kNB); RN_A(s.gsm, NQ * kNB);
+        RN_A(s.featB, NQ * 8); RN_A(s.feat, NQ * kNFeat); RN_A(s.vad, NQ);
+        RN_A(s.sil, NQ); RN_A(s.pidx, NQ); RN_A(s.nzlist, NQ); RN_A(s.rank, NQ); RN_A(s.cand, NQ); RN_A(s.nz_tile, r->N);
+    }
 #undef RN_A
     if (rc == FVAD_OK) {
         cudaError_t e = cudaFuncSetAttribute(k_rn_analysis, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemAna);
@@ -398,37 +416,90 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int device, Rnnoise
     return FVAD_OK;
 }
 
-int rnnoise_batch_process(RnnoiseBatch *r, const float *d_in, size_t in_stride, int C, size_t Tn, float *d_out,
-                          size_t out_stride, size_t out_off, float *d_vad_min, float *d_vad_all, size_t vad_stride,
-                          size_t vad_off, cudaStream_t st) {
+int rnnoise_n_slots(const RnnoiseBatch *r) { return (int)r->slots.size(); }
+
+static int rn_check(RnnoiseBatch *r, int slot, size_t Qs) {
     if (!r) return set_error(FVAD_ENOT_INITIALIZED, "denoiser not initialised");
+    if (slot < 0 || slot >= (int)r->slots.size()) return set_error(FVAD_EINVALID_ARGUMENT, "bad slot %d", slot);
+    if (Qs > r->Qcap) return set_error(FVAD_EINVALID_ARGUMENT, "rnnoise: %zu frames exceed capacity %zu", Qs, r->Qcap);
+    return FVAD_OK;
+}
+
+// Stage A: high-pass biquad over the tile (sample-sequential per state).
+int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stride, int C, size_t Tn, cudaStream_t st) {
     const size_t Qs = Tn * (size_t)C;
+    FVAD_TRY(rn_check(r, slot, Qs));
     if (Qs == 0) return FVAD_OK;
-    if (Qs > r->Qcap) return set_error(FVAD_EINVALID_ARGUMENT, "rnnoise_batch_process: %zu frames exceed capacity %zu", Qs, r->Qcap);
+    RnSlot &s = r->slots[slot];
+    const size_t N = r->N;
+    FVAD_LAUNCH(k_rn_hp_load, (unsigned)N, 256, 0, st, s.hp, r->hp_stride(), r->hp_hist);
+    FVAD_LAUNCH(k_rn_biquad, (unsigned)N, 32, 0, st, d_in, in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
+    FVAD_LAUNCH(k_rn_hp_save, (unsigned)N, 256, 0, st, s.hp, r->hp_stride(), r->hp_hist, (int)Qs);
+    FVAD_CUDA_TRY(cudaGetLastError());
+    return FVAD_OK;
+}
+
+// Stage B: frame-parallel analysis, pitch and features (+ the two tiny sequential scans they need).
+int rnnoise_stage_b(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
+    FVAD_TRY(rn_check(r, slot, Qs));
+    if (Qs == 0) return FVAD_OK;
+    RnSlot &s = r->slots[slot];
     const int Q = (int)Qs;
     const size_t N = r->N, Qcap = r->Qcap, NQ = N * Qs;
     const Tables &t = r->tab.t;
     const unsigned warp_grid = (unsigned)ceil_div(NQ, kWarpsPerCta);
-    FVAD_LAUNCH(k_rn_biquad, (unsigned)N, 32, 0, st, d_in, in_stride, C, Q, r->persist, r->hp, r->hp_stride(), N);
-    FVAD_LAUNCH(k_rn_analysis, warp_grid, 32 * kWarpsPerCta, kSmemAna, st, t, r->hp, r->hp_stride(), N, Q, Qcap, r->X, r->Ex, r->ceps, r->sil);
-    FVAD_LAUNCH(k_rn_pitch, warp_grid, 32 * kWarpsPerCta, kSmemPitch, st, t, r->hp, r->hp_stride(), N, Q, Qcap, r->cand);
-    FVAD_LAUNCH(k_rn_pitch_seq, (unsigned)ceil_div(N, 32), 32, 0, st, r->cand, N, Q, Qcap, r->persist, r->pidx);
-    FVAD_LAUNCH(k_rn_pfeat, warp_grid, 32 * kWarpsPerCta, kSmemAna, st, t, r->hp, r->hp_stride(), N, Q, Qcap, r->pidx, r->X, r->Ex, r->P,
-                r->Ep, r->Exp, r->featB);
-    FVAD_LAUNCH(k_rn_compact, (unsigned)ceil_div(N, 32), 32, 0, st, r->sil, N, Q, Qcap, r->persist, r->rank, r->nzlist);
-    FVAD_LAUNCH(k_rn_compact_copy, (unsigned)ceil_div(NQ * kNB, 256), 256, 0, st, r->ceps, r->nzlist, r->persist, N, Q, Qcap, r->cepsc);
-    FVAD_LAUNCH(k_rn_cepsfeat, warp_grid, 32 * kWarpsPerCta, 0, st, r->cepsc, r->nzlist, r->rank, r->persist, r->featB, N, Q, Qcap, r->feat);
-    FVAD_LAUNCH(k_rn_rnn, (unsigned)N, kRnnThreads, kSmemRnn, st, r->tab.weights, r->tab.bias, t.tansig, r->feat, r->nzlist, r->persist,
-                Qcap, r->gains, r->vad);
-    FVAD_LAUNCH(k_rn_gain_scan, (unsigned)ceil_div(N * kNB, 64), 64, 0, st, r->gains, r->sil, N, Q, Qcap, r->persist, r->gsm, r->vad);
-    FVAD_LAUNCH(k_rn_synth, warp_grid, 32 * kWarpsPerCta, kSmemSyn, st, t, N, Q, Qcap, r->X, r->P, r->Ex, r->Ep, r->Exp, r->gains, r->gsm,
-                r->sil, r->head, r->tail);
-    FVAD_LAUNCH(k_rn_out, (unsigned)ceil_div(NQ * kFrame, 256), 256, 0, st, r->head, r->tail, N, C, Q, Qcap, d_out, out_stride, out_off);
-    if (d_vad_min || d_vad_all)
-        FVAD_LAUNCH(k_rn_vadmin, (unsigned)ceil_div(N * Tn, 128), 128, 0, st, r->vad, N, C, (int)Tn, Qcap, d_vad_min, d_vad_all, vad_stride, vad_off);
-    FVAD_LAUNCH(k_rn_carry, (unsigned)N, 256, 0, st, r->hp, r->hp_stride(), r->cepsc, r->tail, r->persist, Q, Qcap);
+    FVAD_LAUNCH(k_rn_analysis, warp_grid, 32 * kWarpsPerCta, kSmemAna, st, t, s.hp, r->hp_stride(), N, Q, Qcap, s.X, s.Ex, s.ceps, s.sil);
+    FVAD_LAUNCH(k_rn_pitch, warp_grid, 32 * kWarpsPerCta, kSmemPitch, st, t, s.hp, r->hp_stride(), N, Q, Qcap, s.cand);
+    FVAD_LAUNCH(k_rn_pitch_seq, (unsigned)ceil_div(N, 32), 32, 0, st, s.cand, N, Q, Qcap, r->persist, s.pidx);
+    FVAD_LAUNCH(k_rn_pfeat, warp_grid, 32 * kWarpsPerCta, kSmemAna, st, t, s.hp, r->hp_stride(), N, Q, Qcap, s.pidx, s.X, s.Ex, s.P,
+                s.Ep, s.Exp, s.featB);
+    FVAD_LAUNCH(k_rn_compact, (unsigned)ceil_div(N, 32), 32, 0, st, s.sil, N, Q, Qcap, r->persist, s.rank, s.nzlist, s.nz_tile);
+    FVAD_LAUNCH(k_rn_compact_copy, (unsigned)ceil_div(NQ * kNB, 256), 256, 0, st, s.ceps, s.nzlist, s.nz_tile, N, Q, Qcap, r->cepsc);
+    FVAD_LAUNCH(k_rn_cepsfeat, warp_grid, 32 * kWarpsPerCta, 0, st, r->cepsc, s.nzlist, s.rank, s.nz_tile, s.featB, N, Q, Qcap, s.feat);
+    FVAD_LAUNCH(k_rn_ceps_carry, (unsigned)N, 256, 0, st, r->cepsc, s.nz_tile, Qcap);
     FVAD_CUDA_TRY(cudaGetLastError());
     return FVAD_OK;
+}
+
+// Stage C: the RNN, frame-sequential per state.
+int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
+    FVAD_TRY(rn_check(r, slot, Qs));
+    if (Qs == 0) return FVAD_OK;
+    RnSlot &s = r->slots[slot];
+    FVAD_LAUNCH(k_rn_rnn, (unsigned)r->N, kRnnThreads, kSmemRnn, st, r->tab.weights, r->tab.bias, r->tab.t.tansig, s.feat, s.nzlist,
+                s.nz_tile, r->persist, r->Qcap, s.gains, s.vad);
+    FVAD_CUDA_TRY(cudaGetLastError());
+    return FVAD_OK;
+}
+
+// Stage D: gain smoothing scan, synthesis, overlap-add to normalised PCM, per-frame VAD minimum.
+int rnnoise_stage_d(RnnoiseBatch *r, int slot, int C, size_t Tn, float *d_out, size_t out_stride, size_t out_off, float *d_vad_min,
+                    float *d_vad_all, size_t vad_stride, size_t vad_off, cudaStream_t st) {
+    const size_t Qs = Tn * (size_t)C;
+    FVAD_TRY(rn_check(r, slot, Qs));
+    if (Qs == 0) return FVAD_OK;
+    RnSlot &s = r->slots[slot];
+    const int Q = (int)Qs;
+    const size_t N = r->N, Qcap = r->Qcap, NQ = N * Qs;
+    const unsigned warp_grid = (unsigned)ceil_div(NQ, kWarpsPerCta);
+    FVAD_LAUNCH(k_rn_gain_scan, (unsigned)ceil_div(N * kNB, 64), 64, 0, st, s.gains, s.sil, N, Q, Qcap, r->persist, s.gsm, s.vad);
+    FVAD_LAUNCH(k_rn_synth, warp_grid, 32 * kWarpsPerCta, kSmemSyn, st, r->tab.t, N, Q, Qcap, s.X, s.P, s.Ex, s.Ep, s.Exp, s.gains, s.gsm,
+                s.sil, r->head, r->tail);
+    FVAD_LAUNCH(k_rn_out, (unsigned)ceil_div(NQ * kFrame, 256), 256, 0, st, r->head, r->tail, N, C, Q, Qcap, d_out, out_stride, out_off);
+    if (d_vad_min || d_vad_all)
+        FVAD_LAUNCH(k_rn_vadmin, (unsigned)ceil_div(N * Tn, 128), 128, 0, st, s.vad, N, C, (int)Tn, Qcap, d_vad_min, d_vad_all, vad_stride, vad_off);
+    FVAD_LAUNCH(k_rn_tail_carry, (unsigned)N, 256, 0, st, r->tail, Q, Qcap);
+    FVAD_CUDA_TRY(cudaGetLastError());
+    return FVAD_OK;
+}
+
+int rnnoise_batch_process(RnnoiseBatch *r, const float *d_in, size_t in_stride, int C, size_t Tn, float *d_out,
+                          size_t out_stride, size_t out_off, float *d_vad_min, float *d_vad_all, size_t vad_stride,
+                          size_t vad_off, cudaStream_t st) {
+    FVAD_TRY(rnnoise_stage_a(r, 0, d_in, in_stride, C, Tn, st));
+    FVAD_TRY(rnnoise_stage_b(r, 0, Tn * (size_t)C, st));
+    FVAD_TRY(rnnoise_stage_c(r, 0, Tn * (size_t)C, st));
+    return rnnoise_stage_d(r, 0, C, Tn, d_out, out_stride, out_off, d_vad_min, d_vad_all, vad_stride, vad_off, st);
 }
 
 }  // namespace fvad
@@ -468,7 +539,7 @@ extern "C" int fvad_denoiser_batch_create(size_t n_streams, int device, fvad_den
     if (!d) return set_error(FVAD_EOUT_OF_MEMORY, "host allocation failed");
     d->N = n_streams; d->device = device;
     d->Qcap = std::max<size_t>(1, std::min<size_t>(4096, 65536 / n_streams));
-    int rc = rnnoise_batch_create(n_streams, d->Qcap, device, &d->rn);
+    int rc = rnnoise_batch_create(n_streams, d->Qcap, 1, device, &d->rn);
     int prev = 0; cudaGetDevice(&prev); cudaSetDevice(device);
     if (rc == FVAD_OK && (cudaMalloc(&d->d_in, sizeof(float) * d->N * d->Qcap * 480) != cudaSuccess ||
                           cudaMalloc(&d->d_out, sizeof(float) * d->N * d->Qcap * 480) != cudaSuccess ||

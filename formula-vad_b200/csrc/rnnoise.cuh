@@ -9,7 +9,7 @@ struct RnnoiseBatch;
 
 // n_states independent DenoiseStates (Denoiser.init -> rnnoise_create(NULL), Denoiser.zig:22-31),
 // each able to take up to max_frames consecutive 480-sample frames per call.
-int rnnoise_batch_create(size_t n_states, size_t max_frames, int device, RnnoiseBatch **out);
+int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int device, RnnoiseBatch **out);
 void rnnoise_batch_destroy(RnnoiseBatch *r);
 int rnnoise_batch_reset(RnnoiseBatch *r, cudaStream_t stream);
 
@@ -23,5 +23,17 @@ int rnnoise_batch_reset(RnnoiseBatch *r, cudaStream_t stream);
 int rnnoise_batch_process(RnnoiseBatch *r, const float *d_in, size_t in_stride, int n_channels, size_t n_tframes,
                           float *d_out, size_t out_stride, size_t out_off, float *d_vad_min, float *d_vad_all,
                           size_t vad_stride, size_t vad_off, cudaStream_t stream);
+
+
+// The same work as four stages that batch.cu issues on four CUDA streams (wavefront over tiles): arrays
+// that cross a stage boundary exist once per slot, cross-tile carries stay inside their stage.
+//   A: biquad (sample-sequential)           B: analysis / pitch / features (frame-parallel)
+//   C: RNN (frame-sequential)               D: gains, synthesis, overlap-add, VAD minimum
+int rnnoise_n_slots(const RnnoiseBatch *r);
+int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stride, int n_channels, size_t n_tframes, cudaStream_t st);
+int rnnoise_stage_b(RnnoiseBatch *r, int slot, size_t n_vframes, cudaStream_t st);
+int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t n_vframes, cudaStream_t st);
+int rnnoise_stage_d(RnnoiseBatch *r, int slot, int n_channels, size_t n_tframes, float *d_out, size_t out_stride, size_t out_off,
+                    float *d_vad_min, float *d_vad_all, size_t vad_stride, size_t vad_off, cudaStream_t st);
 
 }  // namespace fvad
