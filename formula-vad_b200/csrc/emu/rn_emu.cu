@@ -52,8 +52,10 @@ int rn_emu_tile(void *h, const float *in, size_t in_stride, int Tn, float *out, 
     // k_rn_biquad: sequential per state over the virtual frame sequence
     for (int q = 0; q < Q; q++) {
         const int tt = q / C, c = q % C;
-        for (int i = 0; i < kFrame; i++)
-            hp[kPHist + (size_t)q * kFrame + i] = biquad_step(in[c * in_stride + (size_t)tt * kFrame + i], e.biq[0], e.biq[1]);
+        float sm0[33], sm1[33];
+        int flag = 0;
+        for (int b0 = 0; b0 < kFrame; b0 += 32)
+            biquad_block_warp(&in[c * in_stride + (size_t)tt * kFrame + b0], &hp[kPHist + (size_t)q * kFrame + b0], e.biq[0], e.biq[1], sm0, sm1, &flag);
     }
     std::vector<cpx> X((size_t)Q * kFreq), P((size_t)Q * kFreq);
     std::vector<float> Ex(Q * kNB), Ep(Q * kNB), Exp(Q * kNB), ceps(Q * kNB), featB(Q * 8), feat((size_t)Q * kNFeat, 0.f);

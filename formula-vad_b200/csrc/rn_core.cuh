@@ -841,5 +841,160 @@ RN_HD float biquad_step(float in_norm, float &m0, float &m1) {
     return yi;
 }
 
+// ------------------------------------------------------------------------------------------
+// The same biquad step WITHOUT double precision: error-free transformations in f32 (TwoSum, FMA
+// products) evaluate E0 = m1 - 2x + A0*y and E1 = x - A1*y exactly as short expansions and round them
+// once.  The reference rounds twice (to double, then to float) -- the two agree unless the exact
+// value lies within ~2^-29 ulp of a rounding boundary.  Each step therefore also computes, OFF the
+// dependent chain, the exact distance of E from the rounding boundary and raises `hazard` when it is
+// within 2^-14 ulp of one, or when a tiny result, an underflowing product or a cancellation beyond 2^12
+// (with an inexact double intermediate) makes the bound unsafe.  A hazard never changes the result: the caller discards the
+// block and replays it with biquad_step (the reference's own double arithmetic).  Dependent chain per
+// sample: FADD, FMUL, FADD, TwoSum tail (4), FADD, FADD = 9 f32 ops (~38 cycles) instead of
+// FADD, F2F, DFMA, DADD, F2F (~84 cycles measured on B200).
+// ------------------------------------------------------------------------------------------
+RN_HD unsigned f2u(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(f);
+#else
+    union { float f; unsigned u; } c; c.f = f; return c.u;
+#endif
+}
+RN_HD float u2f(unsigned u) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    union { float f; unsigned u; } c; c.u = u; return c.f;
+#endif
+}
+RN_HD float fma_rn(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+    return __fmaf_rn(a, b, c);
+#else
+    return fmaf(a, b, c);
+#endif
+}
+RN_HD void two_sum(float a, float b, float &s, float &e) {
+    s = a + b;
+    const float bb = s - a;
+    e = (a - (s - bb)) + (b - bb);
+}
+// r = RN(w + uh) was computed with exact residual v (E = r + v up to ~2^-46 |v|): is r = RN(E) beyond doubt?
+// `big` bounds the magnitudes whose 2^-53 relative perturbation the reference's double roundings add.
+RN_HD bool round_hazard(float r, float v, float big) {
+    const unsigned ur = f2u(r), e = (ur >> 23) & 0xffu;
+    const float av = v < 0 ? -v : v, ar = r < 0 ? -r : r;
+    if (e <= 26u || e >= 250u) return !(ar == 0.0f && av == 0.0f && big == 0.0f);   // tiny / zero / huge results: not analysed
+    float half = u2f((e - 24u) << 23);                         // ulp(r) / 2
+    if ((ur & 0x7fffffu) == 0u) half *= 0.5f;                  // below a power of two the grid is twice as fine
+    return (av >= half * 0.99993896484375f) || (big >= ar * 4096.0f);
+}
+RN_HD float biquad_step_eft(float in_norm, float &m0, float &m1, bool &hazard) {
+    const float A0 = 1.99599f, A1 = 0.99600f;
+    const float x = in_norm * 32767.0f;
+    const float c = -2.0f * x;                                 // exact
+    float dh, dl;
+    two_sum(m1, c, dh, dl);                                    // m1 - 2x = dh + dl          (off the chain)
+    const float y = x + m0;                                    // the reference's own float add
+    // ---- m0' = RN(m1 - 2x + A0*y) -------------------------------------------------------------
+    const float p = A0 * y, pl = fma_rn(A0, y, -p);            // A0*y = p + pl
+    float w, f;
+    two_sum(p, dh, w, f);                                      // p + dh = w + f
+    float th, tl, uh, ul, r, g;
+    two_sum(pl, dl, th, tl);
+    two_sum(th, f, uh, ul);                                    // pl + dl + f = uh + ul + tl
+    two_sum(w, uh, r, g);                                      // E0 = r + g + ul + tl
+    // A0*y - 2x and x - A1*y are EXACT in double when x == 0 or the exponents of x and y are within 2
+    // (48-bit product + 24-bit term span <= 53 bits): then the reference's inner rounding perturbs nothing.
+    const int ex = (int)((f2u(x) >> 23) & 0xffu), ey = (int)((f2u(y) >> 23) & 0xffu);
+    const bool inner_exact = (x == 0.0f) || (ex - ey <= 2 && ey - ex <= 2);
+    const float ap = p < 0 ? -p : p, ac = c < 0 ? -c : c;
+    bool hz = round_hazard(r, g + (ul + tl), inner_exact ? 0.0f : ap + ac);
+    hz |= (ap != 0.0f && ap < 1.0e-30f);                       // fma error term would underflow
+    // ---- m1' = RN(x - A1*y) ---------------------------------------------------------------------
+    const float q = A1 * y, ql = fma_rn(A1, y, -q);            // A1*y = q + ql
+    float s, e, u, u2, n1, g1;
+    two_sum(x, -q, s, e);                                      // x - q = s + e
+    two_sum(e, -ql, u, u2);
+    two_sum(s, u, n1, g1);                                     // E1 = n1 + g1 + u2
+    const float aq = q < 0 ? -q : q, ax = x < 0 ? -x : x;
+    hz |= round_hazard(n1, g1 + u2, inner_exact ? 0.0f : aq + ax);
+    hazard |= hz;
+    m0 = r;
+    m1 = n1;
+    return y;
+}
+
+// The chain-only version of biquad_step_eft (same operations for y, m0', m1'; no hazard analysis): what the
+// one sequential lane executes.  ~30 instructions per sample, 9 of them on the dependent chain.
+RN_HD float biquad_step_fast(float in_norm, float &m0, float &m1) {
+    const float A0 = 1.99599f, A1 = 0.99600f;
+    const float x = in_norm * 32767.0f;
+    const float c = -2.0f * x;
+    float dh, dl;
+    two_sum(m1, c, dh, dl);
+    const float y = x + m0;
+    const float p = A0 * y, pl = fma_rn(A0, y, -p);
+    float w, f;
+    two_sum(p, dh, w, f);
+    const float th = pl + dl;
+    const float uh = th + f;
+    const float r = w + uh;
+    m1 = fma_rn(-A1, y, x);                                    // RN(x - A1*y): one rounding of the exact value
+    m0 = r;
+    return y;
+}
+
+// One block of 32 samples for one state, executed by a warp: lane 0 runs the chain with the fast step and
+// records the state before every sample; then all 32 lanes re-run their sample with the full hazard
+// analysis in parallel and compare their result with the state lane 0 carried on; if any lane objects,
+// lane 0 replays the block with the reference's double arithmetic.  (m0, m1) is the filter state, meaningful
+// on lane 0 (a register on the device); sm0/sm1 = 33 floats each; flag = 1 int (0 on entry and on exit).
+// While the state is tiny (digital silence decaying into denormals) every block would be hazardous, so the
+// block goes straight to the double path.
+RN_HD void biquad_block_warp(const float *xin, float *yout, float &m0, float &m1, float *sm0, float *sm1, int *flag) {
+    float e0 = 0, e1 = 0;                                   // lane 0: state at the end of the fast pass
+    RN_PHASE
+        if (lane == 0) {
+            const float a0 = m0 < 0 ? -m0 : m0, a1 = m1 < 0 ? -m1 : m1;
+            if ((a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f)) {
+                for (int i = 0; i < 32; i++) yout[i] = biquad_step(xin[i], m0, m1);
+                *flag = 2;                                  // already final
+            } else {
+                float xr[32];                               // all loads first: nothing on the chain waits for memory
+#pragma unroll
+                for (int i = 0; i < 32; i++) xr[i] = xin[i];
+                e0 = m0; e1 = m1;
+#pragma unroll
+                for (int i = 0; i < 32; i++) {
+                    sm0[i] = e0; sm1[i] = e1;
+                    yout[i] = biquad_step_fast(xr[i], e0, e1);
+                }
+                sm0[32] = e0; sm1[32] = e1;
+            }
+        }
+    RN_END
+    RN_PHASE
+        if (*flag != 2) {
+            float a = sm0[lane], b = sm1[lane];
+            bool hz = false;
+            const float yv = biquad_step_eft(xin[lane], a, b, hz);
+            hz |= (f2u(a) != f2u(sm0[lane + 1])) | (f2u(b) != f2u(sm1[lane + 1])) | (f2u(yv) != f2u(yout[lane]));
+            if (hz) *flag = 1;                              // any lane may set it; same value
+        }
+    RN_END
+    RN_PHASE
+        if (lane == 0) {
+            const int fl = *flag;
+            if (fl == 1) {
+                for (int i = 0; i < 32; i++) yout[i] = biquad_step(xin[i], m0, m1);
+            } else if (fl == 0) {
+                m0 = e0; m1 = e1;
+            }
+            if (fl) *flag = 0;
+        }
+    RN_END
+}
+
 }  // namespace rn
 }  // namespace fvad

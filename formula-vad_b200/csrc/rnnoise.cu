@@ -101,32 +101,105 @@ static int rn_tables_get(int device, RnDevTables *out) {
 // ------------------------------------------------------------------------------------------
 // kernels
 // ------------------------------------------------------------------------------------------
-// One warp per state; lane 0 walks the samples, the warp stages frames through shared memory so
-// that global traffic is coalesced and off the dependent chain.
-__global__ void __launch_bounds__(32) k_rn_biquad(const float *__restrict__ in, size_t in_stride, int C, int Q,
+// Two warps per state.  The IIR is sample-sequential, so ONE lane (warp 0, lane 0) walks the samples with
+// the fast f32 step (rn_core.cuh biquad_step_fast, 9 dependent f32 ops per sample) and records the state
+// before every sample.  Warp 1 runs one block (32 samples) behind: it re-evaluates every sample of the
+// previous block with the full hazard analysis (biquad_step_eft), compares with what lane 0 carried on, and
+// also stages frames between global and shared memory, so neither verification nor memory latency sits on
+// the dependent chain.  A hazardous block is replayed by lane 0 with the reference's double arithmetic from
+// the recorded state; the replay reproduces the fast result unless the fast step was really wrong (a
+// ~2^-29 event per sample), in which case the block in flight is recomputed as well.
+constexpr int kBqBlock = 32, kBqBlocksPerFrame = kFrame / kBqBlock;
+__global__ void __launch_bounds__(64) k_rn_biquad(const float *__restrict__ in, size_t in_stride, int C, int Q,
                                                   RnPersist *persist, float *__restrict__ hp, size_t hp_stride, size_t N) {
     const size_t n = blockIdx.x;
     if (n >= N) return;
-    __shared__ float sx[2][kFrame];
-    __shared__ float sy[kFrame];
-    const int lane = threadIdx.x;
-    float m0 = persist[n].biq[0], m1 = persist[n].biq[1];
+    __shared__ __align__(16) float sx[2][kFrame];
+    __shared__ __align__(16) float sy[2][kFrame];
+    __shared__ __align__(16) float2 P[2][kBqBlock + 2];          // (m0, m1) before every sample of the block, + the end state
+    __shared__ int F[2], FINAL[2];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float m0 = persist[n].biq[0], m1 = persist[n].biq[1];         // meaningful on thread 0
     float *dst = hp + n * hp_stride + kPHist;
     auto src = [&](int q) { return in + (n * C + (q % C)) * in_stride + (size_t)(q / C) * kFrame; };
-    if (Q > 0) for (int i = lane; i < kFrame; i += 32) sx[0][i] = src(0)[i];
-    __syncwarp();
-    for (int q = 0; q < Q; q++) {
-        const int cur = q & 1;
-        if (q + 1 < Q) { const float *s = src(q + 1); for (int i = lane; i < kFrame; i += 32) sx[cur ^ 1][i] = s[i]; }
-        if (lane == 0) {
-#pragma unroll 8
-            for (int i = 0; i < kFrame; i++) sy[i] = biquad_step(sx[cur][i], m0, m1);
+    if (threadIdx.x < 2) { F[threadIdx.x] = 0; FINAL[threadIdx.x] = 0; }
+    if (Q > 0) for (int i = threadIdx.x; i < kFrame; i += 64) sx[0][i] = src(0)[i];
+    __syncthreads();
+    const int G = Q * kBqBlocksPerFrame;
+    for (int g = 0; g <= G + 1; g++) {
+        if (warp == 0) {
+            if (lane == 0 && g < G) {                              // ---- the chain: block g
+                const int q = g / kBqBlocksPerFrame, b0 = (g - q * kBqBlocksPerFrame) * kBqBlock, par = g & 1;
+                const float *xin = &sx[q & 1][b0];
+                float *yout = &sy[q & 1][b0];
+                const float a0 = fabsf(m0), a1 = fabsf(m1);
+                if ((a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f)) {
+                    for (int i = 0; i < kBqBlock; i++) yout[i] = biquad_step(xin[i], m0, m1);   // denormal tail of a silence
+                    FINAL[par] = 1;
+                } else {
+                    float xr[kBqBlock];
+#pragma unroll
+                    for (int i = 0; i < kBqBlock; i++) xr[i] = xin[i];
+                    // one lane issues every shared-memory store of the block, and a later load queues behind them:
+                    // pack 4 samples per store (3 x STS.128 instead of 12 x STS.32)
+#pragma unroll
+                    for (int i = 0; i < kBqBlock; i += 4) {
+                        float4 sa, sb, yy;
+                        sa.x = m0; sa.y = m1; yy.x = biquad_step_fast(xr[i], m0, m1);
+                        sa.z = m0; sa.w = m1; yy.y = biquad_step_fast(xr[i + 1], m0, m1);
+                        sb.x = m0; sb.y = m1; yy.z = biquad_step_fast(xr[i + 2], m0, m1);
+                        sb.z = m0; sb.w = m1; yy.w = biquad_step_fast(xr[i + 3], m0, m1);
+                        *reinterpret_cast<float4 *>(&P[par][i]) = sa;
+                        *reinterpret_cast<float4 *>(&P[par][i + 2]) = sb;
+                        *reinterpret_cast<float4 *>(&yout[i]) = yy;
+                    }
+                    P[par][kBqBlock] = make_float2(m0, m1);
+                    FINAL[par] = 0;
+                }
+            }
+        } else {
+            if (g >= 1 && g - 1 < G) {                             // ---- verification of block g-1
+                const int gv = g - 1, q = gv / kBqBlocksPerFrame, b0 = (gv - q * kBqBlocksPerFrame) * kBqBlock, par = gv & 1;
+                bool hz = false;
+                if (!FINAL[par]) {
+                    const float2 pre = P[par][lane], post = P[par][lane + 1];
+                    float a = pre.x, b = pre.y;
+                    const float yv = biquad_step_eft(sx[q & 1][b0 + lane], a, b, hz);
+                    hz |= (__float_as_uint(a) != __float_as_uint(post.x)) |
+                          (__float_as_uint(b) != __float_as_uint(post.y)) |
+                          (__float_as_uint(yv) != __float_as_uint(sy[q & 1][b0 + lane]));
+                }
+                const unsigned any = __ballot_sync(0xffffffffu, hz);
+                if (lane == 0) F[par] = any != 0u;
+            }
+            if (g >= 2) {                                          // ---- block g-2 is final: frame I/O at frame edges
+                const int gf = g - 2, q = gf / kBqBlocksPerFrame;
+                if (gf - q * kBqBlocksPerFrame == kBqBlocksPerFrame - 1) {
+                    for (int i = lane; i < kFrame; i += 32) dst[(size_t)q * kFrame + i] = sy[q & 1][i];
+                    // sx[q & 1] is free once frame q is final: fetch frame q + 2 (frame q + 1 was fetched a frame ago)
+                    if (q + 2 < Q) { const float *s2 = src(q + 2); for (int i = lane; i < kFrame; i += 32) sx[q & 1][i] = s2[i]; }
+                }
+            }
+            if (g == 0 && Q > 1) { const float *s1 = src(1); for (int i = lane; i < kFrame; i += 32) sx[1][i] = s1[i]; }
         }
-        __syncwarp();
-        for (int i = lane; i < kFrame; i += 32) dst[(size_t)q * kFrame + i] = sy[i];
-        __syncwarp();
+        __syncthreads();
+        if (threadIdx.x == 0 && g >= 1 && g - 1 < G && F[(g - 1) & 1]) {   // ---- replay of a hazardous block g-1
+            const int gv = g - 1, q = gv / kBqBlocksPerFrame, b0 = (gv - q * kBqBlocksPerFrame) * kBqBlock, par = gv & 1;
+            float r0 = P[par][0].x, r1 = P[par][0].y;
+            for (int i = 0; i < kBqBlock; i++) sy[q & 1][b0 + i] = biquad_step(sx[q & 1][b0 + i], r0, r1);
+            if (__float_as_uint(r0) != __float_as_uint(P[par][kBqBlock].x) || __float_as_uint(r1) != __float_as_uint(P[par][kBqBlock].y)) {
+                // the fast step was wrong: block g (computed from its end state) is void, redo it from the true state
+                m0 = r0; m1 = r1;
+                if (g < G) {
+                    const int q2 = g / kBqBlocksPerFrame, c0 = (g - q2 * kBqBlocksPerFrame) * kBqBlock;
+                    for (int i = 0; i < kBqBlock; i++) sy[q2 & 1][c0 + i] = biquad_step(sx[q2 & 1][c0 + i], m0, m1);
+                    FINAL[g & 1] = 1;
+                }
+            }
+        }
+        __syncthreads();                                           // replay results visible before anyone moves on
     }
-    if (lane == 0) { persist[n].biq[0] = m0; persist[n].biq[1] = m1; }
+    if (threadIdx.x == 0) { persist[n].biq[0] = m0; persist[n].biq[1] = m1; }
 }
 
 constexpr int kWarpsPerCta = 8;
@@ -433,7 +506,7 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
     RnSlot &s = r->slots[slot];
     const size_t N = r->N;
     FVAD_LAUNCH(k_rn_hp_load, (unsigned)N, 256, 0, st, s.hp, r->hp_stride(), r->hp_hist);
-    FVAD_LAUNCH(k_rn_biquad, (unsigned)N, 32, 0, st, d_in, in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
+    FVAD_LAUNCH(k_rn_biquad, (unsigned)N, 64, 0, st, d_in, in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
     FVAD_LAUNCH(k_rn_hp_save, (unsigned)N, 256, 0, st, s.hp, r->hp_stride(), r->hp_hist, (int)Qs);
     FVAD_CUDA_TRY(cudaGetLastError());
     return FVAD_OK;
