@@ -117,31 +117,40 @@ __global__ void __launch_bounds__(64) k_rn_biquad(const float *__restrict__ in, 
     __shared__ __align__(16) float sx[2][kFrame];
     __shared__ __align__(16) float sy[2][kFrame];
     __shared__ __align__(16) float2 P[2][kBqBlock + 2];          // (m0, m1) before every sample of the block, + the end state
-    __shared__ int F[2], FINAL[2];
+    __shared__ int FINAL[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float m0 = persist[n].biq[0], m1 = persist[n].biq[1];         // meaningful on thread 0
     float *dst = hp + n * hp_stride + kPHist;
     auto src = [&](int q) { return in + (n * C + (q % C)) * in_stride + (size_t)(q / C) * kFrame; };
-    if (threadIdx.x < 2) { F[threadIdx.x] = 0; FINAL[threadIdx.x] = 0; }
+    if (threadIdx.x < 2) FINAL[threadIdx.x] = 0;
     if (Q > 0) for (int i = threadIdx.x; i < kFrame; i += 64) sx[0][i] = src(0)[i];
     __syncthreads();
     const int G = Q * kBqBlocksPerFrame;
+    float pf[kFrame / 32]; int pf_buf = -1;                        // warp 1: a frame in flight from global memory
+    float xr[kBqBlock];                                            // thread 0: the block's input, fetched one block ahead
+    if (threadIdx.x == 0 && G > 0) {
+#pragma unroll
+        for (int i = 0; i < kBqBlock; i++) xr[i] = sx[0][i];
+    }
     for (int g = 0; g <= G + 1; g++) {
+        bool hz = false;
         if (warp == 0) {
             if (lane == 0 && g < G) {                              // ---- the chain: block g
                 const int q = g / kBqBlocksPerFrame, b0 = (g - q * kBqBlocksPerFrame) * kBqBlock, par = g & 1;
-                const float *xin = &sx[q & 1][b0];
                 float *yout = &sy[q & 1][b0];
+                float xn[kBqBlock];                                // next block's input: loaded before this block's stores queue up
+                if (g + 1 < G) {
+                    const int q1 = (g + 1) / kBqBlocksPerFrame, b1 = (g + 1 - q1 * kBqBlocksPerFrame) * kBqBlock;
+#pragma unroll
+                    for (int i = 0; i < kBqBlock; i++) xn[i] = sx[q1 & 1][b1 + i];
+                }
                 const float a0 = fabsf(m0), a1 = fabsf(m1);
                 if ((a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f)) {
-                    for (int i = 0; i < kBqBlock; i++) yout[i] = biquad_step(xin[i], m0, m1);   // denormal tail of a silence
+#pragma unroll
+                    for (int i = 0; i < kBqBlock; i++) yout[i] = biquad_step(xr[i], m0, m1);   // denormal tail of a silence
                     FINAL[par] = 1;
                 } else {
-                    float xr[kBqBlock];
-#pragma unroll
-                    for (int i = 0; i < kBqBlock; i++) xr[i] = xin[i];
-                    // one lane issues every shared-memory store of the block, and a later load queues behind them:
-                    // pack 4 samples per store (3 x STS.128 instead of 12 x STS.32)
+                    // one lane issues every shared-memory store of the block: pack 4 samples per store
 #pragma unroll
                     for (int i = 0; i < kBqBlock; i += 4) {
                         float4 sa, sb, yy;
@@ -156,11 +165,17 @@ __global__ void __launch_bounds__(64) k_rn_biquad(const float *__restrict__ in, 
                     P[par][kBqBlock] = make_float2(m0, m1);
                     FINAL[par] = 0;
                 }
+#pragma unroll
+                for (int i = 0; i < kBqBlock; i++) xr[i] = xn[i];
             }
         } else {
+            if (pf_buf >= 0) {                                     // ---- the frame fetched one iteration ago lands in shared memory
+#pragma unroll
+                for (int k = 0; k < kFrame / 32; k++) sx[pf_buf][lane + 32 * k] = pf[k];
+                pf_buf = -1;
+            }
             if (g >= 1 && g - 1 < G) {                             // ---- verification of block g-1
                 const int gv = g - 1, q = gv / kBqBlocksPerFrame, b0 = (gv - q * kBqBlocksPerFrame) * kBqBlock, par = gv & 1;
-                bool hz = false;
                 if (!FINAL[par]) {
                     const float2 pre = P[par][lane], post = P[par][lane + 1];
                     float a = pre.x, b = pre.y;
@@ -169,21 +184,30 @@ __global__ void __launch_bounds__(64) k_rn_biquad(const float *__restrict__ in, 
                           (__float_as_uint(b) != __float_as_uint(post.y)) |
                           (__float_as_uint(yv) != __float_as_uint(sy[q & 1][b0 + lane]));
                 }
-                const unsigned any = __ballot_sync(0xffffffffu, hz);
-                if (lane == 0) F[par] = any != 0u;
             }
             if (g >= 2) {                                          // ---- block g-2 is final: frame I/O at frame edges
                 const int gf = g - 2, q = gf / kBqBlocksPerFrame;
                 if (gf - q * kBqBlocksPerFrame == kBqBlocksPerFrame - 1) {
                     for (int i = lane; i < kFrame; i += 32) dst[(size_t)q * kFrame + i] = sy[q & 1][i];
                     // sx[q & 1] is free once frame q is final: fetch frame q + 2 (frame q + 1 was fetched a frame ago)
-                    if (q + 2 < Q) { const float *s2 = src(q + 2); for (int i = lane; i < kFrame; i += 32) sx[q & 1][i] = s2[i]; }
+                    // (into registers now, into shared memory next iteration: the load latency never meets the barrier)
+                    if (q + 2 < Q) {
+                        const float *s2 = src(q + 2);
+#pragma unroll
+                        for (int k = 0; k < kFrame / 32; k++) pf[k] = s2[lane + 32 * k];
+                        pf_buf = q & 1;
+                    }
                 }
             }
-            if (g == 0 && Q > 1) { const float *s1 = src(1); for (int i = lane; i < kFrame; i += 32) sx[1][i] = s1[i]; }
+            if (g == 0 && Q > 1) {
+                const float *s1 = src(1);
+#pragma unroll
+                for (int k = 0; k < kFrame / 32; k++) pf[k] = s1[lane + 32 * k];
+                pf_buf = 1;
+            }
         }
-        __syncthreads();
-        if (threadIdx.x == 0 && g >= 1 && g - 1 < G && F[(g - 1) & 1]) {   // ---- replay of a hazardous block g-1
+        const int verdict = __syncthreads_or(hz ? 1 : 0);          // the verdict on block g-1 travels with the barrier
+        if (threadIdx.x == 0 && verdict) {                         // ---- replay of a hazardous block g-1
             const int gv = g - 1, q = gv / kBqBlocksPerFrame, b0 = (gv - q * kBqBlocksPerFrame) * kBqBlock, par = gv & 1;
             float r0 = P[par][0].x, r1 = P[par][0].y;
             for (int i = 0; i < kBqBlock; i++) sy[q & 1][b0 + i] = biquad_step(sx[q & 1][b0 + i], r0, r1);
