@@ -70,6 +70,19 @@ int stft_tables_get(int device, const StftTables **out) {
         FVAD_CUDA_TRY(cudaMalloc(&t.d_window, sizeof(float) * kFft));
         FVAD_CUDA_TRY(cudaMalloc(&t.d_tw, sizeof(cpx) * kFftC));
         FVAD_CUDA_TRY(cudaMalloc(&t.d_stw, sizeof(cpx) * kFftC / 2));
+        FVAD_CUDA_TRY(cudaMalloc(&t.d_twB, sizeof(cpx) * 15 * 64));
+        {   // pass-B twiddles per thread t = (pb, jj): row-major [15][64] so that a warp reads 256 contiguous bytes
+            std::vector<cpx> twb(15 * 64);
+            for (int th = 0; th < 64; th++) {
+                const int jj = th & 15;
+                for (int q = 1; q < 4; q++) twb[(q - 1) * 64 + th] = tw[jj * 16 * q];                       // stage m=16
+                for (int g = 0; g < 4; g++)
+                    for (int q = 1; q < 4; q++) twb[(3 + 3 * g + q - 1) * 64 + th] = tw[(jj + 16 * g) * 4 * q];   // stage m=64
+            }
+            FVAD_CUDA_TRY(cudaMemcpy(t.d_twB, twb.data(), sizeof(cpx) * twb.size(), cudaMemcpyHostToDevice));
+            for (int k = 1; k < 4; k++)
+                for (int q = 1; q < 4; q++) t.twA.v[(k - 1) * 3 + q - 1] = tw[k * 64 * q];                 // stage m=4, uniform
+        }
         FVAD_CUDA_TRY(cudaMemcpy(t.d_window, w.data(), sizeof(float) * kFft, cudaMemcpyHostToDevice));
         FVAD_CUDA_TRY(cudaMemcpy(t.d_tw, tw.data(), sizeof(cpx) * kFftC, cudaMemcpyHostToDevice));
         FVAD_CUDA_TRY(cudaMemcpy(t.d_stw, stw.data(), sizeof(cpx) * kFftC / 2, cudaMemcpyHostToDevice));
@@ -105,9 +118,10 @@ __device__ __forceinline__ int slot(int pos) { return pos + (pos >> 4) + (pos >>
 constexpr int kSlots = 1024 + 64 + 4 + 4;
 
 template <bool FULL>
-__global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, size_t n_rows, size_t row_stride,
+__global__ void __launch_bounds__(64, 16) k_stft2048(const float *__restrict__ pcm, size_t n_rows, size_t row_stride,
                                                  size_t n_frames, size_t hop, const float *__restrict__ window,
                                                  const cpx *__restrict__ tw, const cpx *__restrict__ stw,
+                                                 const cpx *__restrict__ twB, const StftTwA twA,
                                                  float norm_factor, StftBands bands, float *__restrict__ d_band,
                                                  size_t band_frame_stride, size_t band_frame_offset,
                                                  float *__restrict__ d_spectra) {
@@ -115,23 +129,10 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
     __shared__ float mags[FULL ? kBins + 3 : 256];
     const int t = threadIdx.x;
 
-    // ---- per-thread twiddles, loaded once ----
-    // pass A, stage m=4 (fstride 64): tw[k*64], tw[k*128], tw[k*192] for k=1..3 (uniform)
-    cpx twA[3][3];
-#pragma unroll
-    for (int k = 1; k < 4; k++)
-#pragma unroll
-        for (int q = 1; q < 4; q++) twA[k - 1][q - 1] = tw[k * 64 * q];
-    // pass B: b = 256-block, jj = position inside the 16-stride comb
+    // Twiddles are NOT kept in registers across frames (48 registers would halve the occupancy): pass A's are
+    // uniform and arrive as kernel parameters (constant-bank operands), pass B's come from a compact
+    // per-thread table that stays in L1.
     const int pb = t >> 4, jj = t & 15;
-    cpx twB1[3];            // stage m=16 (fstride 16): tw[jj*16*q]
-#pragma unroll
-    for (int q = 1; q < 4; q++) twB1[q - 1] = tw[jj * 16 * q];
-    cpx twB2[4][3];         // stage m=64 (fstride 4): tw[(jj+16g)*4*q]
-#pragma unroll
-    for (int g = 0; g < 4; g++)
-#pragma unroll
-        for (int q = 1; q < 4; q++) twB2[g][q - 1] = tw[(jj + 16 * g) * 4 * q];
     // pass A block: thread t owns input residue n_low = t; its 16 points land in block blk
     const int blk = ((t & 3) << 4) | (t & 12) | (t >> 4);
     const float2 *win2 = reinterpret_cast<const float2 *>(window);
@@ -158,13 +159,18 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
         bfly4(a[0], a[4], a[8], a[12], a[4], a[8], a[12]);   // stage m=4, k=0
 #pragma unroll
         for (int k = 1; k < 4; k++)
-            bfly4(a[k], a[k + 4], a[k + 8], a[k + 12], c_mul(a[k + 4], twA[k - 1][0]), c_mul(a[k + 8], twA[k - 1][1]),
-                  c_mul(a[k + 12], twA[k - 1][2]));
+            bfly4(a[k], a[k + 4], a[k + 8], a[k + 12], c_mul(a[k + 4], twA.v[(k - 1) * 3]), c_mul(a[k + 8], twA.v[(k - 1) * 3 + 1]),
+                  c_mul(a[k + 12], twA.v[(k - 1) * 3 + 2]));
 #pragma unroll
         for (int i = 0; i < 16; i++) sm[slot(16 * blk + i)] = make_float2(a[i].r, a[i].i);
         __syncthreads();
 
         // ---------------- pass B: stages m=16 and m=64 -------------------------------------
+        const cpx *twb = twB + t;
+        asm volatile("" : "+l"(twb));                   // opaque per frame: keeps the 15 loads inside the loop
+        cpx twB1[3];
+#pragma unroll
+        for (int q = 0; q < 3; q++) twB1[q] = twb[q * 64];
 #pragma unroll
         for (int i = 0; i < 16; i++) {
             float2 v = sm[slot(256 * pb + jj + 16 * i)];
@@ -180,11 +186,11 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
         }
 #pragma unroll
         for (int g = 0; g < 4; g++) {                   // m=64: points (jj+16g)+64r, twiddle index jj+16g
+            const cpx w1 = twb[(3 + 3 * g) * 64], w2 = twb[(4 + 3 * g) * 64], w3 = twb[(5 + 3 * g) * 64];
             if (g == 0 && jj == 0)
                 bfly4(a[0], a[4], a[8], a[12], a[4], a[8], a[12]);
             else
-                bfly4(a[g], a[g + 4], a[g + 8], a[g + 12], c_mul(a[g + 4], twB2[g][0]), c_mul(a[g + 8], twB2[g][1]),
-                      c_mul(a[g + 12], twB2[g][2]));
+                bfly4(a[g], a[g + 4], a[g + 8], a[g + 12], c_mul(a[g + 4], w1), c_mul(a[g + 8], w2), c_mul(a[g + 12], w3));
         }
 #pragma unroll
         for (int i = 0; i < 16; i++) sm[slot(256 * pb + jj + 16 * i)] = make_float2(a[i].r, a[i].i);
@@ -290,11 +296,11 @@ int stft_launch(const StftTables &tb, const float *d_pcm, size_t n_rows, size_t 
     const float norm = d_window_override ? norm_override : tb.norm_factor;
     const size_t total = n_rows * n_frames;
     const int sms = device_sm_count(device);
-    size_t grid = (size_t)sms * 12;                    // persistent: 12 CTAs of 2 warps per SM
+    size_t grid = (size_t)sms * 16;                    // persistent: 16 CTAs of 2 warps per SM (64 registers per thread)
     if (grid > total) grid = total;
     if (full) {
         FVAD_LAUNCH(k_stft2048<true>, (unsigned)grid, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win,
-                    tb.d_tw, tb.d_stw, norm, b, d_band, band_frame_stride, band_frame_offset, d_spectra);
+                    tb.d_tw, tb.d_stw, tb.d_twB, tb.twA, norm, b, d_band, band_frame_stride, band_frame_offset, d_spectra);
     } else {
         // covering range for the pruned pass: lo[0]..hi[n-1] must span every band
         StftBands bb = b;
@@ -308,10 +314,10 @@ int stft_launch(const StftTables &tb, const float *d_pcm, size_t n_rows, size_t 
         bool ok = bb.lo[0] == lo && bb.hi[bb.n_bands - 1] == hi;
         if (!ok) {
             FVAD_LAUNCH(k_stft2048<true>, (unsigned)grid, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win,
-                        tb.d_tw, tb.d_stw, norm, b, d_band, band_frame_stride, band_frame_offset, d_spectra);
+                        tb.d_tw, tb.d_stw, tb.d_twB, tb.twA, norm, b, d_band, band_frame_stride, band_frame_offset, d_spectra);
         } else {
             FVAD_LAUNCH(k_stft2048<false>, (unsigned)grid, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop,
-                        win, tb.d_tw, tb.d_stw, norm, bb, d_band, band_frame_stride, band_frame_offset, d_spectra);
+                        win, tb.d_tw, tb.d_stw, tb.d_twB, tb.twA, norm, bb, d_band, band_frame_stride, band_frame_offset, d_spectra);
         }
     }
     FVAD_CUDA_TRY(cudaGetLastError());
