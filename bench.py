@@ -36,6 +36,7 @@ SEED = 0xF1AD5EED00000000
 METRIC = "audio-sec processed/sec (x real-time)"
 UNIT = "audio_s/s"
 SR = 48000
+_REAL_STDOUT = sys.stdout
 
 # Algorithmic bytes per unit for each kernel (DESIGN.md "Kernels"): the stage's compulsory input + output,
 # tables and weights resident.  Unit = one 480-sample RNNoise frame unless noted.
@@ -128,7 +129,7 @@ def reference_arm(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "segments": segs,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     return 0
 
 
@@ -392,7 +393,7 @@ def b200_arm(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "stft": stft,
             "cpu_baseline": cpu, "kernel_shares": shares, "segments": n_segments,
         }
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -400,6 +401,12 @@ def b200_arm(args):
 
 
 def main():
+    # Libraries (NCCL's version banner, torchrun notices) write to stdout; the contract is ONE JSON line there.
+    # Point fd 1 at stderr for the whole run and print the JSON line through a saved copy of the real stdout.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         return reference_arm(args)

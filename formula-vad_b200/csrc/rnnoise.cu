@@ -438,6 +438,7 @@ __global__ void __launch_bounds__(256) k_rn_tail_carry(float *tail, int Q, size_
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
+constexpr size_t kBiquadSmemHog = 200 * 1024;
 constexpr size_t kSmemAna = (size_t)kWarpsPerCta * kScrAna * sizeof(float);
 constexpr size_t kSmemPitch = (size_t)kWarpsPerCta * kScrPitch * sizeof(float);
 constexpr size_t kSmemSyn = (size_t)kWarpsPerCta * kScrSyn * sizeof(float);
@@ -503,6 +504,7 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_pitch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemPitch);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_synth, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemSyn);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemRnn);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBiquadSmemHog);
         if (e != cudaSuccess) rc = set_error(FVAD_ECUDA, "cudaFuncSetAttribute: %s (is this an sm_100 device?)", cudaGetErrorString(e));
     }
     if (rc == FVAD_OK) rc = rnnoise_batch_reset(r, 0);
@@ -530,7 +532,9 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
     RnSlot &s = r->slots[slot];
     const size_t N = r->N;
     FVAD_LAUNCH(k_rn_hp_load, (unsigned)N, 256, 0, st, s.hp, r->hp_stride(), r->hp_hist);
-    FVAD_LAUNCH(k_rn_biquad, (unsigned)N, 64, 0, st, d_in, in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
+    // kBiquadSmemHog bytes of unused dynamic shared memory keep every other CTA off the chain's SM: the chain
+    // lane is issue-latency bound and loses ~13 % when frame-parallel kernels of other stages share its scheduler
+    FVAD_LAUNCH(k_rn_biquad, (unsigned)N, 64, kBiquadSmemHog, st, d_in, in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
     FVAD_LAUNCH(k_rn_hp_save, (unsigned)N, 256, 0, st, s.hp, r->hp_stride(), r->hp_hist, (int)Qs);
     FVAD_CUDA_TRY(cudaGetLastError());
     return FVAD_OK;

@@ -112,6 +112,11 @@ __device__ __forceinline__ void bfly4(cpx &f0, cpx &f1, cpx &f2, cpx &f3, cpx s0
     f3.i = s5.i + s4.r;
 }
 
+__device__ __forceinline__ cpx ldg_cpx(const cpx *p) {        // 8-byte read-only global load
+    const float2 v = __ldg(reinterpret_cast<const float2 *>(p));
+    return cpx{v.x, v.y};
+}
+
 // shared-memory slot of complex position pos (0..1023): one float2 of padding per 16 and per
 // 256 positions keeps all three access patterns (16-blocks, stride-16, stride-256) conflict-free.
 __device__ __forceinline__ int slot(int pos) { return pos + (pos >> 4) + (pos >> 8); }
@@ -170,7 +175,7 @@ __global__ void __launch_bounds__(64, 16) k_stft2048(const float *__restrict__ p
         asm volatile("" : "+l"(twb));                   // opaque per frame: keeps the 15 loads inside the loop
         cpx twB1[3];
 #pragma unroll
-        for (int q = 0; q < 3; q++) twB1[q] = twb[q * 64];
+        for (int q = 0; q < 3; q++) twB1[q] = ldg_cpx(twb + q * 64);
 #pragma unroll
         for (int i = 0; i < 16; i++) {
             float2 v = sm[slot(256 * pb + jj + 16 * i)];
@@ -178,19 +183,14 @@ __global__ void __launch_bounds__(64, 16) k_stft2048(const float *__restrict__ p
         }
 #pragma unroll
         for (int g = 0; g < 4; g++) {                   // m=16: points jj+16*(4g+r), twiddle index jj
-            if (jj == 0)
-                bfly4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3]);
-            else
-                bfly4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3], c_mul(a[4 * g + 1], twB1[0]),
-                      c_mul(a[4 * g + 2], twB1[1]), c_mul(a[4 * g + 3], twB1[2]));
+            // (lanes with jj == 0 multiply by W^0 = (1,-0) exactly as KissFFT does: no divergent special case)
+            bfly4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3], c_mul(a[4 * g + 1], twB1[0]),
+                  c_mul(a[4 * g + 2], twB1[1]), c_mul(a[4 * g + 3], twB1[2]));
         }
 #pragma unroll
         for (int g = 0; g < 4; g++) {                   // m=64: points (jj+16g)+64r, twiddle index jj+16g
-            const cpx w1 = twb[(3 + 3 * g) * 64], w2 = twb[(4 + 3 * g) * 64], w3 = twb[(5 + 3 * g) * 64];
-            if (g == 0 && jj == 0)
-                bfly4(a[0], a[4], a[8], a[12], a[4], a[8], a[12]);
-            else
-                bfly4(a[g], a[g + 4], a[g + 8], a[g + 12], c_mul(a[g + 4], w1), c_mul(a[g + 8], w2), c_mul(a[g + 12], w3));
+            const cpx w1 = ldg_cpx(twb + (3 + 3 * g) * 64), w2 = ldg_cpx(twb + (4 + 3 * g) * 64), w3 = ldg_cpx(twb + (5 + 3 * g) * 64);
+            bfly4(a[g], a[g + 4], a[g + 8], a[g + 12], c_mul(a[g + 4], w1), c_mul(a[g + 8], w2), c_mul(a[g + 12], w3));
         }
 #pragma unroll
         for (int i = 0; i < 16; i++) sm[slot(256 * pb + jj + 16 * i)] = make_float2(a[i].r, a[i].i);

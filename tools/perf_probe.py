@@ -9,21 +9,28 @@ secs = int(sys.argv[2]) if len(sys.argv) > 2 else 120
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
 use_dn = int(sys.argv[4]) if len(sys.argv) > 4 else 1
 prof = int(sys.argv[5]) if len(sys.argv) > 5 else 0
+host = int(sys.argv[6]) if len(sys.argv) > 6 else 0
 n = secs * 48000
 x = torch.empty(S, n, dtype=torch.float32, device="cuda")
 fvad.synth_device(x.data_ptr(), n, 0xF1AD5EED00000000, 0, S, 0, n)
 torch.cuda.synchronize()
 b = fvad.PipelineBatch(S, use_denoiser=bool(use_dn))
+if host:
+    h = torch.empty(S, n, dtype=torch.float32, pin_memory=True); h.copy_(x); torch.cuda.synchronize()
+    rows = [h.data_ptr() + 4 * n * r for r in range(S)]
 for r in range(reps):
     b.reset()
     if prof and r == reps - 1:
         fvad.profile_enable(True)
     t0 = time.time()
-    b.push_device(x.data_ptr(), n, n, n)
+    if host:
+        b.push_rows(rows, n)
+    else:
+        b.push_device(x.data_ptr(), n, n, n)
     b.sync()
     dt = time.time() - t0
     nseg = sum(len(b.segments(s)) for s in range(S))
-    print(f"S={S} secs={secs} dn={use_dn} rep {r}: {dt*1e3:.1f} ms  -> {S*secs/dt:.0f} x real-time, segments {nseg}", flush=True)
+    print(f"S={S} secs={secs} dn={use_dn} host={host} rep {r}: {dt*1e3:.1f} ms  -> {S*secs/dt:.0f} x real-time, segments {nseg}", flush=True)
 if prof:
     rep = fvad.profile_report()
     tot = sum(v["total_ms"] for v in rep.values())
