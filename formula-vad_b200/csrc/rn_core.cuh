@@ -935,8 +935,12 @@ RN_HD float biquad_step_fast(float in_norm, float &m0, float &m1) {
     two_sum(m1, c, dh, dl);
     const float y = x + m0;
     const float p = A0 * y, pl = fma_rn(A0, y, -p);
-    float w, f;
-    two_sum(p, dh, w, f);
+    // error term of w = p + dh by Fast2Sum on the magnitude-ordered pair (2 dependent operations after w
+    // instead of TwoSum's 4; the ordering is decided while w is being computed)
+    const float w = p + dh;
+    const bool pbig = fabsf(p) >= fabsf(dh);
+    const float hi = pbig ? p : dh, lo = pbig ? dh : p;
+    const float f = (hi - w) + lo;
     const float th = pl + dl;
     const float uh = th + f;
     const float r = w + uh;

@@ -68,24 +68,30 @@ int stft_tables_get(int device, const StftTables **out) {
         FVAD_CUDA_TRY(cudaGetDevice(&prev));
         FVAD_CUDA_TRY(cudaSetDevice(device));
         FVAD_CUDA_TRY(cudaMalloc(&t.d_window, sizeof(float) * kFft));
-        FVAD_CUDA_TRY(cudaMalloc(&t.d_tw, sizeof(cpx) * kFftC));
-        FVAD_CUDA_TRY(cudaMalloc(&t.d_stw, sizeof(cpx) * kFftC / 2));
-        FVAD_CUDA_TRY(cudaMalloc(&t.d_twB, sizeof(cpx) * 15 * 64));
-        {   // pass-B twiddles per thread t = (pb, jj): row-major [15][64] so that a warp reads 256 contiguous bytes
-            std::vector<cpx> twb(15 * 64);
-            for (int th = 0; th < 64; th++) {
-                const int jj = th & 15;
-                for (int q = 1; q < 4; q++) twb[(q - 1) * 64 + th] = tw[jj * 16 * q];                       // stage m=16
-                for (int g = 0; g < 4; g++)
-                    for (int q = 1; q < 4; q++) twb[(3 + 3 * g + q - 1) * 64 + th] = tw[(jj + 16 * g) * 4 * q];   // stage m=64
-            }
-            FVAD_CUDA_TRY(cudaMemcpy(t.d_twB, twb.data(), sizeof(cpx) * twb.size(), cudaMemcpyHostToDevice));
-            for (int k = 1; k < 4; k++)
-                for (int q = 1; q < 4; q++) t.twA.v[(k - 1) * 3 + q - 1] = tw[k * 64 * q];                 // stage m=4, uniform
-        }
         FVAD_CUDA_TRY(cudaMemcpy(t.d_window, w.data(), sizeof(float) * kFft, cudaMemcpyHostToDevice));
-        FVAD_CUDA_TRY(cudaMemcpy(t.d_tw, tw.data(), sizeof(cpx) * kFftC, cudaMemcpyHostToDevice));
-        FVAD_CUDA_TRY(cudaMemcpy(t.d_stw, stw.data(), sizeof(cpx) * kFftC / 2, cudaMemcpyHostToDevice));
+        FVAD_CUDA_TRY(cudaMalloc(&t.d_twB4, sizeof(float) * 4 * 15 * 64));
+        FVAD_CUDA_TRY(cudaMalloc(&t.d_tw4, sizeof(float) * 4 * kFftC));
+        FVAD_CUDA_TRY(cudaMalloc(&t.d_stw4, sizeof(float) * 4 * kFftC / 2));
+        {   // packed-arithmetic twiddles: every entry is (wr, wr, wi, wi), one 16-byte load feeds both frames
+            auto dup = [](cpx w, float *o) { o[0] = w.r; o[1] = w.r; o[2] = w.i; o[3] = w.i; };
+            std::vector<float> twb(4 * 15 * 64), t4(4 * kFftC), s4(4 * kFftC / 2);
+            for (int th = 0; th < 64; th++) {             // pass-B twiddles per thread t = (pb, jj), [15][64]
+                const int jj = th & 15;
+                for (int q = 1; q < 4; q++) dup(tw[jj * 16 * q], &twb[4 * ((q - 1) * 64 + th)]);                            // stage m=16
+                for (int g = 0; g < 4; g++)
+                    for (int q = 1; q < 4; q++) dup(tw[(jj + 16 * g) * 4 * q], &twb[4 * ((3 + 3 * g + q - 1) * 64 + th)]);  // stage m=64
+            }
+            for (int i = 0; i < kFftC; i++) dup(tw[i], &t4[4 * i]);
+            for (int i = 0; i < kFftC / 2; i++) dup(stw[i], &s4[4 * i]);
+            FVAD_CUDA_TRY(cudaMemcpy(t.d_twB4, twb.data(), sizeof(float) * twb.size(), cudaMemcpyHostToDevice));
+            FVAD_CUDA_TRY(cudaMemcpy(t.d_tw4, t4.data(), sizeof(float) * t4.size(), cudaMemcpyHostToDevice));
+            FVAD_CUDA_TRY(cudaMemcpy(t.d_stw4, s4.data(), sizeof(float) * s4.size(), cudaMemcpyHostToDevice));
+            for (int k = 1; k < 4; k++)
+                for (int q = 1; q < 4; q++) {             // stage m=4, uniform over threads: kernel parameter
+                    const cpx w = tw[k * 64 * q];
+                    t.twA.v[(k - 1) * 3 + q - 1] = make_float4(w.r, w.r, w.i, w.i);
+                }
+        }
         FVAD_CUDA_TRY(cudaSetDevice(prev));
         g_tabs[device] = t;
         g_tab_ready[device] = true;
@@ -97,178 +103,198 @@ int stft_tables_get(int device, const StftTables **out) {
 // ------------------------------------------------------------------------------------------
 // device
 // ------------------------------------------------------------------------------------------
-// radix-4 butterfly, forward branch of kf_bfly4 (kiss_fft.c:38-84); s0,s1,s2 are the
-// already twiddled inputs F[m]*tw1, F[2m]*tw2, F[3m]*tw3.
-__device__ __forceinline__ void bfly4(cpx &f0, cpx &f1, cpx &f2, cpx &f3, cpx s0, cpx s1, cpx s2) {
-    cpx s5 = c_sub(f0, s1);
-    f0 = c_add(f0, s1);
-    cpx s3 = c_add(s0, s2);
-    cpx s4 = c_sub(s0, s2);
-    f2 = c_sub(f0, s3);
-    f0 = c_add(f0, s3);
-    f1.r = s5.r + s4.i;
-    f1.i = s5.i - s4.r;
-    f3.r = s5.r - s4.i;
-    f3.i = s5.i + s4.r;
+// One CTA of 64 threads transforms TWO frames at a time with Blackwell's packed f32x2 arithmetic
+// (FADD2 / FMUL2; sm_100 __fadd2_rn / __fmul2_rn): every complex value is held as re = (A.re, B.re),
+// im = (A.im, B.im) for frames A and B, so both frames execute the same instruction on the same twiddle
+// and each IEEE operation is done once per frame exactly as KissFFT does it -- half the issue slots per
+// frame, which is what moves this kernel from issue-bound to HBM-bound.
+struct c2 { float2 re, im; };                                   // one complex value of frame A and of frame B
+__device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 sub2(float2 a, float2 b) { return __fadd2_rn(a, make_float2(-b.x, -b.y)); }   // a + (-b) == a - b
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+// ptxas (12.9) contracts a packed multiply feeding a packed add/sub into FFMA2 even for mul.rn.f32x2 and with
+// -fmad=false, which would drop a rounding the reference performs.  Sums of products therefore add with SCALAR
+// instructions (never contracted under -fmad=false); tools/check_sass.sh asserts the library has no FFMA2.
+__device__ __forceinline__ float2 padd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 psub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ c2 cadd(c2 a, c2 b) { return c2{add2(a.re, b.re), add2(a.im, b.im)}; }
+__device__ __forceinline__ c2 csub(c2 a, c2 b) { return c2{sub2(a.re, b.re), sub2(a.im, b.im)}; }
+// C_MUL (kiss_fft _kiss_fft_guts.h): m.r = a.r*b.r - a.i*b.i, m.i = a.r*b.i + a.i*b.r.  w = (wr,wr,wi,wi).
+__device__ __forceinline__ c2 cmul(c2 a, float4 w) {
+    const float2 wr = make_float2(w.x, w.y), wi = make_float2(w.z, w.w);
+    return c2{psub(mul2(a.re, wr), mul2(a.im, wi)), padd(mul2(a.re, wi), mul2(a.im, wr))};
+}
+// radix-4 butterfly, forward branch of kf_bfly4 (kiss_fft.c:38-84); s0,s1,s2 are the already twiddled
+// inputs F[m]*tw1, F[2m]*tw2, F[3m]*tw3.
+__device__ __forceinline__ void bfly4(c2 &f0, c2 &f1, c2 &f2, c2 &f3, c2 s0, c2 s1, c2 s2) {
+    const c2 s5 = csub(f0, s1);
+    f0 = cadd(f0, s1);
+    const c2 s3 = cadd(s0, s2);
+    const c2 s4 = csub(s0, s2);
+    f2 = csub(f0, s3);
+    f0 = cadd(f0, s3);
+    f1.re = add2(s5.re, s4.im);
+    f1.im = sub2(s5.im, s4.re);
+    f3.re = sub2(s5.re, s4.im);
+    f3.im = add2(s5.im, s4.re);
 }
 
-__device__ __forceinline__ cpx ldg_cpx(const cpx *p) {        // 8-byte read-only global load
-    const float2 v = __ldg(reinterpret_cast<const float2 *>(p));
-    return cpx{v.x, v.y};
-}
-
-// shared-memory slot of complex position pos (0..1023): one float2 of padding per 16 and per
-// 256 positions keeps all three access patterns (16-blocks, stride-16, stride-256) conflict-free.
+// shared-memory slot of complex position pos (0..1023): one element of padding per 16 and per 256 positions
+// keeps all three access patterns (16-blocks, stride-16, stride-256) conflict-free (16-byte elements:
+// every quarter-warp touches eight distinct 16-byte bank groups).
 __device__ __forceinline__ int slot(int pos) { return pos + (pos >> 4) + (pos >> 8); }
 constexpr int kSlots = 1024 + 64 + 4 + 4;
+__device__ __forceinline__ c2 lds_c2(const float4 *sm, int pos) { const float4 v = sm[slot(pos)]; return c2{make_float2(v.x, v.y), make_float2(v.z, v.w)}; }
+__device__ __forceinline__ void sts_c2(float4 *sm, int pos, c2 v) { sm[slot(pos)] = make_float4(v.re.x, v.re.y, v.im.x, v.im.y); }
 
 template <bool FULL>
-__global__ void __launch_bounds__(64, 16) k_stft2048(const float *__restrict__ pcm, size_t n_rows, size_t row_stride,
+__global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, size_t n_rows, size_t row_stride,
                                                  size_t n_frames, size_t hop, const float *__restrict__ window,
-                                                 const cpx *__restrict__ tw, const cpx *__restrict__ stw,
-                                                 const cpx *__restrict__ twB, const StftTwA twA,
+                                                 const float4 *__restrict__ tw4, const float4 *__restrict__ stw4,
+                                                 const float4 *__restrict__ twB4, const StftTwA twA,
                                                  float norm_factor, StftBands bands, float *__restrict__ d_band,
                                                  size_t band_frame_stride, size_t band_frame_offset,
                                                  float *__restrict__ d_spectra) {
-    __shared__ float2 sm[kSlots];
-    __shared__ float mags[FULL ? kBins + 3 : 256];
+    __shared__ __align__(16) float4 sm[kSlots];
+    __shared__ float mags[2][FULL ? kBins + 3 : 256];
     const int t = threadIdx.x;
-
-    // Twiddles are NOT kept in registers across frames (48 registers would halve the occupancy): pass A's are
-    // uniform and arrive as kernel parameters (constant-bank operands), pass B's come from a compact
-    // per-thread table that stays in L1.
+    // pass B: b = 256-block, jj = position inside the 16-stride comb
     const int pb = t >> 4, jj = t & 15;
     // pass A block: thread t owns input residue n_low = t; its 16 points land in block blk
     const int blk = ((t & 3) << 4) | (t & 12) | (t >> 4);
     const float2 *win2 = reinterpret_cast<const float2 *>(window);
+    const size_t total = n_rows * n_frames, pairs = (total + 1) / 2;
 
-    const size_t total = n_rows * n_frames;
-    for (size_t fid = blockIdx.x; fid < total; fid += gridDim.x) {
-        const size_t r = fid / n_frames, f = fid - r * n_frames;
-        const float2 *src = reinterpret_cast<const float2 *>(pcm + r * row_stride + f * hop);
+    for (size_t pid = blockIdx.x; pid < pairs; pid += gridDim.x) {
+        const size_t fidA = 2 * pid, fidB = (fidA + 1 < total) ? fidA + 1 : fidA;     // odd tail: B repeats A, not stored
+        const size_t rA = fidA / n_frames, fA = fidA - rA * n_frames;
+        const size_t rB = fidB / n_frames, fB = fidB - rB * n_frames;
+        const float2 *srcA = reinterpret_cast<const float2 *>(pcm + rA * row_stride + fA * hop);
+        const float2 *srcB = reinterpret_cast<const float2 *>(pcm + rB * row_stride + fB * hop);
 
         // ---------------- pass A: load + window, stages m=1 and m=4 in registers ------------
-        cpx a[16];
+        c2 a[16];
 #pragma unroll
         for (int e = 0; e < 16; e++) {
-            float2 v = src[64 * e + t];                 // coalesced: 32 lanes x 8 B contiguous
-            float2 w = win2[64 * e + t];
+            const float2 vA = srcA[64 * e + t];          // coalesced: 32 lanes x 8 B contiguous
+            const float2 vB = srcB[64 * e + t];
+            const float2 w = win2[64 * e + t];
             // input n = t + 64 e = t + 64 (k4 + 4 k5) -> local slot i = 4 k4 + k5
             const int i = 4 * (e & 3) + (e >> 2);
-            a[i].r = v.x * w.x;                         // FFT.zig:150,155 sample * window[idx]
-            a[i].i = v.y * w.y;
+            a[i].re = make_float2(vA.x * w.x, vB.x * w.x);   // FFT.zig:150,155 sample * window[idx]
+            a[i].im = make_float2(vA.y * w.y, vB.y * w.y);
         }
 #pragma unroll
-        for (int g = 0; g < 4; g++)                     // stage m=1: twiddles are all W^0
+        for (int g = 0; g < 4; g++)                     // stage m=1: twiddles are all W^0 (x*(1,-0) == x)
             bfly4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3]);
         bfly4(a[0], a[4], a[8], a[12], a[4], a[8], a[12]);   // stage m=4, k=0
 #pragma unroll
         for (int k = 1; k < 4; k++)
-            bfly4(a[k], a[k + 4], a[k + 8], a[k + 12], c_mul(a[k + 4], twA.v[(k - 1) * 3]), c_mul(a[k + 8], twA.v[(k - 1) * 3 + 1]),
-                  c_mul(a[k + 12], twA.v[(k - 1) * 3 + 2]));
+            bfly4(a[k], a[k + 4], a[k + 8], a[k + 12], cmul(a[k + 4], twA.v[(k - 1) * 3]), cmul(a[k + 8], twA.v[(k - 1) * 3 + 1]),
+                  cmul(a[k + 12], twA.v[(k - 1) * 3 + 2]));
 #pragma unroll
-        for (int i = 0; i < 16; i++) sm[slot(16 * blk + i)] = make_float2(a[i].r, a[i].i);
+        for (int i = 0; i < 16; i++) sts_c2(sm, 16 * blk + i, a[i]);
         __syncthreads();
 
         // ---------------- pass B: stages m=16 and m=64 -------------------------------------
-        const cpx *twb = twB + t;
-        asm volatile("" : "+l"(twb));                   // opaque per frame: keeps the 15 loads inside the loop
-        cpx twB1[3];
+        const float4 *twb = twB4 + t;
 #pragma unroll
-        for (int q = 0; q < 3; q++) twB1[q] = ldg_cpx(twb + q * 64);
+        for (int i = 0; i < 16; i++) a[i] = lds_c2(sm, 256 * pb + jj + 16 * i);
+        {
+            const float4 w1 = __ldg(twb), w2 = __ldg(twb + 64), w3 = __ldg(twb + 128);
 #pragma unroll
-        for (int i = 0; i < 16; i++) {
-            float2 v = sm[slot(256 * pb + jj + 16 * i)];
-            a[i].r = v.x; a[i].i = v.y;
-        }
-#pragma unroll
-        for (int g = 0; g < 4; g++) {                   // m=16: points jj+16*(4g+r), twiddle index jj
-            // (lanes with jj == 0 multiply by W^0 = (1,-0) exactly as KissFFT does: no divergent special case)
-            bfly4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3], c_mul(a[4 * g + 1], twB1[0]),
-                  c_mul(a[4 * g + 2], twB1[1]), c_mul(a[4 * g + 3], twB1[2]));
+            for (int g = 0; g < 4; g++)                 // m=16: points jj+16*(4g+r), twiddle index jj
+                bfly4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3], cmul(a[4 * g + 1], w1), cmul(a[4 * g + 2], w2),
+                      cmul(a[4 * g + 3], w3));
         }
 #pragma unroll
         for (int g = 0; g < 4; g++) {                   // m=64: points (jj+16g)+64r, twiddle index jj+16g
-            const cpx w1 = ldg_cpx(twb + (3 + 3 * g) * 64), w2 = ldg_cpx(twb + (4 + 3 * g) * 64), w3 = ldg_cpx(twb + (5 + 3 * g) * 64);
-            bfly4(a[g], a[g + 4], a[g + 8], a[g + 12], c_mul(a[g + 4], w1), c_mul(a[g + 8], w2), c_mul(a[g + 12], w3));
+            const float4 w1 = __ldg(twb + (3 + 3 * g) * 64), w2 = __ldg(twb + (4 + 3 * g) * 64), w3 = __ldg(twb + (5 + 3 * g) * 64);
+            bfly4(a[g], a[g + 4], a[g + 8], a[g + 12], cmul(a[g + 4], w1), cmul(a[g + 8], w2), cmul(a[g + 12], w3));
         }
 #pragma unroll
-        for (int i = 0; i < 16; i++) sm[slot(256 * pb + jj + 16 * i)] = make_float2(a[i].r, a[i].i);
+        for (int i = 0; i < 16; i++) sts_c2(sm, 256 * pb + jj + 16 * i, a[i]);
         __syncthreads();
 
         // ---------------- pass C: stage m=256 + kiss_fftr split + |X|*norm -----------------
+        const float2 half2 = make_float2(0.5f, 0.5f);
         if (FULL) {
 #pragma unroll
             for (int it = 0; it < 4; it++) {
                 const int k = t + 64 * it;
-                float2 v0 = sm[slot(k)], v1 = sm[slot(k + 256)], v2 = sm[slot(k + 512)], v3 = sm[slot(k + 768)];
-                cpx f0{v0.x, v0.y}, f1{v1.x, v1.y}, f2{v2.x, v2.y}, f3{v3.x, v3.y};
-                if (k == 0) bfly4(f0, f1, f2, f3, f1, f2, f3);
-                else bfly4(f0, f1, f2, f3, c_mul(f1, tw[k]), c_mul(f2, tw[2 * k]), c_mul(f3, tw[3 * k]));
-                sm[slot(k)] = make_float2(f0.r, f0.i);
-                sm[slot(k + 256)] = make_float2(f1.r, f1.i);
-                sm[slot(k + 512)] = make_float2(f2.r, f2.i);
-                sm[slot(k + 768)] = make_float2(f3.r, f3.i);
+                c2 f0 = lds_c2(sm, k), f1 = lds_c2(sm, k + 256), f2 = lds_c2(sm, k + 512), f3 = lds_c2(sm, k + 768);
+                bfly4(f0, f1, f2, f3, cmul(f1, __ldg(tw4 + k)), cmul(f2, __ldg(tw4 + 2 * k)), cmul(f3, __ldg(tw4 + 3 * k)));
+                sts_c2(sm, k, f0); sts_c2(sm, k + 256, f1); sts_c2(sm, k + 512, f2); sts_c2(sm, k + 768, f3);
             }
             __syncthreads();
             for (int k = t; k <= 512; k += 64) {        // kiss_fftr.c:90-116
                 if (k == 0) {
-                    float2 d = sm[slot(0)];
-                    float r0 = d.x + d.y, rn = d.x - d.y;
-                    mags[0] = sqrtf(r0 * r0 + 0.0f * 0.0f) * norm_factor;
-                    mags[1024] = sqrtf(rn * rn + 0.0f * 0.0f) * norm_factor;
+                    const c2 d = lds_c2(sm, 0);
+                    const float2 r0 = add2(d.re, d.im), rn = sub2(d.re, d.im);
+                    const float2 z = make_float2(0.0f * 0.0f, 0.0f * 0.0f);
+                    const float2 q0 = padd(mul2(r0, r0), z), qn = padd(mul2(rn, rn), z);
+                    mags[0][0] = sqrtf(q0.x) * norm_factor; mags[1][0] = sqrtf(q0.y) * norm_factor;
+                    mags[0][1024] = sqrtf(qn.x) * norm_factor; mags[1][1024] = sqrtf(qn.y) * norm_factor;
                 } else {
-                    float2 p = sm[slot(k)], q = sm[slot(1024 - k)];
-                    cpx fpk{p.x, p.y}, fpnk{q.x, -q.y};
-                    cpx f1k = c_add(fpk, fpnk), f2k = c_sub(fpk, fpnk);
-                    cpx w = c_mul(f2k, stw[k - 1]);
-                    float re = (f1k.r + w.r) * 0.5f, im = (f1k.i + w.i) * 0.5f;
-                    float re2 = (f1k.r - w.r) * 0.5f, im2 = (w.i - f1k.i) * 0.5f;
+                    const c2 p = lds_c2(sm, k), q = lds_c2(sm, 1024 - k);
+                    // fpnk = conj(q): f1k = p + fpnk, f2k = p - fpnk
+                    const c2 f1k{add2(p.re, q.re), sub2(p.im, q.im)}, f2k{sub2(p.re, q.re), add2(p.im, q.im)};
+                    const c2 w = cmul(f2k, __ldg(stw4 + (k - 1)));
+                    const float2 re = mul2(add2(f1k.re, w.re), half2), im = mul2(add2(f1k.im, w.im), half2);
+                    const float2 re2 = mul2(sub2(f1k.re, w.re), half2), im2 = mul2(sub2(w.im, f1k.im), half2);
                     // k == 512: the reference writes freqdata[512] twice, the second wins
-                    mags[1024 - k] = sqrtf(re2 * re2 + im2 * im2) * norm_factor;
-                    if (k != 512) mags[k] = sqrtf(re * re + im * im) * norm_factor;   // FFT.zig:167-176
+                    const float2 m2 = padd(mul2(re2, re2), mul2(im2, im2));
+                    mags[0][1024 - k] = sqrtf(m2.x) * norm_factor; mags[1][1024 - k] = sqrtf(m2.y) * norm_factor;
+                    if (k != 512) {
+                        const float2 m1 = padd(mul2(re, re), mul2(im, im));      // FFT.zig:167-176
+                        mags[0][k] = sqrtf(m1.x) * norm_factor; mags[1][k] = sqrtf(m1.y) * norm_factor;
+                    }
                 }
             }
         } else {
             // only the bins some band reads (all within 1..255)
             const int lo = bands.lo[0], hi = bands.hi[bands.n_bands - 1];   // host guarantees a covering range
             for (int k = lo + t; k <= hi; k += 64) {
-                cpx x0, y3;
+                c2 x0, y3;
                 {   // output 0 of butterfly k = tmp[k]
-                    float2 v0 = sm[slot(k)], v1 = sm[slot(k + 256)], v2 = sm[slot(k + 512)], v3 = sm[slot(k + 768)];
-                    cpx f0{v0.x, v0.y};
-                    cpx s0 = c_mul(cpx{v1.x, v1.y}, tw[k]), s1 = c_mul(cpx{v2.x, v2.y}, tw[2 * k]),
-                        s2 = c_mul(cpx{v3.x, v3.y}, tw[3 * k]);
-                    f0 = c_add(f0, s1);
-                    x0 = c_add(f0, c_add(s0, s2));
+                    const c2 v0 = lds_c2(sm, k);
+                    const c2 s0 = cmul(lds_c2(sm, k + 256), __ldg(tw4 + k)), s1 = cmul(lds_c2(sm, k + 512), __ldg(tw4 + 2 * k)),
+                             s2 = cmul(lds_c2(sm, k + 768), __ldg(tw4 + 3 * k));
+                    x0 = cadd(cadd(v0, s1), cadd(s0, s2));
                 }
                 {   // output 3 of butterfly 256-k = tmp[1024-k]
                     const int kk = 256 - k;
-                    float2 v0 = sm[slot(kk)], v1 = sm[slot(kk + 256)], v2 = sm[slot(kk + 512)], v3 = sm[slot(kk + 768)];
-                    cpx f0{v0.x, v0.y};
-                    cpx s0 = c_mul(cpx{v1.x, v1.y}, tw[kk]), s1 = c_mul(cpx{v2.x, v2.y}, tw[2 * kk]),
-                        s2 = c_mul(cpx{v3.x, v3.y}, tw[3 * kk]);
-                    cpx s5 = c_sub(f0, s1), s4 = c_sub(s0, s2);
-                    y3.r = s5.r - s4.i;
-                    y3.i = s5.i + s4.r;
+                    const c2 v0 = lds_c2(sm, kk);
+                    const c2 s0 = cmul(lds_c2(sm, kk + 256), __ldg(tw4 + kk)), s1 = cmul(lds_c2(sm, kk + 512), __ldg(tw4 + 2 * kk)),
+                             s2 = cmul(lds_c2(sm, kk + 768), __ldg(tw4 + 3 * kk));
+                    const c2 s5 = csub(v0, s1), s4 = csub(s0, s2);
+                    y3.re = sub2(s5.re, s4.im);
+                    y3.im = add2(s5.im, s4.re);
                 }
-                cpx fpnk{y3.r, -y3.i};
-                cpx f1k = c_add(x0, fpnk), f2k = c_sub(x0, fpnk);
-                cpx w = c_mul(f2k, stw[k - 1]);
-                float re = (f1k.r + w.r) * 0.5f, im = (f1k.i + w.i) * 0.5f;
-                mags[k] = sqrtf(re * re + im * im) * norm_factor;
+                const c2 f1k{add2(x0.re, y3.re), sub2(x0.im, y3.im)}, f2k{sub2(x0.re, y3.re), add2(x0.im, y3.im)};
+                const c2 w = cmul(f2k, __ldg(stw4 + (k - 1)));
+                const float2 re = mul2(add2(f1k.re, w.re), half2), im = mul2(add2(f1k.im, w.im), half2);
+                const float2 m1 = padd(mul2(re, re), mul2(im, im));
+                mags[0][k] = sqrtf(m1.x) * norm_factor; mags[1][k] = sqrtf(m1.y) * norm_factor;
             }
         }
         __syncthreads();
-        // averageVolumeInBand (PipelineFFT.zig:99-112): in-order f32 SUM of bins lo..hi
-        if (t < bands.n_bands) {
-            float v = 0.0f;
-            for (int i = bands.lo[t]; i <= bands.hi[t]; i++) v += mags[i];
-            d_band[((size_t)t * n_rows + r) * band_frame_stride + band_frame_offset + f] = v;
+        // averageVolumeInBand (PipelineFFT.zig:99-112): in-order f32 SUM of bins lo..hi, for frame A and frame B
+        if (t < 2 * bands.n_bands) {
+            const int fr = t >= bands.n_bands, bd = t - fr * bands.n_bands;
+            if (!fr || fidB != fidA) {
+                float v = 0.0f;
+                for (int i = bands.lo[bd]; i <= bands.hi[bd]; i++) v += mags[fr][i];
+                d_band[((size_t)bd * n_rows + (fr ? rB : rA)) * band_frame_stride + band_frame_offset + (fr ? fB : fA)] = v;
+            }
         }
         if (FULL && d_spectra != nullptr) {
-            float *dst = d_spectra + fid * (size_t)kBins;
-            for (int k = t; k < kBins; k += 64) dst[k] = mags[k];
+            float *dstA = d_spectra + fidA * (size_t)kBins;
+            for (int k = t; k < kBins; k += 64) dstA[k] = mags[0][k];
+            if (fidB != fidA) {
+                float *dstB = d_spectra + fidB * (size_t)kBins;
+                for (int k = t; k < kBins; k += 64) dstB[k] = mags[1][k];
+            }
         }
         __syncthreads();
     }
@@ -294,13 +320,22 @@ int stft_launch(const StftTables &tb, const float *d_pcm, size_t n_rows, size_t 
     if (!full && hi - lo > 200) full = true;
     const float *win = d_window_override ? d_window_override : tb.d_window;
     const float norm = d_window_override ? norm_override : tb.norm_factor;
-    const size_t total = n_rows * n_frames;
+    const size_t total = n_rows * n_frames, pairs = (total + 1) / 2;
     const int sms = device_sm_count(device);
-    size_t grid = (size_t)sms * 16;                    // persistent: 16 CTAs of 2 warps per SM (64 registers per thread)
-    if (grid > total) grid = total;
+    // persistent grid: exactly the CTAs that are resident at once (two frames per CTA iteration)
+    static int occ_full = 0, occ_pruned = 0;
+    if (!occ_full) {
+        FVAD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_full, k_stft2048<true>, 64, 0));
+        FVAD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_pruned, k_stft2048<false>, 64, 0));
+        if (occ_full < 1) occ_full = 1;
+        if (occ_pruned < 1) occ_pruned = 1;
+    }
+    size_t grid_full = (size_t)sms * occ_full, grid_pruned = (size_t)sms * occ_pruned;
+    if (grid_full > pairs) grid_full = pairs;
+    if (grid_pruned > pairs) grid_pruned = pairs;
     if (full) {
-        FVAD_LAUNCH(k_stft2048<true>, (unsigned)grid, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win,
-                    tb.d_tw, tb.d_stw, tb.d_twB, tb.twA, norm, b, d_band, band_frame_stride, band_frame_offset, d_spectra);
+        FVAD_LAUNCH(k_stft2048<true>, (unsigned)grid_full, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win,
+                    tb.d_tw4, tb.d_stw4, tb.d_twB4, tb.twA, norm, b, d_band, band_frame_stride, band_frame_offset, d_spectra);
     } else {
         // covering range for the pruned pass: lo[0]..hi[n-1] must span every band
         StftBands bb = b;
@@ -313,11 +348,11 @@ int stft_launch(const StftTables &tb, const float *d_pcm, size_t n_rows, size_t 
         // generally possible, so fall back to FULL unless the given order already satisfies it.
         bool ok = bb.lo[0] == lo && bb.hi[bb.n_bands - 1] == hi;
         if (!ok) {
-            FVAD_LAUNCH(k_stft2048<true>, (unsigned)grid, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win,
-                        tb.d_tw, tb.d_stw, tb.d_twB, tb.twA, norm, b, d_band, band_frame_stride, band_frame_offset, d_spectra);
+            FVAD_LAUNCH(k_stft2048<true>, (unsigned)grid_full, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win,
+                        tb.d_tw4, tb.d_stw4, tb.d_twB4, tb.twA, norm, b, d_band, band_frame_stride, band_frame_offset, d_spectra);
         } else {
-            FVAD_LAUNCH(k_stft2048<false>, (unsigned)grid, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop,
-                        win, tb.d_tw, tb.d_stw, tb.d_twB, tb.twA, norm, bb, d_band, band_frame_stride, band_frame_offset, d_spectra);
+            FVAD_LAUNCH(k_stft2048<false>, (unsigned)grid_pruned, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop,
+                        win, tb.d_tw4, tb.d_stw4, tb.d_twB4, tb.twA, norm, bb, d_band, band_frame_stride, band_frame_offset, d_spectra);
         }
     }
     FVAD_CUDA_TRY(cudaGetLastError());
