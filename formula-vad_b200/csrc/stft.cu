@@ -69,27 +69,24 @@ int stft_tables_get(int device, const StftTables **out) {
         FVAD_CUDA_TRY(cudaSetDevice(device));
         FVAD_CUDA_TRY(cudaMalloc(&t.d_window, sizeof(float) * kFft));
         FVAD_CUDA_TRY(cudaMemcpy(t.d_window, w.data(), sizeof(float) * kFft, cudaMemcpyHostToDevice));
-        FVAD_CUDA_TRY(cudaMalloc(&t.d_twB4, sizeof(float) * 4 * 15 * 64));
-        FVAD_CUDA_TRY(cudaMalloc(&t.d_tw4, sizeof(float) * 4 * kFftC));
-        FVAD_CUDA_TRY(cudaMalloc(&t.d_stw4, sizeof(float) * 4 * kFftC / 2));
-        {   // packed-arithmetic twiddles: every entry is (wr, wr, wi, wi), one 16-byte load feeds both frames
-            auto dup = [](cpx w, float *o) { o[0] = w.r; o[1] = w.r; o[2] = w.i; o[3] = w.i; };
-            std::vector<float> twb(4 * 15 * 64), t4(4 * kFftC), s4(4 * kFftC / 2);
+        FVAD_CUDA_TRY(cudaMalloc(&t.d_twB4, sizeof(float2) * 15 * 64));
+        FVAD_CUDA_TRY(cudaMalloc(&t.d_tw4, sizeof(float2) * kFftC));
+        FVAD_CUDA_TRY(cudaMalloc(&t.d_stw4, sizeof(float2) * kFftC / 2));
+        {
+            std::vector<cpx> twb(15 * 64);
             for (int th = 0; th < 64; th++) {             // pass-B twiddles per thread t = (pb, jj), [15][64]
                 const int jj = th & 15;
-                for (int q = 1; q < 4; q++) dup(tw[jj * 16 * q], &twb[4 * ((q - 1) * 64 + th)]);                            // stage m=16
+                for (int q = 1; q < 4; q++) twb[(q - 1) * 64 + th] = tw[jj * 16 * q];                            // stage m=16
                 for (int g = 0; g < 4; g++)
-                    for (int q = 1; q < 4; q++) dup(tw[(jj + 16 * g) * 4 * q], &twb[4 * ((3 + 3 * g + q - 1) * 64 + th)]);  // stage m=64
+                    for (int q = 1; q < 4; q++) twb[(3 + 3 * g + q - 1) * 64 + th] = tw[(jj + 16 * g) * 4 * q];  // stage m=64
             }
-            for (int i = 0; i < kFftC; i++) dup(tw[i], &t4[4 * i]);
-            for (int i = 0; i < kFftC / 2; i++) dup(stw[i], &s4[4 * i]);
-            FVAD_CUDA_TRY(cudaMemcpy(t.d_twB4, twb.data(), sizeof(float) * twb.size(), cudaMemcpyHostToDevice));
-            FVAD_CUDA_TRY(cudaMemcpy(t.d_tw4, t4.data(), sizeof(float) * t4.size(), cudaMemcpyHostToDevice));
-            FVAD_CUDA_TRY(cudaMemcpy(t.d_stw4, s4.data(), sizeof(float) * s4.size(), cudaMemcpyHostToDevice));
+            FVAD_CUDA_TRY(cudaMemcpy(t.d_twB4, twb.data(), sizeof(cpx) * twb.size(), cudaMemcpyHostToDevice));
+            FVAD_CUDA_TRY(cudaMemcpy(t.d_tw4, tw.data(), sizeof(cpx) * tw.size(), cudaMemcpyHostToDevice));
+            FVAD_CUDA_TRY(cudaMemcpy(t.d_stw4, stw.data(), sizeof(cpx) * stw.size(), cudaMemcpyHostToDevice));
             for (int k = 1; k < 4; k++)
                 for (int q = 1; q < 4; q++) {             // stage m=4, uniform over threads: kernel parameter
                     const cpx w = tw[k * 64 * q];
-                    t.twA.v[(k - 1) * 3 + q - 1] = make_float4(w.r, w.r, w.i, w.i);
+                    t.twA.v[(k - 1) * 3 + q - 1] = make_float2(w.r, w.i);
                 }
         }
         FVAD_CUDA_TRY(cudaSetDevice(prev));
@@ -119,9 +116,10 @@ __device__ __forceinline__ float2 padd(float2 a, float2 b) { return make_float2(
 __device__ __forceinline__ float2 psub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
 __device__ __forceinline__ c2 cadd(c2 a, c2 b) { return c2{add2(a.re, b.re), add2(a.im, b.im)}; }
 __device__ __forceinline__ c2 csub(c2 a, c2 b) { return c2{sub2(a.re, b.re), sub2(a.im, b.im)}; }
-// C_MUL (kiss_fft _kiss_fft_guts.h): m.r = a.r*b.r - a.i*b.i, m.i = a.r*b.i + a.i*b.r.  w = (wr,wr,wi,wi).
-__device__ __forceinline__ c2 cmul(c2 a, float4 w) {
-    const float2 wr = make_float2(w.x, w.y), wi = make_float2(w.z, w.w);
+// C_MUL (kiss_fft _kiss_fft_guts.h): m.r = a.r*b.r - a.i*b.i, m.i = a.r*b.i + a.i*b.r.  The twiddle arrives as
+// 8 bytes and is duplicated in registers: the load/store pipe, not the ALU, is this kernel's scarce resource.
+__device__ __forceinline__ c2 cmul(c2 a, float2 w) {
+    const float2 wr = make_float2(w.x, w.x), wi = make_float2(w.y, w.y);
     return c2{psub(mul2(a.re, wr), mul2(a.im, wi)), padd(mul2(a.re, wi), mul2(a.im, wr))};
 }
 // radix-4 butterfly, forward branch of kf_bfly4 (kiss_fft.c:38-84); s0,s1,s2 are the already twiddled
@@ -150,8 +148,8 @@ __device__ __forceinline__ void sts_c2(float4 *sm, int pos, c2 v) { sm[slot(pos)
 template <bool FULL>
 __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, size_t n_rows, size_t row_stride,
                                                  size_t n_frames, size_t hop, const float *__restrict__ window,
-                                                 const float4 *__restrict__ tw4, const float4 *__restrict__ stw4,
-                                                 const float4 *__restrict__ twB4, const StftTwA twA,
+                                                 const float2 *__restrict__ tw4, const float2 *__restrict__ stw4,
+                                                 const float2 *__restrict__ twB4, const StftTwA twA,
                                                  float norm_factor, StftBands bands, float *__restrict__ d_band,
                                                  size_t band_frame_stride, size_t band_frame_offset,
                                                  float *__restrict__ d_spectra) {
@@ -163,6 +161,9 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
     // pass A block: thread t owns input residue n_low = t; its 16 points land in block blk
     const int blk = ((t & 3) << 4) | (t & 12) | (t >> 4);
     const float2 *win2 = reinterpret_cast<const float2 *>(window);
+    float2 wreg[16];                                            // this thread's 32 window values stay in registers
+#pragma unroll
+    for (int e = 0; e < 16; e++) wreg[e] = win2[64 * e + t];
     const size_t total = n_rows * n_frames, pairs = (total + 1) / 2;
 
     for (size_t pid = blockIdx.x; pid < pairs; pid += gridDim.x) {
@@ -178,7 +179,7 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
         for (int e = 0; e < 16; e++) {
             const float2 vA = srcA[64 * e + t];          // coalesced: 32 lanes x 8 B contiguous
             const float2 vB = srcB[64 * e + t];
-            const float2 w = win2[64 * e + t];
+            const float2 w = wreg[e];
             // input n = t + 64 e = t + 64 (k4 + 4 k5) -> local slot i = 4 k4 + k5
             const int i = 4 * (e & 3) + (e >> 2);
             a[i].re = make_float2(vA.x * w.x, vB.x * w.x);   // FFT.zig:150,155 sample * window[idx]
@@ -197,11 +198,11 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
         __syncthreads();
 
         // ---------------- pass B: stages m=16 and m=64 -------------------------------------
-        const float4 *twb = twB4 + t;
+        const float2 *twb = twB4 + t;
 #pragma unroll
         for (int i = 0; i < 16; i++) a[i] = lds_c2(sm, 256 * pb + jj + 16 * i);
         {
-            const float4 w1 = __ldg(twb), w2 = __ldg(twb + 64), w3 = __ldg(twb + 128);
+            const float2 w1 = __ldg(twb), w2 = __ldg(twb + 64), w3 = __ldg(twb + 128);
 #pragma unroll
             for (int g = 0; g < 4; g++)                 // m=16: points jj+16*(4g+r), twiddle index jj
                 bfly4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3], cmul(a[4 * g + 1], w1), cmul(a[4 * g + 2], w2),
@@ -209,7 +210,7 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
         }
 #pragma unroll
         for (int g = 0; g < 4; g++) {                   // m=64: points (jj+16g)+64r, twiddle index jj+16g
-            const float4 w1 = __ldg(twb + (3 + 3 * g) * 64), w2 = __ldg(twb + (4 + 3 * g) * 64), w3 = __ldg(twb + (5 + 3 * g) * 64);
+            const float2 w1 = __ldg(twb + (3 + 3 * g) * 64), w2 = __ldg(twb + (4 + 3 * g) * 64), w3 = __ldg(twb + (5 + 3 * g) * 64);
             bfly4(a[g], a[g + 4], a[g + 8], a[g + 12], cmul(a[g + 4], w1), cmul(a[g + 8], w2), cmul(a[g + 12], w3));
         }
 #pragma unroll

@@ -17,13 +17,13 @@ struct StftBands {
     int lo[kMaxBands], hi[kMaxBands];   // inclusive bin ranges (freqToBin(min), freqToBin(max))
 };
 
-struct StftTwA { float4 v[9]; };       // stage m=4 twiddles tw[k*64*q], k,q = 1..3, as (wr, wr, wi, wi) (uniform over threads)
+struct StftTwA { float2 v[9]; };       // stage m=4 twiddles tw[k*64*q], k,q = 1..3 (uniform over threads)
 
 struct StftTables {                  // per device
     float *d_window = nullptr;       // periodic Hann, 2048 (PipelineFFT.zig:66-68)
-    float4 *d_twB4 = nullptr;        // [15][64] per-thread twiddles of stages m=16 and m=64, (wr, wr, wi, wi)
-    float4 *d_tw4 = nullptr;         // 1024 twiddles (kiss_fft.c:357-363), packed form
-    float4 *d_stw4 = nullptr;        // 512 super twiddles (kiss_fftr.c:53-59), packed form
+    float2 *d_twB4 = nullptr;        // [15][64] per-thread twiddles of stages m=16 and m=64
+    float2 *d_tw4 = nullptr;         // 1024 twiddles (kiss_fft.c:357-363)
+    float2 *d_stw4 = nullptr;        // 512 super twiddles (kiss_fftr.c:53-59)
     StftTwA twA{};
     float norm_factor = 0;           // (N / sum(w)) / (N/2)  (FFT.zig:94,165)
 };
