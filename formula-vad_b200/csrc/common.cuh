@@ -35,10 +35,12 @@ void profile_begin(const char *name, cudaStream_t stream);
 void profile_end(cudaStream_t stream);
 
 // Every kernel launch of the library goes through this so that fvad_launch_count() is honest.
-#define FVAD_LAUNCH(kernel, grid, block, smem, stream, ...)                 \
+#define FVAD_LAUNCH(kernel, grid, block, smem, stream, ...) \
+    FVAD_LAUNCH_NAMED(#kernel, kernel, grid, block, smem, stream, __VA_ARGS__)
+#define FVAD_LAUNCH_NAMED(name, kernel, grid, block, smem, stream, ...)     \
     do {                                                                    \
         const bool prof__ = ::fvad::g_profile_on.load(std::memory_order_relaxed) != 0; \
-        if (prof__) ::fvad::profile_begin(#kernel, (stream));               \
+        if (prof__) ::fvad::profile_begin(name, (stream));                  \
         kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);         \
         if (prof__) ::fvad::profile_end((stream));                          \
         ::fvad::g_launch_count.fetch_add(1, std::memory_order_relaxed);     \

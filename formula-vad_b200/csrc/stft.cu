@@ -88,6 +88,7 @@ int stft_tables_get(int device, const StftTables **out) {
                     const cpx w = tw[k * 64 * q];
                     t.twA.v[(k - 1) * 3 + q - 1] = make_float2(w.r, w.i);
                 }
+            t.twA.neg_zero = 0x8000000080000000ull;
         }
         FVAD_CUDA_TRY(cudaSetDevice(prev));
         g_tabs[device] = t;
@@ -110,17 +111,25 @@ __device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a
 __device__ __forceinline__ float2 sub2(float2 a, float2 b) { return __fadd2_rn(a, make_float2(-b.x, -b.y)); }   // a + (-b) == a - b
 __device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
 // ptxas (12.9) contracts a packed multiply feeding a packed add/sub into FFMA2 even for mul.rn.f32x2 and with
-// -fmad=false, which would drop a rounding the reference performs.  Sums of products therefore add with SCALAR
-// instructions (never contracted under -fmad=false); tools/check_sass.sh asserts the library has no FFMA2.
-__device__ __forceinline__ float2 padd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 psub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+// -fmad=false, which would drop a rounding the reference performs.  Products that feed a sum are therefore
+// formed as fma(a, b, -0): round(a*b) + (-0) is round(a*b) bit for bit (signed zeros included), it issues in
+// the same slot as FMUL2, and an FFMA2 result cannot be contracted into the following FADD2.  The (-0, -0)
+// addend is a kernel parameter (StftTwA::neg_zero): given it as a literal, ptxas folds the fma back to a
+// multiply and then contracts that.
+// tools/check_sass.sh asserts the FFMA2 count of each kernel variant equals the number written here.
+__device__ __forceinline__ float2 prod2(float2 a, float2 b, unsigned long long nz) {
+    float2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(*reinterpret_cast<unsigned long long *>(&d))
+        : "l"(*reinterpret_cast<const unsigned long long *>(&a)), "l"(*reinterpret_cast<const unsigned long long *>(&b)), "l"(nz));
+    return d;
+}
 __device__ __forceinline__ c2 cadd(c2 a, c2 b) { return c2{add2(a.re, b.re), add2(a.im, b.im)}; }
 __device__ __forceinline__ c2 csub(c2 a, c2 b) { return c2{sub2(a.re, b.re), sub2(a.im, b.im)}; }
 // C_MUL (kiss_fft _kiss_fft_guts.h): m.r = a.r*b.r - a.i*b.i, m.i = a.r*b.i + a.i*b.r.  The twiddle arrives as
 // 8 bytes and is duplicated in registers: the load/store pipe, not the ALU, is this kernel's scarce resource.
-__device__ __forceinline__ c2 cmul(c2 a, float2 w) {
+__device__ __forceinline__ c2 cmul(c2 a, float2 w, unsigned long long nz) {
     const float2 wr = make_float2(w.x, w.x), wi = make_float2(w.y, w.y);
-    return c2{psub(mul2(a.re, wr), mul2(a.im, wi)), padd(mul2(a.re, wi), mul2(a.im, wr))};
+    return c2{sub2(prod2(a.re, wr, nz), prod2(a.im, wi, nz)), add2(prod2(a.re, wi, nz), prod2(a.im, wr, nz))};
 }
 // radix-4 butterfly, forward branch of kf_bfly4 (kiss_fft.c:38-84); s0,s1,s2 are the already twiddled
 // inputs F[m]*tw1, F[2m]*tw2, F[3m]*tw3.
@@ -145,7 +154,41 @@ constexpr int kSlots = 1024 + 64 + 4 + 4;
 __device__ __forceinline__ c2 lds_c2(const float4 *sm, int pos) { const float4 v = sm[slot(pos)]; return c2{make_float2(v.x, v.y), make_float2(v.z, v.w)}; }
 __device__ __forceinline__ void sts_c2(float4 *sm, int pos, c2 v) { sm[slot(pos)] = make_float4(v.re.x, v.re.y, v.im.x, v.im.y); }
 
-template <bool FULL>
+// ---- mbarrier + 1-D bulk copy (TMA engine, no tensor map needed for a contiguous 8 KB frame) ----------
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// one thread: order the CTA's earlier generic-proxy reads of the staging buffer before the async-proxy refill, arm
+// the barrier with the byte count and start both frame copies of pair `pid`
+__device__ __forceinline__ void stage_pair(float *dstA, float *dstB, unsigned long long *bar, const float *pcm, size_t rA,
+                                           size_t fA, size_t n_rows, size_t n_frames, size_t row_stride, size_t hop) {
+    size_t rB = rA, fB = fA + 1;
+    if (fB == n_frames) { fB = 0; rB = rA + 1; }
+    if (rB >= n_rows) { rB = rA; fB = fA; }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(2u * kFft * 4u) : "memory");
+    bulk_g2s(dstA, pcm + rA * row_stride + fA * hop, kFft * 4u, bar);
+    bulk_g2s(dstB, pcm + rB * row_stride + fB * hop, kFft * 4u, bar);
+}
+
+template <bool FULL, bool TMA>
 __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, size_t n_rows, size_t row_stride,
                                                  size_t n_frames, size_t hop, const float *__restrict__ window,
                                                  const float2 *__restrict__ tw4, const float2 *__restrict__ stw4,
@@ -155,7 +198,13 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
                                                  float *__restrict__ d_spectra) {
     __shared__ __align__(16) float4 sm[kSlots];
     __shared__ float mags[2][FULL ? kBins + 3 : 256];
+    // TMA staging: the next pair's two frames (2 x 8 KB, each contiguous in HBM) are fetched by cp.async.bulk into
+    // shared memory while this pair is transformed, so no warp ever waits on an HBM load (with 12 warps per SM the
+    // register file leaves nothing to hide that latency with).
+    __shared__ __align__(128) float stage[TMA ? 2 : 1][TMA ? kFft : 4];
+    __shared__ __align__(8) unsigned long long mbar;
     const int t = threadIdx.x;
+    const unsigned long long nz = twA.neg_zero;
     // pass B: b = 256-block, jj = position inside the 16-stride comb
     const int pb = t >> 4, jj = t & 15;
     // pass A block: thread t owns input residue n_low = t; its 16 points land in block blk
@@ -165,13 +214,37 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
 #pragma unroll
     for (int e = 0; e < 16; e++) wreg[e] = win2[64 * e + t];
     const size_t total = n_rows * n_frames, pairs = (total + 1) / 2;
+    // (row, frame) of this CTA's current frame A, advanced incrementally: a 64-bit division per pair would cost
+    // more issue slots than a whole butterfly stage
+    const size_t step_r = (2 * (size_t)gridDim.x) / n_frames, step_f = (2 * (size_t)gridDim.x) % n_frames;
+    size_t rA = (2 * (size_t)blockIdx.x) / n_frames, fA = (2 * (size_t)blockIdx.x) % n_frames;
+    unsigned phase = 0;
+    if (TMA) {
+        if (t == 0) {
+            mbar_init(&mbar, 1);
+            if (blockIdx.x < pairs) stage_pair(stage[0], stage[1], &mbar, pcm, rA, fA, n_rows, n_frames, row_stride, hop);
+        }
+        __syncthreads();
+    }
 
     for (size_t pid = blockIdx.x; pid < pairs; pid += gridDim.x) {
-        const size_t fidA = 2 * pid, fidB = (fidA + 1 < total) ? fidA + 1 : fidA;     // odd tail: B repeats A, not stored
-        const size_t rA = fidA / n_frames, fA = fidA - rA * n_frames;
-        const size_t rB = fidB / n_frames, fB = fidB - rB * n_frames;
-        const float2 *srcA = reinterpret_cast<const float2 *>(pcm + rA * row_stride + fA * hop);
-        const float2 *srcB = reinterpret_cast<const float2 *>(pcm + rB * row_stride + fB * hop);
+        // frame B = the next frame in (row, frame) order; odd tail: B repeats A and is not stored
+        size_t rB = rA, fB = fA + 1;
+        if (fB == n_frames) { fB = 0; rB = rA + 1; }
+        const bool has_b = rB < n_rows;
+        if (!has_b) { rB = rA; fB = fA; }
+        size_t rN = rA + step_r, fN = fA + step_f;      // frame A of this CTA's next pair
+        if (fN >= n_frames) { fN -= n_frames; rN++; }
+        const float2 *srcA, *srcB;
+        if (TMA) {
+            srcA = reinterpret_cast<const float2 *>(stage[0]);
+            srcB = reinterpret_cast<const float2 *>(stage[1]);
+            mbar_wait(&mbar, phase);
+            phase ^= 1;
+        } else {
+            srcA = reinterpret_cast<const float2 *>(pcm + rA * row_stride + fA * hop);
+            srcB = reinterpret_cast<const float2 *>(pcm + rB * row_stride + fB * hop);
+        }
 
         // ---------------- pass A: load + window, stages m=1 and m=4 in registers ------------
         c2 a[16];
@@ -191,11 +264,13 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
         bfly4(a[0], a[4], a[8], a[12], a[4], a[8], a[12]);   // stage m=4, k=0
 #pragma unroll
         for (int k = 1; k < 4; k++)
-            bfly4(a[k], a[k + 4], a[k + 8], a[k + 12], cmul(a[k + 4], twA.v[(k - 1) * 3]), cmul(a[k + 8], twA.v[(k - 1) * 3 + 1]),
-                  cmul(a[k + 12], twA.v[(k - 1) * 3 + 2]));
+            bfly4(a[k], a[k + 4], a[k + 8], a[k + 12], cmul(a[k + 4], twA.v[(k - 1) * 3], nz), cmul(a[k + 8], twA.v[(k - 1) * 3 + 1], nz),
+                  cmul(a[k + 12], twA.v[(k - 1) * 3 + 2], nz));
 #pragma unroll
         for (int i = 0; i < 16; i++) sts_c2(sm, 16 * blk + i, a[i]);
         __syncthreads();
+        if (TMA && t == 0 && pid + gridDim.x < pairs)   // every thread has consumed the staged frames: refill
+            stage_pair(stage[0], stage[1], &mbar, pcm, rN, fN, n_rows, n_frames, row_stride, hop);
 
         // ---------------- pass B: stages m=16 and m=64 -------------------------------------
         const float2 *twb = twB4 + t;
@@ -205,13 +280,13 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
             const float2 w1 = __ldg(twb), w2 = __ldg(twb + 64), w3 = __ldg(twb + 128);
 #pragma unroll
             for (int g = 0; g < 4; g++)                 // m=16: points jj+16*(4g+r), twiddle index jj
-                bfly4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3], cmul(a[4 * g + 1], w1), cmul(a[4 * g + 2], w2),
-                      cmul(a[4 * g + 3], w3));
+                bfly4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3], cmul(a[4 * g + 1], w1, nz), cmul(a[4 * g + 2], w2, nz),
+                      cmul(a[4 * g + 3], w3, nz));
         }
 #pragma unroll
         for (int g = 0; g < 4; g++) {                   // m=64: points (jj+16g)+64r, twiddle index jj+16g
             const float2 w1 = __ldg(twb + (3 + 3 * g) * 64), w2 = __ldg(twb + (4 + 3 * g) * 64), w3 = __ldg(twb + (5 + 3 * g) * 64);
-            bfly4(a[g], a[g + 4], a[g + 8], a[g + 12], cmul(a[g + 4], w1), cmul(a[g + 8], w2), cmul(a[g + 12], w3));
+            bfly4(a[g], a[g + 4], a[g + 8], a[g + 12], cmul(a[g + 4], w1, nz), cmul(a[g + 8], w2, nz), cmul(a[g + 12], w3, nz));
         }
 #pragma unroll
         for (int i = 0; i < 16; i++) sts_c2(sm, 256 * pb + jj + 16 * i, a[i]);
@@ -224,7 +299,7 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
             for (int it = 0; it < 4; it++) {
                 const int k = t + 64 * it;
                 c2 f0 = lds_c2(sm, k), f1 = lds_c2(sm, k + 256), f2 = lds_c2(sm, k + 512), f3 = lds_c2(sm, k + 768);
-                bfly4(f0, f1, f2, f3, cmul(f1, __ldg(tw4 + k)), cmul(f2, __ldg(tw4 + 2 * k)), cmul(f3, __ldg(tw4 + 3 * k)));
+                bfly4(f0, f1, f2, f3, cmul(f1, __ldg(tw4 + k), nz), cmul(f2, __ldg(tw4 + 2 * k), nz), cmul(f3, __ldg(tw4 + 3 * k), nz));
                 sts_c2(sm, k, f0); sts_c2(sm, k + 256, f1); sts_c2(sm, k + 512, f2); sts_c2(sm, k + 768, f3);
             }
             __syncthreads();
@@ -233,21 +308,21 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
                     const c2 d = lds_c2(sm, 0);
                     const float2 r0 = add2(d.re, d.im), rn = sub2(d.re, d.im);
                     const float2 z = make_float2(0.0f * 0.0f, 0.0f * 0.0f);
-                    const float2 q0 = padd(mul2(r0, r0), z), qn = padd(mul2(rn, rn), z);
+                    const float2 q0 = add2(prod2(r0, r0, nz), z), qn = add2(prod2(rn, rn, nz), z);
                     mags[0][0] = sqrtf(q0.x) * norm_factor; mags[1][0] = sqrtf(q0.y) * norm_factor;
                     mags[0][1024] = sqrtf(qn.x) * norm_factor; mags[1][1024] = sqrtf(qn.y) * norm_factor;
                 } else {
                     const c2 p = lds_c2(sm, k), q = lds_c2(sm, 1024 - k);
                     // fpnk = conj(q): f1k = p + fpnk, f2k = p - fpnk
                     const c2 f1k{add2(p.re, q.re), sub2(p.im, q.im)}, f2k{sub2(p.re, q.re), add2(p.im, q.im)};
-                    const c2 w = cmul(f2k, __ldg(stw4 + (k - 1)));
+                    const c2 w = cmul(f2k, __ldg(stw4 + (k - 1)), nz);
                     const float2 re = mul2(add2(f1k.re, w.re), half2), im = mul2(add2(f1k.im, w.im), half2);
                     const float2 re2 = mul2(sub2(f1k.re, w.re), half2), im2 = mul2(sub2(w.im, f1k.im), half2);
                     // k == 512: the reference writes freqdata[512] twice, the second wins
-                    const float2 m2 = padd(mul2(re2, re2), mul2(im2, im2));
+                    const float2 m2 = add2(prod2(re2, re2, nz), prod2(im2, im2, nz));
                     mags[0][1024 - k] = sqrtf(m2.x) * norm_factor; mags[1][1024 - k] = sqrtf(m2.y) * norm_factor;
                     if (k != 512) {
-                        const float2 m1 = padd(mul2(re, re), mul2(im, im));      // FFT.zig:167-176
+                        const float2 m1 = add2(prod2(re, re, nz), prod2(im, im, nz));      // FFT.zig:167-176
                         mags[0][k] = sqrtf(m1.x) * norm_factor; mags[1][k] = sqrtf(m1.y) * norm_factor;
                     }
                 }
@@ -259,23 +334,23 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
                 c2 x0, y3;
                 {   // output 0 of butterfly k = tmp[k]
                     const c2 v0 = lds_c2(sm, k);
-                    const c2 s0 = cmul(lds_c2(sm, k + 256), __ldg(tw4 + k)), s1 = cmul(lds_c2(sm, k + 512), __ldg(tw4 + 2 * k)),
-                             s2 = cmul(lds_c2(sm, k + 768), __ldg(tw4 + 3 * k));
+                    const c2 s0 = cmul(lds_c2(sm, k + 256), __ldg(tw4 + k), nz), s1 = cmul(lds_c2(sm, k + 512), __ldg(tw4 + 2 * k), nz),
+                             s2 = cmul(lds_c2(sm, k + 768), __ldg(tw4 + 3 * k), nz);
                     x0 = cadd(cadd(v0, s1), cadd(s0, s2));
                 }
                 {   // output 3 of butterfly 256-k = tmp[1024-k]
                     const int kk = 256 - k;
                     const c2 v0 = lds_c2(sm, kk);
-                    const c2 s0 = cmul(lds_c2(sm, kk + 256), __ldg(tw4 + kk)), s1 = cmul(lds_c2(sm, kk + 512), __ldg(tw4 + 2 * kk)),
-                             s2 = cmul(lds_c2(sm, kk + 768), __ldg(tw4 + 3 * kk));
+                    const c2 s0 = cmul(lds_c2(sm, kk + 256), __ldg(tw4 + kk), nz), s1 = cmul(lds_c2(sm, kk + 512), __ldg(tw4 + 2 * kk), nz),
+                             s2 = cmul(lds_c2(sm, kk + 768), __ldg(tw4 + 3 * kk), nz);
                     const c2 s5 = csub(v0, s1), s4 = csub(s0, s2);
                     y3.re = sub2(s5.re, s4.im);
                     y3.im = add2(s5.im, s4.re);
                 }
                 const c2 f1k{add2(x0.re, y3.re), sub2(x0.im, y3.im)}, f2k{sub2(x0.re, y3.re), add2(x0.im, y3.im)};
-                const c2 w = cmul(f2k, __ldg(stw4 + (k - 1)));
+                const c2 w = cmul(f2k, __ldg(stw4 + (k - 1)), nz);
                 const float2 re = mul2(add2(f1k.re, w.re), half2), im = mul2(add2(f1k.im, w.im), half2);
-                const float2 m1 = padd(mul2(re, re), mul2(im, im));
+                const float2 m1 = add2(prod2(re, re, nz), prod2(im, im, nz));
                 mags[0][k] = sqrtf(m1.x) * norm_factor; mags[1][k] = sqrtf(m1.y) * norm_factor;
             }
         }
@@ -283,23 +358,38 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
         // averageVolumeInBand (PipelineFFT.zig:99-112): in-order f32 SUM of bins lo..hi, for frame A and frame B
         if (t < 2 * bands.n_bands) {
             const int fr = t >= bands.n_bands, bd = t - fr * bands.n_bands;
-            if (!fr || fidB != fidA) {
+            if (!fr || has_b) {
                 float v = 0.0f;
                 for (int i = bands.lo[bd]; i <= bands.hi[bd]; i++) v += mags[fr][i];
                 d_band[((size_t)bd * n_rows + (fr ? rB : rA)) * band_frame_stride + band_frame_offset + (fr ? fB : fA)] = v;
             }
         }
         if (FULL && d_spectra != nullptr) {
-            float *dstA = d_spectra + fidA * (size_t)kBins;
+            float *dstA = d_spectra + (rA * n_frames + fA) * (size_t)kBins;
             for (int k = t; k < kBins; k += 64) dstA[k] = mags[0][k];
-            if (fidB != fidA) {
-                float *dstB = d_spectra + fidB * (size_t)kBins;
+            if (has_b) {
+                float *dstB = d_spectra + (rB * n_frames + fB) * (size_t)kBins;
                 for (int k = t; k < kBins; k += 64) dstB[k] = mags[1][k];
             }
         }
         __syncthreads();
+        rA = rN; fA = fN;
     }
 }
+
+namespace {
+struct StftGrid { int occ[2][2] = {{0, 0}, {0, 0}}; int sms = 0; bool ready = false; };
+StftGrid g_grid[64];
+
+template <bool FULL, bool TMA>
+int stft_occupancy(int *occ) {
+    // the staged variant needs the whole shared-memory carve-out to keep six CTAs (12 warps) per SM
+    FVAD_CUDA_TRY(cudaFuncSetAttribute(k_stft2048<FULL, TMA>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    FVAD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_stft2048<FULL, TMA>, 64, 0));
+    if (*occ < 1) *occ = 1;
+    return FVAD_OK;
+}
+}  // namespace
 
 int stft_launch(const StftTables &tb, const float *d_pcm, size_t n_rows, size_t row_stride, size_t n_frames,
                 size_t hop, const StftBands &bands, float *d_band, size_t band_frame_stride,
@@ -308,54 +398,40 @@ int stft_launch(const StftTables &tb, const float *d_pcm, size_t n_rows, size_t 
     if (n_rows == 0 || n_frames == 0) return FVAD_OK;
     if ((reinterpret_cast<uintptr_t>(d_pcm) & 7) || (row_stride & 1) || (hop & 1))
         return set_error(FVAD_EINVALID_ARGUMENT, "stft: pcm must be 8-byte aligned with even strides");
-    bool full = d_spectra != nullptr;
-    StftBands b = bands;
-    // the pruned kernel needs every band inside 1..255 and reads the covering range lo[0]..hi[last]
-    int lo = 1 << 30, hi = -1;
-    for (int i = 0; i < b.n_bands; i++) {
-        if (b.lo[i] < 1 || b.hi[i] > 255 || b.hi[i] < b.lo[i]) full = true;
-        lo = b.lo[i] < lo ? b.lo[i] : lo;
-        hi = b.hi[i] > hi ? b.hi[i] : hi;
-    }
-    if (b.n_bands == 0) full = true;
-    if (!full && hi - lo > 200) full = true;
+    // cp.async.bulk wants 16-byte aligned sources; anything else takes the plain-load variant
+    bool tma = !(reinterpret_cast<uintptr_t>(d_pcm) & 15) && !(row_stride & 3) && !(hop & 3);
+    // The pruned variant computes only the bins lo[0]..hi[last]; it needs every band inside 1..255 and the first /
+    // last band to carry the extremes (true for the pipeline's single speech band).  Otherwise: all 1025 bins.
+    bool full = d_spectra != nullptr || bands.n_bands == 0;
+    for (int i = 0; i < bands.n_bands && !full; i++)
+        full = bands.lo[i] < 1 || bands.hi[i] > 255 || bands.hi[i] < bands.lo[i] || bands.lo[i] < bands.lo[0] ||
+               bands.hi[i] > bands.hi[bands.n_bands - 1];
+    if (!full && bands.hi[bands.n_bands - 1] - bands.lo[0] > 200) full = true;
     const float *win = d_window_override ? d_window_override : tb.d_window;
     const float norm = d_window_override ? norm_override : tb.norm_factor;
     const size_t total = n_rows * n_frames, pairs = (total + 1) / 2;
-    const int sms = device_sm_count(device);
-    // persistent grid: exactly the CTAs that are resident at once (two frames per CTA iteration)
-    static int occ_full = 0, occ_pruned = 0;
-    if (!occ_full) {
-        FVAD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_full, k_stft2048<true>, 64, 0));
-        FVAD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_pruned, k_stft2048<false>, 64, 0));
-        if (occ_full < 1) occ_full = 1;
-        if (occ_pruned < 1) occ_pruned = 1;
-    }
-    size_t grid_full = (size_t)sms * occ_full, grid_pruned = (size_t)sms * occ_pruned;
-    if (grid_full > pairs) grid_full = pairs;
-    if (grid_pruned > pairs) grid_pruned = pairs;
-    if (full) {
-        FVAD_LAUNCH(k_stft2048<true>, (unsigned)grid_full, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win,
-                    tb.d_tw4, tb.d_stw4, tb.d_twB4, tb.twA, norm, b, d_band, band_frame_stride, band_frame_offset, d_spectra);
-    } else {
-        // covering range for the pruned pass: lo[0]..hi[n-1] must span every band
-        StftBands bb = b;
-        // keep bands as given but make element 0 / last carry the extremes for the kernel's range read
-        int imin = 0, imax = 0;
-        for (int i = 0; i < b.n_bands; i++) { if (b.lo[i] < b.lo[imin]) imin = i; if (b.hi[i] > b.hi[imax]) imax = i; }
-        (void)imin; (void)imax;
-        // simplest: pass the range through a dedicated pair by reordering is unnecessary when n_bands==1;
-        // for several bands sort so that lo[0] is the smallest lo and hi[last] the largest hi is not
-        // generally possible, so fall back to FULL unless the given order already satisfies it.
-        bool ok = bb.lo[0] == lo && bb.hi[bb.n_bands - 1] == hi;
-        if (!ok) {
-            FVAD_LAUNCH(k_stft2048<true>, (unsigned)grid_full, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win,
-                        tb.d_tw4, tb.d_stw4, tb.d_twB4, tb.twA, norm, b, d_band, band_frame_stride, band_frame_offset, d_spectra);
-        } else {
-            FVAD_LAUNCH(k_stft2048<false>, (unsigned)grid_pruned, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop,
-                        win, tb.d_tw4, tb.d_stw4, tb.d_twB4, tb.twA, norm, bb, d_band, band_frame_stride, band_frame_offset, d_spectra);
+    if (device < 0 || device >= 64) return set_error(FVAD_EINVALID_ARGUMENT, "stft: bad device %d", device);
+    StftGrid &g = g_grid[device];
+    {
+        std::lock_guard<std::mutex> lock(g_tab_mu);
+        if (!g.ready) {
+            FVAD_CUDA_TRY(cudaDeviceGetAttribute(&g.sms, cudaDevAttrMultiProcessorCount, device));
+            int rc;
+            if ((rc = stft_occupancy<false, false>(&g.occ[0][0])) != FVAD_OK) return rc;
+            if ((rc = stft_occupancy<false, true>(&g.occ[0][1])) != FVAD_OK) return rc;
+            if ((rc = stft_occupancy<true, false>(&g.occ[1][0])) != FVAD_OK) return rc;
+            g.ready = true;
         }
     }
+    if (full) tma = false;                    // write-dominated; the staging buffer would cost it a resident CTA
+    size_t grid = (size_t)g.sms * g.occ[full][tma];
+    if (grid > pairs) grid = pairs;
+#define FVAD_STFT_GO(F, T)                                                                                              \
+    FVAD_LAUNCH_NAMED("k_stft2048<" #F ">", (k_stft2048<F, T>), (unsigned)grid, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win, tb.d_tw4, \
+                tb.d_stw4, tb.d_twB4, tb.twA, norm, bands, d_band, band_frame_stride, band_frame_offset, d_spectra)
+    if (full) FVAD_STFT_GO(true, false);
+    else      { if (tma) FVAD_STFT_GO(false, true); else FVAD_STFT_GO(false, false); }
+#undef FVAD_STFT_GO
     FVAD_CUDA_TRY(cudaGetLastError());
     return FVAD_OK;
 }

@@ -17,7 +17,10 @@ struct StftBands {
     int lo[kMaxBands], hi[kMaxBands];   // inclusive bin ranges (freqToBin(min), freqToBin(max))
 };
 
-struct StftTwA { float2 v[9]; };       // stage m=4 twiddles tw[k*64*q], k,q = 1..3 (uniform over threads)
+struct StftTwA {
+    float2 v[9];                        // stage m=4 twiddles tw[k*64*q], k,q = 1..3 (uniform over threads)
+    unsigned long long neg_zero;        // the pair (-0.0f, -0.0f): addend of the product-forming fma (see prod2)
+};
 
 struct StftTables {                  // per device
     float *d_window = nullptr;       // periodic Hann, 2048 (PipelineFFT.zig:66-68)
