@@ -140,7 +140,8 @@ extern "C" void fvad_batch_destroy(fvad_batch *b) {
         cudaFree(b->d_vad_stft); cudaFree(b->d_spectra); cudaFree(b->d_params); cudaFree(b->d_states);
         cudaFree(b->d_rings); cudaFree(b->d_segs); cudaFree(b->d_seg_count); cudaFree(b->d_events);
         cudaFree(b->d_event_count); cudaFree(b->d_trace);
-        for (cudaStream_t st : {b->sA, b->sB, b->sC, b->stream}) if (st) cudaStreamDestroy(st);
+        for (cudaStream_t st : {b->sA, b->sB, b->sC}) if (st && st != b->stream) cudaStreamDestroy(st);
+        if (b->stream) cudaStreamDestroy(b->stream);
     }
     delete b;
 }
@@ -179,10 +180,14 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
 
     int rc = FVAD_OK;
     auto fail = [&](int code) { fvad_batch_destroy(b); return code; };
-    if (cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&b->sA, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&b->sB, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&b->sC, cudaStreamNonBlocking) != cudaSuccess)
+    if (cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess)
+        return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
+    if (getenv("FVAD_SERIAL_STAGES")) {
+        // measurement aid: all four stages on one stream, so the per-kernel event times are free of overlap
+        b->sA = b->sB = b->sC = b->stream;
+    } else if (cudaStreamCreateWithFlags(&b->sA, cudaStreamNonBlocking) != cudaSuccess ||
+               cudaStreamCreateWithFlags(&b->sB, cudaStreamNonBlocking) != cudaSuccess ||
+               cudaStreamCreateWithFlags(&b->sC, cudaStreamNonBlocking) != cudaSuccess)
         return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
     {
         const char *es = getenv("FVAD_SLOTS");

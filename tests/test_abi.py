@@ -97,3 +97,17 @@ def test_host_side_tables_and_synth(fv, port):
     b = fv.synth_host(0xF1AD5EED00000000, 5, 2400, 2400)
     assert np.array_equal(a[2400:], b) and np.abs(a).max() <= 1.0      # pure function of (seed, stream, n)
     assert not np.array_equal(a, fv.synth_host(0xF1AD5EED00000000, 6, 0, 4800))
+
+
+def test_sass_exactness_guard():
+    """The built library's STFT kernels use packed f32x2 arithmetic + TMA bulk copies and contain no contracted
+    multiply-add (every FFMA2 is fma(a, b, -0), see stft.cu prod2): tools/check_sass.sh inspects the SASS."""
+    import os
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if shutil.which("cuobjdump") is None and not os.path.exists("/usr/local/cuda/bin/cuobjdump"):
+        pytest.skip("cuobjdump not available")
+    env = dict(os.environ, PATH=os.environ.get("PATH", "") + ":/usr/local/cuda/bin")
+    r = subprocess.run(["bash", os.path.join(root, "tools", "check_sass.sh")], capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
