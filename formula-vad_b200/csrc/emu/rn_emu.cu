@@ -96,7 +96,8 @@ int rn_emu_tile(void *h, const float *in, size_t in_stride, int Tn, float *out, 
     for (int j = 0; j < nz; j++) {
         const int q = nzlist[j];
         memcpy(e.rnn_scr.data() + kRv_feat, &feat[(size_t)q * kNFeat], sizeof(float) * kNFeat);
-        rnn_frame_cta(e.ht.weights.data(), e.ht.bias.data(), t.tansig, e.rnn_scr.data(), &gains[(size_t)q * kNB], &vadv[q]);
+        RnnOut<1> out; out.gains[0] = &gains[(size_t)q * kNB]; out.vad[0] = &vadv[q];
+        rnn_frame_cta<1>(e.ht.weights2.data(), e.ht.bias.data(), t.tansig, e.rnn_scr.data(), 1u, out);
     }
     // k_rn_gain_scan (denoise.c:478-482)
     std::vector<float> gsm((size_t)Q * kNB, 0.f);

@@ -710,10 +710,14 @@ RN_HD float sigmoid_approx(const float *table, float x) {
 
 
 // ------------------------------------------------------------------------------------------
-// compute_rnn (rnn.c:160-178) for one state, executed by a CTA of kRnnThreads threads.
-// Weights: per layer one matrix W[j][col] (bf16 bit patterns: every int8 weight is exact in bf16),
-// j running over the layer's inputs and then, for a GRU, its recurrent inputs -- the order in which
-// compute_gru accumulates (rnn.c:122-127).  Columns: z | r | h gates.
+// compute_rnn (rnn.c:160-178), executed by a CTA of kRnnThreads threads for R states at once.
+// Weights: per layer one matrix W[j][col] (bf16 bit patterns: every int8 weight is exact in bf16), j running
+// over the layer's inputs and then, for a GRU, its recurrent inputs -- the order in which compute_gru accumulates
+// (rnn.c:122-127).  Columns: z | r | h gates.  Rows are stored in PAIRS: word W2[j/2][col] = W[j][col] | W[j+1][col]<<16
+// (every chain length is even), so one 32-bit load feeds two steps of the chain.
+// A thread owns one column and runs the chains of all R states interleaved: the weight fetch and unpack are shared
+// by the R states, and R independent FADD chains fill each other's latency slots.  Every chain is still evaluated
+// in the reference's order on one thread.
 // ------------------------------------------------------------------------------------------
 #if defined(__CUDA_ARCH__)
 #define RN_CTA_PHASE { const int tid = threadIdx.x;
@@ -724,6 +728,7 @@ RN_HD float sigmoid_approx(const float *table, float x) {
 #endif
 
 constexpr int kRnnThreads = 288;
+constexpr int kRnnMaxR = 4;
 struct RnnLayer { int J, M, cols, w_off, b_off; };        // J = chain length, M = inputs before the recurrent part
 constexpr int kL_in = 0, kL_vad = 1, kL_vout = 2, kL_noise = 3, kL_den = 4, kL_out = 5;
 __host__ __device__ constexpr RnnLayer rnn_layer(int l) {
@@ -735,94 +740,196 @@ __host__ __device__ constexpr RnnLayer rnn_layer(int l) {
          :          RnnLayer{96, 96, 22, 84840, 529};
 }
 constexpr int kRnnWeights = 86952, kRnnBiases = 551;
-// scratch floats of the CTA, after the weights: vectors
+// vectors of ONE state (floats); state r of a CTA lives at scr + r * kRv_end
 constexpr int kRv_feat = 0, kRv_v1 = 48, kRv_v3 = 96, kRv_v4 = 240, kRv_zr = 456, kRv_hp = 648, kRv_hn = 744, kRv_end = 840;
 
-RN_HD float bf16_to_f32(unsigned short b) {
+RN_HD float bits_to_f32(unsigned u) {
 #if defined(__CUDA_ARCH__)
-    return __uint_as_float(((unsigned)b) << 16);
+    return __uint_as_float(u);
 #else
-    union { unsigned u; float f; } c; c.u = ((unsigned)b) << 16; return c.f;
+    union { unsigned u; float f; } c; c.u = u; return c.f;
 #endif
 }
+struct RnnF2 { float x, y; };                              // two consecutive vector elements (8-byte aligned: j is even)
 
-// bias + sum_{j in [j0,j1)} W[j][col]*v[j]   continuing from `sum`
-RN_HD float rnn_chain(const unsigned short *W, int cols, int col, const float *v, int j0, int j1, float sum) {
-    for (int j = j0; j < j1; j++) sum += bf16_to_f32(W[j * cols + col]) * v[j];
-    return sum;
+// sum[r] += W[j][col]*v_r[j] for j in [j0,j1), in order, for the R states.  j0 is even and j1-j0 a multiple of 6 (true
+// for every layer): the chain is walked in blocks of three row pairs, and the next block's weight words and vector
+// elements are fetched before the current block is accumulated, so no shared-memory latency sits on the FADD chain.
+constexpr int kRnnP = 3;
+template <int R> struct RnnBlk { RnnF2 x[R][kRnnP]; };
+struct RnnWBlk { unsigned u[kRnnP]; };
+RN_HD void rnn_w_load(RnnWBlk &b, const unsigned *W2, int cols, int col, int j) {
+#pragma unroll
+    for (int p = 0; p < kRnnP; p++) b.u[p] = W2[((j >> 1) + p) * cols + col];
 }
-// recurrent part of the candidate gate: sum += (W[j][col]*state[j-M])*r[j-M]  (rnn.c:147)
-RN_HD float rnn_chain_r(const unsigned short *W, int cols, int col, const float *v, const float *r, int M, int J, float sum) {
-    for (int j = M; j < J; j++) sum += bf16_to_f32(W[j * cols + col]) * v[j] * r[j - M];
-    return sum;
+template <int R>
+RN_HD void rnn_blk_load(RnnBlk<R> &b, const float *v, int j) {
+#pragma unroll
+    for (int p = 0; p < kRnnP; p++) {
+#pragma unroll
+        for (int r = 0; r < R; r++) b.x[r][p] = *reinterpret_cast<const RnnF2 *>(v + r * kRv_end + j + 2 * p);
+    }
+}
+template <int R>
+RN_HD void rnn_chain(const unsigned *W2, int cols, int col, const float *v, int j0, int j1, float (&sum)[R]) {
+    RnnBlk<R> cur, nxt;
+    RnnWBlk wc, wn;
+    rnn_w_load(wc, W2, cols, col, j0);
+    rnn_blk_load<R>(cur, v, j0);
+    for (int j = j0; j < j1; j += 2 * kRnnP) {
+        const int jn = j + 2 * kRnnP < j1 ? j + 2 * kRnnP : j;      // last block: a harmless re-fetch instead of a branch
+        rnn_w_load(wn, W2, cols, col, jn);
+        rnn_blk_load<R>(nxt, v, jn);
+#pragma unroll
+        for (int p = 0; p < kRnnP; p++) {
+            const float w0 = bits_to_f32(wc.u[p] << 16), w1 = bits_to_f32(wc.u[p] & 0xffff0000u);
+#pragma unroll
+            for (int r = 0; r < R; r++) {
+                sum[r] += w0 * cur.x[r][p].x;
+                sum[r] += w1 * cur.x[r][p].y;
+            }
+        }
+        cur = nxt; wc = wn;
+    }
+}
+// recurrent part of the candidate gate: sum += (W[j][col]*state[j-M])*r[j-M]  (rnn.c:147); same blocking
+template <int R>
+RN_HD void rnn_chain_r(const unsigned *W2, int cols, int col, const float *v, const float *rg, int M, int J, float (&sum)[R]) {
+    RnnBlk<R> cur, nxt, gcur, gnxt;                         // g*: the reset-gate values
+    RnnWBlk wc, wn;
+    rnn_w_load(wc, W2, cols, col, M);
+    rnn_blk_load<R>(cur, v, M);
+    rnn_blk_load<R>(gcur, rg - M, M);
+    for (int j = M; j < J; j += 2 * kRnnP) {
+        const int jn = j + 2 * kRnnP < J ? j + 2 * kRnnP : j;
+        rnn_w_load(wn, W2, cols, col, jn);
+        rnn_blk_load<R>(nxt, v, jn);
+        rnn_blk_load<R>(gnxt, rg - M, jn);
+#pragma unroll
+        for (int p = 0; p < kRnnP; p++) {
+            const float w0 = bits_to_f32(wc.u[p] << 16), w1 = bits_to_f32(wc.u[p] & 0xffff0000u);
+#pragma unroll
+            for (int r = 0; r < R; r++) {
+                sum[r] += w0 * cur.x[r][p].x * gcur.x[r][p].x;
+                sum[r] += w1 * cur.x[r][p].y * gcur.x[r][p].y;
+            }
+        }
+        cur = nxt; gcur = gnxt; wc = wn;
+    }
 }
 
 constexpr float kWScale = 1.f / 256;
 
-// One GRU layer: v = [inputs(M) | state(N)], zr/hp/hn scratch.  Three CTA phases.
-RN_HD void rnn_gru_cta(const unsigned short *W, const float *bias, const float *tansig, int layer, float *v,
-                       float *zr, float *hp, float *hn) {
+// One GRU layer: v = [inputs(M) | state(N)], zr/hp/hn scratch (all of state 0; state r at + r*kRv_end).  Two CTA phases.
+template <int R>
+RN_HD void rnn_gru_cta(const unsigned *W2, const float *bias, const float *tansig, int layer, float *v, float *zr, float *hp,
+                       float *hn) {
     const RnnLayer L = rnn_layer(layer);
     const int N = L.cols / 3;
-    const unsigned short *Wl = W + L.w_off;
+    const unsigned *Wl = W2 + L.w_off / 2;
     const float *bl = bias + L.b_off;
     RN_CTA_PHASE
-        if (tid < 2 * N) {                                   // update and reset gates (rnn.c:119-139)
-            const float s = rnn_chain(Wl, L.cols, tid, v, 0, L.J, bl[tid]);
-            zr[tid] = sigmoid_approx(tansig, kWScale * s);
-        } else if (tid < 3 * N) {                            // candidate: input part (rnn.c:143-145)
-            hp[tid - 2 * N] = rnn_chain(Wl, L.cols, tid, v, 0, L.M, bl[tid]);
+        if (tid < 3 * N) {
+            float s[R];
+#pragma unroll
+            for (int r = 0; r < R; r++) s[r] = bl[tid];
+            if (tid < 2 * N) {                               // update and reset gates (rnn.c:119-139)
+                rnn_chain<R>(Wl, L.cols, tid, v, 0, L.J, s);
+#pragma unroll
+                for (int r = 0; r < R; r++) zr[r * kRv_end + tid] = sigmoid_approx(tansig, kWScale * s[r]);
+            } else {                                         // candidate: input part (rnn.c:143-145)
+                rnn_chain<R>(Wl, L.cols, tid, v, 0, L.M, s);
+#pragma unroll
+                for (int r = 0; r < R; r++) hp[r * kRv_end + tid - 2 * N] = s[r];
+            }
         }
     RN_CTA_END
     RN_CTA_PHASE
         if (tid < N) {                                       // candidate: recurrent part, ReLU, blend (rnn.c:146-152)
-            float s = rnn_chain_r(Wl, L.cols, 2 * N + tid, v, zr + N, L.M, L.J, hp[tid]);
-            s = kWScale * s;
-            s = s < 0 ? 0 : s;
-            const float z = zr[tid];
-            hn[tid] = z * v[L.M + tid] + (1 - z) * s;
+            float s[R];
+#pragma unroll
+            for (int r = 0; r < R; r++) s[r] = hp[r * kRv_end + tid];
+            rnn_chain_r<R>(Wl, L.cols, 2 * N + tid, v, zr + N, L.M, L.J, s);
+#pragma unroll
+            for (int r = 0; r < R; r++) {
+                float x = kWScale * s[r];
+                x = x < 0 ? 0 : x;
+                const float z = zr[r * kRv_end + tid];
+                hn[r * kRv_end + tid] = z * v[r * kRv_end + L.M + tid] + (1 - z) * x;
+            }
         }
     RN_CTA_END
 }
 
-// Whole network for one frame.  scr = vectors (kRv_* offsets); feat already at scr[kRv_feat..+42).
-RN_HD void rnn_frame_cta(const unsigned short *W, const float *bias, const float *tansig, float *scr, float *gains_out,
-                         float *vad_out) {
+template <int R> struct RnnOut { float *gains[R]; float *vad[R]; };
+
+// Whole network for one frame of each of the R states.  scr = vectors (kRv_* offsets) of state 0, state r at
+// + r*kRv_end; the frame's features are already at kRv_feat..+42.  Bit r of `act` says state r has a frame this
+// round: an inactive state is computed on stale inputs (harmless) but neither its GRU states nor any output is written.
+template <int R>
+RN_HD void rnn_frame_cta(const unsigned *W2, const float *bias, const float *tansig, float *scr, unsigned act, const RnnOut<R> &out) {
     float *feat = scr + kRv_feat, *v1 = scr + kRv_v1, *v3 = scr + kRv_v3, *v4 = scr + kRv_v4;
     float *zr = scr + kRv_zr, *hp = scr + kRv_hp, *hn = scr + kRv_hn;
     RN_CTA_PHASE
         if (tid < 24) {                                      // input_dense, tanh (rnn.c:79-107)
             const RnnLayer L = rnn_layer(kL_in);
-            const float s = rnn_chain(W + L.w_off, L.cols, tid, feat, 0, L.J, bias[L.b_off + tid]);
-            v1[tid] = tansig_approx(tansig, kWScale * s);
+            float s[R];
+#pragma unroll
+            for (int r = 0; r < R; r++) s[r] = bias[L.b_off + tid];
+            rnn_chain<R>(W2 + L.w_off / 2, L.cols, tid, feat, 0, L.J, s);
+#pragma unroll
+            for (int r = 0; r < R; r++) v1[r * kRv_end + tid] = tansig_approx(tansig, kWScale * s[r]);
         }
     RN_CTA_END
-    rnn_gru_cta(W, bias, tansig, kL_vad, v1, zr, hp, hn);
+    rnn_gru_cta<R>(W2, bias, tansig, kL_vad, v1, zr, hp, hn);
     RN_CTA_PHASE
-        if (tid < 24) { v1[24 + tid] = hn[tid]; v3[24 + tid] = hn[tid]; v4[tid] = hn[tid]; }   // vad_gru_state
-        else if (tid < 48) v3[tid - 24] = v1[tid - 24];                                      // dense_out
-        else if (tid < 90) { v3[48 + tid - 48] = feat[tid - 48]; v4[72 + tid - 48] = feat[tid - 48]; }
-    RN_CTA_END
-    RN_CTA_PHASE
-        if (tid == kRnnThreads - 1) {                        // vad_output, sigmoid (rnn.c:166)
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const int o = r * kRv_end;
+            if (tid < 24) {                                                                  // vad_gru_state
+                if ((act >> r) & 1) v1[o + 24 + tid] = hn[o + tid];
+                v3[o + 24 + tid] = hn[o + tid]; v4[o + tid] = hn[o + tid];
+            } else if (tid < 48) v3[o + tid - 24] = v1[o + tid - 24];                        // dense_out
+            else if (tid < 90) { v3[o + tid] = feat[o + tid - 48]; v4[o + 24 + tid] = feat[o + tid - 48]; }
+        }
+        if (tid == kRnnThreads - 1) {                        // vad_output, sigmoid (rnn.c:166), on another warp
             const RnnLayer L = rnn_layer(kL_vout);
-            const float s = rnn_chain(W + L.w_off, L.cols, 0, v1 + 24, 0, L.J, bias[L.b_off]);
-            *vad_out = sigmoid_approx(tansig, kWScale * s);
+            float s[R];
+#pragma unroll
+            for (int r = 0; r < R; r++) s[r] = bias[L.b_off];
+            // its input is the NEW vad state, read from hn (v1[24..] is being written by warp 0)
+            rnn_chain<R>(W2 + L.w_off / 2, L.cols, 0, hn, 0, L.J, s);
+#pragma unroll
+            for (int r = 0; r < R; r++)
+                if ((act >> r) & 1) *out.vad[r] = sigmoid_approx(tansig, kWScale * s[r]);
         }
     RN_CTA_END
-    rnn_gru_cta(W, bias, tansig, kL_noise, v3, zr, hp, hn);
+    rnn_gru_cta<R>(W2, bias, tansig, kL_noise, v3, zr, hp, hn);
     RN_CTA_PHASE
-        if (tid < 48) { v3[90 + tid] = hn[tid]; v4[24 + tid] = hn[tid]; }                    // noise_gru_state
+        if (tid < 48) {                                                                      // noise_gru_state
+#pragma unroll
+            for (int r = 0; r < R; r++) {
+                const int o = r * kRv_end;
+                if ((act >> r) & 1) v3[o + 90 + tid] = hn[o + tid];
+                v4[o + 24 + tid] = hn[o + tid];
+            }
+        }
     RN_CTA_END
-    rnn_gru_cta(W, bias, tansig, kL_den, v4, zr, hp, hn);
+    rnn_gru_cta<R>(W2, bias, tansig, kL_den, v4, zr, hp, hn);
     RN_CTA_PHASE
-        if (tid < 96) v4[114 + tid] = hn[tid];                                               // denoise_gru_state
-    RN_CTA_END
-    RN_CTA_PHASE
-        if (tid < 22) {                                      // denoise_output, sigmoid (rnn.c:177)
+        if (tid < 22) {                                      // denoise_output, sigmoid (rnn.c:177) on the NEW denoise state (hn)
             const RnnLayer L = rnn_layer(kL_out);
-            const float s = rnn_chain(W + L.w_off, L.cols, tid, v4 + 114, 0, L.J, bias[L.b_off + tid]);
-            gains_out[tid] = sigmoid_approx(tansig, kWScale * s);
+            float s[R];
+#pragma unroll
+            for (int r = 0; r < R; r++) s[r] = bias[L.b_off + tid];
+            rnn_chain<R>(W2 + L.w_off / 2, L.cols, tid, hn, 0, L.J, s);
+#pragma unroll
+            for (int r = 0; r < R; r++)
+                if ((act >> r) & 1) out.gains[r][tid] = sigmoid_approx(tansig, kWScale * s[r]);
+        } else if (tid >= 32 && tid < 128) {                                                 // denoise_gru_state, warps 1-3
+#pragma unroll
+            for (int r = 0; r < R; r++)
+                if ((act >> r) & 1) v4[r * kRv_end + 114 + tid - 32] = hn[r * kRv_end + tid - 32];
         }
     RN_CTA_END
 }

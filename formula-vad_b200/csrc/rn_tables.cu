@@ -82,6 +82,15 @@ int host_tables_build(HostTables *out, const char *blob_path) {
                 for (int c = 0; c < cols; c++) out->weights[L.w_off + (s.M + j) * cols + c] = bf16_of_int8(r[j * cols + c]);
         for (int c = 0; c < cols; c++) out->bias[L.b_off + c] = (float)bi[c];
     }
+    out->weights2.assign(kRnnWeights / 2, 0u);
+    for (int l = 0; l < 6; l++) {
+        const RnnLayer L = rnn_layer(l);
+        if ((L.J & 1) || (L.M & 1) || (L.w_off & 1)) return set_error(FVAD_ENOT_INITIALIZED, "layer %d cannot be row-paired", l);
+        for (int j = 0; j < L.J; j += 2)
+            for (int c = 0; c < L.cols; c++)
+                out->weights2[L.w_off / 2 + (j / 2) * L.cols + c] =
+                    (unsigned)out->weights[L.w_off + j * L.cols + c] | ((unsigned)out->weights[L.w_off + (j + 1) * L.cols + c] << 16);
+    }
     const float *ts = (const float *)b.find("tansig_table", 201, 1);
     if (!ts) return set_error(FVAD_ENOT_INITIALIZED, "model blob lacks tansig_table");
     out->tansig.assign(ts, ts + 201);

@@ -13,6 +13,7 @@ struct HostTables {
     std::vector<cpx> tw;
     std::vector<short> rev;
     std::vector<unsigned short> weights;     // bf16 bit patterns, layer matrices W[j][col] (rn_core.cuh rnn_layer)
+    std::vector<unsigned> weights2;          // the same matrices with rows paired: W[j][col] | W[j+1][col] << 16
     double dct_scale = 0;
     Tables view() const {
         Tables t;

@@ -32,7 +32,7 @@ struct RnPersist {                 // per state, lives across tiles (DenoiseStat
 
 struct RnDevTables {
     Tables t{};
-    unsigned short *weights = nullptr;
+    unsigned *weights2 = nullptr;            // row-paired bf16 matrices (rn_core.cuh)
     float *bias = nullptr;
 };
 
@@ -88,7 +88,7 @@ static int rn_tables_get(int device, RnDevTables *out) {
         float *hw, *dct, *frac, *omf, *ts; cpx *tw; short *rev;
         FVAD_TRY(up(&hw, h.half_window)); FVAD_TRY(up(&dct, h.dct)); FVAD_TRY(up(&frac, h.frac)); FVAD_TRY(up(&omf, h.omf));
         FVAD_TRY(up(&ts, h.tansig)); FVAD_TRY(up(&tw, h.tw)); FVAD_TRY(up(&rev, h.rev));
-        FVAD_TRY(up(&d.weights, h.weights)); FVAD_TRY(up(&d.bias, h.bias));
+        FVAD_TRY(up(&d.weights2, h.weights2)); FVAD_TRY(up(&d.bias, h.bias));
         d.t.half_window = hw; d.t.dct = dct; d.t.frac = frac; d.t.omf = omf; d.t.tansig = ts; d.t.tw = tw; d.t.rev = rev;
         d.t.dct_scale = h.dct_scale;
         g_rn_tab[device] = d;
@@ -317,32 +317,68 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_cepsfeat(const float *
     cepsfeat_warp(cepsc + (n * (8 + Qcap) + 8 + j) * kNB, rank[f], featB + f * 8, feat + f * kNFeat, smem + w * 80);
 }
 
-// One CTA per state walks its non-silent frames in order.  Weights (bf16, 174 KB) stay in shared memory.
-__global__ void __launch_bounds__(kRnnThreads) k_rn_rnn(const unsigned short *__restrict__ weights, const float *__restrict__ bias,
+// One CTA walks the non-silent frames of R states in lock-step (round j = the j-th non-silent frame of each state; a
+// state with fewer frames idles).  Weights (row-paired bf16, 174 KB) stay in shared memory, so there is one CTA per SM:
+// R > 1 is what lets more than one state per SM make progress.  The frame index and the 42 features of the NEXT round
+// are fetched while this round computes.
+template <int R>
+__global__ void __launch_bounds__(kRnnThreads) k_rn_rnn(const unsigned *__restrict__ weights2, const float *__restrict__ bias,
                                                         const float *__restrict__ tansig, const float *__restrict__ feat,
                                                         const int *__restrict__ nzlist, const int *__restrict__ nz_tile,
-                                                        RnPersist *persist, size_t Qcap, float *gains, float *vad) {
+                                                        RnPersist *persist, size_t Qcap, size_t N, float *gains, float *vad) {
     extern __shared__ __align__(16) unsigned char smraw[];
-    unsigned short *W = reinterpret_cast<unsigned short *>(smraw);
+    unsigned *W2 = reinterpret_cast<unsigned *>(smraw);
     float *b = reinterpret_cast<float *>(smraw + ((kRnnWeights * 2 + 15) & ~15));
     float *ts = b + 560;
     float *scr = ts + 208;
-    const size_t n = blockIdx.x;
-    for (int i = threadIdx.x; i < kRnnWeights / 2; i += kRnnThreads)
-        reinterpret_cast<unsigned *>(W)[i] = reinterpret_cast<const unsigned *>(weights)[i];
-    for (int i = threadIdx.x; i < kRnnBiases; i += kRnnThreads) b[i] = bias[i];
-    for (int i = threadIdx.x; i < 201; i += kRnnThreads) ts[i] = tansig[i];
-    for (int i = threadIdx.x; i < kRv_end; i += kRnnThreads) scr[i] = persist[n].rnn_vec[i];
-    __syncthreads();
-    const int nz = nz_tile[n];
-    for (int j = 0; j < nz; j++) {
-        const int q = nzlist[n * Qcap + j];
-        const size_t f = n * Qcap + q;
-        if (threadIdx.x < kNFeat) scr[kRv_feat + threadIdx.x] = feat[f * kNFeat + threadIdx.x];
-        __syncthreads();
-        rnn_frame_cta(W, b, ts, scr, gains + f * kNB, vad + f);
+    const int tid = threadIdx.x;
+    const size_t n0 = (size_t)blockIdx.x * R;
+    for (int i = tid; i < kRnnWeights / 2; i += kRnnThreads) W2[i] = weights2[i];
+    for (int i = tid; i < kRnnBiases; i += kRnnThreads) b[i] = bias[i];
+    for (int i = tid; i < 201; i += kRnnThreads) ts[i] = tansig[i];
+    int nz[R], nzmax = 0;
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+        const bool live = n0 + r < N;
+        for (int i = tid; i < kRv_end; i += kRnnThreads) scr[r * kRv_end + i] = live ? persist[n0 + r].rnn_vec[i] : 0.f;
+        nz[r] = live ? nz_tile[n0 + r] : 0;
+        nzmax = nz[r] > nzmax ? nz[r] : nzmax;
     }
-    for (int i = threadIdx.x; i < kRv_end; i += kRnnThreads) persist[n].rnn_vec[i] = scr[i];
+    // rounds j (current), j+1 (features in flight), j+2 (frame index in flight)
+    int qa[R], qb[R];
+    float fnext[R];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+        qa[r] = 0 < nz[r] ? nzlist[(n0 + r) * Qcap + 0] : 0;
+        qb[r] = 1 < nz[r] ? nzlist[(n0 + r) * Qcap + 1] : 0;
+        fnext[r] = (tid < kNFeat && 0 < nz[r]) ? feat[((n0 + r) * Qcap + qa[r]) * kNFeat + tid] : 0.f;
+    }
+    __syncthreads();
+    for (int j = 0; j < nzmax; j++) {
+        unsigned act = 0;
+        RnnOut<R> out;
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            const bool on = j < nz[r];
+            act |= on ? 1u << r : 0u;
+            const size_t f = (n0 + r) * Qcap + qa[r];
+            out.gains[r] = gains + f * kNB;
+            out.vad[r] = vad + f;
+            if (tid < kNFeat && on) scr[r * kRv_end + kRv_feat + tid] = fnext[r];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < R; r++) {                       // prefetch for the next two rounds
+            if (tid < kNFeat && j + 1 < nz[r]) fnext[r] = feat[((n0 + r) * Qcap + qb[r]) * kNFeat + tid];
+            qa[r] = qb[r];
+            qb[r] = j + 2 < nz[r] ? nzlist[(n0 + r) * Qcap + j + 2] : 0;
+        }
+        rnn_frame_cta<R>(W2, b, ts, scr, act, out);
+    }
+#pragma unroll
+    for (int r = 0; r < R; r++)
+        if (n0 + r < N)
+            for (int i = tid; i < kRv_end; i += kRnnThreads) persist[n0 + r].rnn_vec[i] = scr[r * kRv_end + i];
 }
 
 // lastg floor (denoise.c:478-482): one thread per (state, band); also zeroes vad/gains bookkeeping of silent frames
@@ -442,7 +478,7 @@ constexpr size_t kBiquadSmemHog = 200 * 1024;
 constexpr size_t kSmemAna = (size_t)kWarpsPerCta * kScrAna * sizeof(float);
 constexpr size_t kSmemPitch = (size_t)kWarpsPerCta * kScrPitch * sizeof(float);
 constexpr size_t kSmemSyn = (size_t)kWarpsPerCta * kScrSyn * sizeof(float);
-constexpr size_t kSmemRnn = ((kRnnWeights * 2 + 15) & ~15) + (560 + 208 + kRv_end) * sizeof(float);
+constexpr size_t smem_rnn(int R) { return ((kRnnWeights * 2 + 15) & ~15) + (560 + 208 + (size_t)R * kRv_end) * sizeof(float); }
 
 template <class T> static int rn_alloc(RnnoiseBatch *r, T **p, size_t n) {
     void *q = nullptr;
@@ -503,7 +539,9 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_pfeat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemAna);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_pitch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemPitch);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_synth, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemSyn);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemRnn);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(1));
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(2));
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(4));
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBiquadSmemHog);
         if (e != cudaSuccess) rc = set_error(FVAD_ECUDA, "cudaFuncSetAttribute: %s (is this an sm_100 device?)", cudaGetErrorString(e));
     }
@@ -570,8 +608,17 @@ int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     FVAD_TRY(rn_check(r, slot, Qs));
     if (Qs == 0) return FVAD_OK;
     RnSlot &s = r->slots[slot];
-    FVAD_LAUNCH(k_rn_rnn, (unsigned)r->N, kRnnThreads, kSmemRnn, st, r->tab.weights, r->tab.bias, r->tab.t.tansig, s.feat, s.nzlist,
-                s.nz_tile, r->persist, r->Qcap, s.gains, s.vad);
+    // States per CTA: 1 while every state can have an SM of its own (shortest chain), then 2, then 4.
+    // FVAD_RNN_R overrides (tests exercise every variant on a handful of states).
+    const size_t sms = (size_t)device_sm_count(r->device);
+    int R = r->N <= sms ? 1 : r->N <= 2 * sms ? 2 : 4;
+    if (const char *e = getenv("FVAD_RNN_R")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) R = v; }
+    const unsigned grid = (unsigned)ceil_div(r->N, (size_t)R);
+#define FVAD_RNN_GO(RR)                                                                                                  \
+    FVAD_LAUNCH_NAMED("k_rn_rnn", k_rn_rnn<RR>, grid, kRnnThreads, smem_rnn(RR), st, r->tab.weights2, r->tab.bias,        \
+                      r->tab.t.tansig, s.feat, s.nzlist, s.nz_tile, r->persist, r->Qcap, r->N, s.gains, s.vad)
+    if (R == 1) FVAD_RNN_GO(1); else if (R == 2) FVAD_RNN_GO(2); else FVAD_RNN_GO(4);
+#undef FVAD_RNN_GO
     FVAD_CUDA_TRY(cudaGetLastError());
     return FVAD_OK;
 }

@@ -10,8 +10,14 @@ from conftest import synth, assert_segments_equal
 pytestmark = pytest.mark.gpu
 
 
-def test_denoiser_batch_bit_exact(fv, checker):
-    S, secs = 4, 8
+@pytest.mark.parametrize("rnn_r", [None, 2, 4])
+def test_denoiser_batch_bit_exact(fv, checker, rnn_r, monkeypatch):
+    """rnn_r forces the RNN kernel variant that walks 2 / 4 states per CTA in lock-step (chosen by itself only beyond
+    148 states); 5 states leave the last CTA partly filled and the streams' silent frames make the states' frame counts
+    differ, so idle states are exercised."""
+    if rnn_r:
+        monkeypatch.setenv("FVAD_RNN_R", str(rnn_r))
+    S, secs = 5, 8
     pcm = np.stack([synth(fv, 20 + s, secs) for s in range(S)])
     d = fv.DenoiserBatch(S)
     out, vad = d.run(pcm)
