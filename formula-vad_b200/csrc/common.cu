@@ -72,6 +72,7 @@ const char *fvad_status_name(int s) {
     case FVAD_EINVALID_ARGUMENT: return "InvalidArgument";
     case FVAD_EUNSUPPORTED: return "Unsupported";
     case FVAD_ECUDA: return "CudaError";
+    case FVAD_EINSUFFICIENT_SAMPLES: return "InsufficientSamples";
     default: return "Unknown";
     }
 }

@@ -98,6 +98,64 @@ extern "C" int fvad_stft_batch(fvad_fft *f, const float *d_pcm, size_t n_rows, s
                        f->device, (cudaStream_t)cuda_stream);
 }
 
+// ---- Spectrogram.compute (src/audio_utils/Spectrogram.zig:30-94) ---------------------------------------------
+extern "C" int fvad_spectrogram_shape(size_t n_samples, size_t sample_rate, size_t fft_size, size_t hop_size,
+                                      fvad_spectrogram_info *info) {
+    if (!info) return set_error(FVAD_EINVALID_ARGUMENT, "null info");
+    if (fft_size == 0 || (fft_size % 2) != 0) return set_error(FVAD_EINVALID_FFT_SIZE, "fft_size %zu must be even and non-zero", fft_size);
+    if (hop_size == 0) return set_error(FVAD_EINVALID_ARGUMENT, "hop_size 0 (division by zero in the reference)");
+    if (n_samples < fft_size) return set_error(FVAD_EINSUFFICIENT_SAMPLES, "%zu samples < fft_size %zu", n_samples, fft_size);   // :34-36
+    if (hop_size > n_samples) return set_error(FVAD_EOUT_OF_RANGE, "hop_size %zu > %zu samples (usize underflow in the reference)", hop_size, n_samples);
+    const size_t steps = (n_samples - hop_size) / hop_size;                                                                          // :39
+    if (steps > 0 && (steps - 1) * hop_size + fft_size > n_samples)
+        return set_error(FVAD_EOUT_OF_RANGE, "last frame ends at %zu > %zu samples (the reference's slice panics)",
+                         (steps - 1) * hop_size + fft_size, n_samples);
+    info->height = fft_size / 2 + 1;
+    info->width = steps;
+    info->bin_width = (float)sample_rate / (float)fft_size;
+    info->nyquist_freq = (float)sample_rate / 2;
+    const size_t processed = steps ? (steps - 1) * hop_size + fft_size : 0;                                                          // :66
+    info->length_sec = (double)processed / (double)sample_rate;
+    return FVAD_OK;
+}
+
+extern "C" int fvad_spectrogram_compute(const float *samples, size_t n_samples, size_t sample_rate, size_t fft_size,
+                                        size_t hop_size, float *values, size_t values_len, float *bin_labels,
+                                        fvad_spectrogram_info *info) {
+    fvad_spectrogram_info local;
+    if (!info) info = &local;
+    FVAD_TRY(fvad_spectrogram_shape(n_samples, sample_rate, fft_size, hop_size, info));
+    if (!samples || !values) return set_error(FVAD_EINVALID_ARGUMENT, "null samples/values");
+    if (values_len != info->width * info->height)
+        return set_error(FVAD_EINVALID_RESULT_LEN, "values length %zu != width*height %zu", values_len, info->width * info->height);
+    if (fft_size != (size_t)kFft) return set_error(FVAD_EUNSUPPORTED, "this build's FFT kernel covers fft_size 2048 only (got %zu)", fft_size);
+    if (hop_size & 1) return set_error(FVAD_EUNSUPPORTED, "odd hop_size %zu: the kernel loads sample pairs", hop_size);
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return set_error(FVAD_ECUDA, "cudaGetDevice: %s (no CPU fallback exists)", cudaGetErrorString(e));
+    const StftTables *tabs = nullptr;
+    FVAD_TRY(stft_tables_get(device, &tabs));
+    if (bin_labels)
+        for (size_t k = 0; k < info->height; k++) bin_labels[k] = (float)k * info->bin_width;     // FFT.binToFreq, FFT.zig:134-144
+    if (info->width == 0) return FVAD_OK;
+    float *d_in = nullptr, *d_out = nullptr;
+    int rc = FVAD_OK;
+    if (cudaMalloc(&d_in, sizeof(float) * n_samples) != cudaSuccess || cudaMalloc(&d_out, sizeof(float) * values_len) != cudaSuccess)
+        rc = set_error(FVAD_EOUT_OF_MEMORY, "device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (rc == FVAD_OK && cudaMemcpy(d_in, samples, sizeof(float) * n_samples, cudaMemcpyHostToDevice) != cudaSuccess)
+        rc = set_error(FVAD_ECUDA, "H2D: %s", cudaGetErrorString(cudaGetLastError()));
+    if (rc == FVAD_OK) {
+        StftBands b{}; b.n_bands = 0;
+        // one row, `width` overlapping frames `hop_size` apart; the window norm factor FFT.fft recomputes per call
+        // (FFT.zig:94) is the table's (same in-order f32 sum over the same Hann values)
+        rc = stft_launch(*tabs, d_in, 1, n_samples, info->width, hop_size, b, nullptr, info->width, 0, d_out, nullptr, 0.f, device, 0);
+    }
+    if (rc == FVAD_OK && cudaMemcpy(values, d_out, sizeof(float) * values_len, cudaMemcpyDeviceToHost) != cudaSuccess)
+        rc = set_error(FVAD_ECUDA, "D2H: %s", cudaGetErrorString(cudaGetLastError()));
+    cudaFree(d_in); cudaFree(d_out);
+    return rc;
+}
+
 // ---- VADMachine sweep (BASELINE config 5) --------------------------------------------------
 // One scan per (stream, config) over the same records: VAD.stateMachineStep's alt machines
 // (VAD.zig:375-380) run on "shared features".  Machines are laid out as n_configs machines per stream.

@@ -46,6 +46,11 @@ _fp = C.POINTER(C.c_float)
 _lib = None
 
 
+class SpectrogramInfo(C.Structure):
+    _fields_ = [("height", C.c_size_t), ("width", C.c_size_t), ("bin_width", C.c_float), ("nyquist_freq", C.c_float),
+                ("length_sec", C.c_double)]
+
+
 class FvadError(RuntimeError):
     """Carries the reference's Zig error name (e.g. 'InvalidSampleRate') as .name."""
 
@@ -98,6 +103,8 @@ def lib():
         "fvad_fft_bin_to_freq": (C.c_int, [vp, sz, _fp]),
         "fvad_hann_window_periodic": (None, [_fp, sz]), "fvad_window_norm_factor": (C.c_float, [_fp, sz]),
         "fvad_stft_batch": (C.c_int, [vp, vp, sz, sz, sz, sz, sz, sz, vp, vp, vp]),
+        "fvad_spectrogram_shape": (C.c_int, [sz, sz, sz, sz, C.POINTER(SpectrogramInfo)]),
+        "fvad_spectrogram_compute": (C.c_int, [_fp, sz, sz, sz, sz, _fp, sz, _fp, C.POINTER(SpectrogramInfo)]),
         "fvad_denoiser_create": (C.c_int, [C.POINTER(vp)]), "fvad_denoiser_destroy": (None, [vp]),
         "fvad_denoiser_frame_size": (sz, []),
         "fvad_denoiser_denoise": (C.c_int, [vp, _fp, sz, _fp, sz, _fp, sz, _fp]),
@@ -350,6 +357,37 @@ class FFT:
         _check(lib().fvad_stft_batch(self._h, C.c_void_p(dev_ptr), n_rows, row_stride, n_frames, hop, min_bin, max_bin,
                                      C.c_void_p(band_ptr), C.c_void_p(spectra_ptr) if spectra_ptr else None,
                                      C.c_void_p(cuda_stream) if cuda_stream else None))
+
+
+class Spectrogram:
+    """audio_utils/Spectrogram.zig drop-in: Spectrogram.compute(samples, sample_rate, fft_size, hop_size) with the
+    reference's fields values (width x height, row = one FFT step), bin_labels, bin_width, height, width,
+    nyquist_freq, length_sec.  Errors carry the Zig names (InsufficientSamples, ...)."""
+
+    @staticmethod
+    def shape(n_samples, sample_rate, fft_size=2048, hop_size=2048):
+        info = SpectrogramInfo()
+        _check(lib().fvad_spectrogram_shape(n_samples, sample_rate, fft_size, hop_size, C.byref(info)))
+        return info
+
+    @classmethod
+    def compute(cls, samples, sample_rate, fft_size=2048, hop_size=2048):
+        samples = np.ascontiguousarray(samples, np.float32)
+        info = cls.shape(samples.size, sample_rate, fft_size, hop_size)
+        self = cls()
+        self.values = np.empty((info.width, info.height), np.float32)
+        self.bin_labels = np.empty(info.height, np.float32)
+        _check(lib().fvad_spectrogram_compute(_f(samples), samples.size, sample_rate, fft_size, hop_size, _f(self.values),
+                                              self.values.size, _f(self.bin_labels), C.byref(info)))
+        self.height, self.width = int(info.height), int(info.width)
+        self.bin_width, self.nyquist_freq, self.length_sec = float(info.bin_width), float(info.nyquist_freq), float(info.length_sec)
+        return self
+
+
+def norm_to_dbfs(values):
+    """audio_utils.normToDBFS (src/audio_utils.zig:6-12): 20*log10(v), host-side (numpy's f32 log10 may differ from
+    Zig's by an ulp; it feeds only the viewer)."""
+    return (np.float32(20.0) * np.log10(np.asarray(values, np.float32))).astype(np.float32)
 
 
 def hann_window_periodic(n):

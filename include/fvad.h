@@ -44,7 +44,8 @@ typedef enum fvad_status {
     FVAD_EOUT_OF_MEMORY         = -12,  /* error.OutOfMemory (host or device) */
     FVAD_EINVALID_ARGUMENT      = -13,  /* null handle, bad index, zero-length ring, ... */
     FVAD_EUNSUPPORTED           = -14,  /* valid in the reference, not covered by this build */
-    FVAD_ECUDA                  = -15   /* CUDA runtime / driver failure, or no sm_100 device: there is no CPU path */
+    FVAD_ECUDA                  = -15,  /* CUDA runtime / driver failure, or no sm_100 device: there is no CPU path */
+    FVAD_EINSUFFICIENT_SAMPLES  = -16   /* Spectrogram.zig:34-36 error.InsufficientSamples */
 } fvad_status;
 
 const char *fvad_last_error(void);
@@ -205,6 +206,28 @@ float  fvad_window_norm_factor(const float *w, size_t n);
 int    fvad_stft_batch(fvad_fft *f, const float *d_pcm, size_t n_rows, size_t row_stride, size_t n_frames,
                        size_t hop, size_t min_bin, size_t max_bin, float *d_band_sum, float *d_spectra,
                        void *cuda_stream);
+
+/* Spectrogram.compute (src/audio_utils/Spectrogram.zig:30-94): the second consumer of FFT.fft.
+ * width = (n_samples - hop_size) / hop_size frames (incomplete frames dropped, :39), frame i covers
+ * samples[i*hop_size, i*hop_size + fft_size), periodic Hann window (the reference ignores
+ * SpectrogramOptions.window_function, :49-50), values[i*height + k] = normalised magnitude of bin k.
+ * `samples` and `values` are HOST arrays (the reference's []f32 in, []f32 out); `bin_labels` (height floats,
+ * FFT.binToFreq) may be NULL.  fvad_spectrogram_shape does no compute and needs no device.
+ * Errors: InsufficientSamples (n_samples < fft_size, :34-36); OutOfRange where the reference's slice
+ * samples[from..to] would run past the input (hop_size < fft_size/2: a bounds panic in the reference);
+ * Unsupported for fft_size != 2048 or odd hop_size. */
+typedef struct fvad_spectrogram_info {
+    size_t height;          /* bins = fft_size/2 + 1 */
+    size_t width;           /* steps */
+    float  bin_width;
+    float  nyquist_freq;
+    double length_sec;      /* processed samples / sample_rate (:81) */
+} fvad_spectrogram_info;
+int    fvad_spectrogram_shape(size_t n_samples, size_t sample_rate, size_t fft_size, size_t hop_size,
+                              fvad_spectrogram_info *info);
+int    fvad_spectrogram_compute(const float *samples, size_t n_samples, size_t sample_rate, size_t fft_size,
+                                size_t hop_size, float *values, size_t values_len, float *bin_labels,
+                                fvad_spectrogram_info *info);
 
 /* Denoiser.zig: init/denoise/getFrameSize/deinit (src/Denoiser.zig:22-70) */
 typedef struct fvad_denoiser fvad_denoiser;
