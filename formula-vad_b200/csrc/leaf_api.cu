@@ -148,7 +148,7 @@ extern "C" int fvad_spectrogram_compute(const float *samples, size_t n_samples, 
         StftBands b{}; b.n_bands = 0;
         // one row, `width` overlapping frames `hop_size` apart; the window norm factor FFT.fft recomputes per call
         // (FFT.zig:94) is the table's (same in-order f32 sum over the same Hann values)
-        rc = stft_launch(*tabs, d_in, 1, n_samples, info->width, hop_size, b, nullptr, info->width, 0, d_out, nullptr, 0.f, device, 0);
+        rc = stft_launch(*tabs, d_in, 1, 0 /* one row: stride unused */, info->width, hop_size, b, nullptr, info->width, 0, d_out, nullptr, 0.f, device, 0);
     }
     if (rc == FVAD_OK && cudaMemcpy(values, d_out, sizeof(float) * values_len, cudaMemcpyDeviceToHost) != cudaSuccess)
         rc = set_error(FVAD_ECUDA, "D2H: %s", cudaGetErrorString(cudaGetLastError()));

@@ -112,6 +112,7 @@ def lib():
         "fvad_denoiser_batch_destroy": (None, [vp]),
         "fvad_denoiser_batch_run": (C.c_int, [vp, C.POINTER(_fp), sz, C.POINTER(_fp), C.POINTER(_fp)]),
         "fvad_vadm_sweep": (C.c_int, [vp, sz, sz, C.POINTER(VadMachineConfig), sz, sz, sz, C.c_int, vp, sz, vp]),
+        "fvad_eval_stats_batch": (C.c_int, [vp, sz, sz, vp, vp, vp, vp, vp, sz, sz, vp, C.c_int, vp]),
         "fvad_synth_fill_host": (C.c_int, [_fp, C.c_uint64, C.c_uint64, C.c_uint64, sz]),
         "fvad_synth_fill_device": (C.c_int, [vp, sz, C.c_uint64, C.c_uint64, sz, C.c_uint64, sz, vp]),
     }

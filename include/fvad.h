@@ -253,6 +253,31 @@ int    fvad_vadm_sweep(const fvad_stft_record *records, size_t n_streams, size_t
                        const fvad_vad_machine_config *configs, size_t n_configs, size_t sample_rate,
                        size_t fft_size, int device, fvad_segment *segs, size_t max_segs, uint32_t *counts);
 
+/* ---- Evaluator statistics over many result sets (the sweep's consumer) ------------
+ * statistics.fromEvaluator (src/Evaluator/statistics.zig:85-113) on top of Evaluator.initAndRun's overlap matching
+ * (src/Evaluator.zig:90-156; SpeechSegment.findOverlapping/overlapWith, src/Evaluator/SpeechSegment.zig:22-49) with
+ * the extrusion / gap filling of extrudeSegments (statistics.zig:225-250), all in f32 in the reference's order.
+ * One device thread per result set.  Set i has counts[i] VAD segments at segs[i*max_segs ...] (the layout
+ * fvad_vadm_sweep writes; seconds = (f32)sample / (f32)sample_rate as SimulationInstance.storeResult does,
+ * src/simulator/SimulationInstance.zig:226-227) and is scored against reference list set_ref[i]: labels
+ * ref_from/ref_to[ref_offsets[j] .. ref_offsets[j+1]) in seconds.  Both sides must be ordered by start
+ * (initAndRun sorts them; VADMachine emits in time order, Audacity labels are sorted by fvad's host code). */
+typedef struct fvad_stat_config {           /* statistics.StatConfig, statistics.zig:77-83 */
+    float ignore_shorter_than_sec;
+    float extrude_start;
+    float extrude_end;
+    float fill_gaps;
+} fvad_stat_config;
+typedef struct fvad_single_stats {          /* statistics.SingleStats, statistics.zig:8-39 */
+    float total_positives_sec, true_positives_sec, false_positives_sec, false_negatives_sec;
+    float true_positive_rate, false_negative_rate, false_discovery_rate, precision;
+    float fm_index, f_score, f_score_beta;
+} fvad_single_stats;
+int    fvad_eval_stats_batch(const fvad_segment *segs, size_t n_sets, size_t max_segs, const uint32_t *counts,
+                             const uint32_t *set_ref, const float *ref_from, const float *ref_to,
+                             const uint32_t *ref_offsets, size_t n_refs, size_t sample_rate,
+                             const fvad_stat_config *config, int device, fvad_single_stats *out);
+
 /* ---- seeded synthetic 48 kHz input ------------------------------ */
 /* Bit-identical on host and device.  Sample i of stream `stream_id` (absolute index
  * first_sample + i).  kind 0 = "onboard": engine bed + radio-speech bursts + gaps. */

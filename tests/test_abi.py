@@ -111,3 +111,16 @@ def test_sass_exactness_guard():
     env = dict(os.environ, PATH=os.environ.get("PATH", "") + ":/usr/local/cuda/bin")
     r = subprocess.run(["bash", os.path.join(root, "tools", "check_sass.sh")], capture_output=True, text=True, env=env)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_spectrogram_shape_host_logic(fv):
+    """Spectrogram.compute's bookkeeping (Spectrogram.zig:34-39,66,81) needs no device."""
+    i = fv.Spectrogram.shape(48000 * 3, 48000, 2048, 1024)
+    assert (i.height, i.width) == (1025, (48000 * 3 - 1024) // 1024)
+    assert i.bin_width == np.float32(23.4375) and i.nyquist_freq == 24000.0
+    assert i.length_sec == ((i.width - 1) * 1024 + 2048) / 48000
+    for args, name in (((100, 48000, 2048, 2048), "InsufficientSamples"), ((4096, 48000, 2048, 512), "OutOfRange"),
+                       ((4096, 48000, 2047, 512), "InvalidFFTSize")):
+        with pytest.raises(fv.FvadError) as e:
+            fv.Spectrogram.shape(*args)
+        assert e.value.name == name
