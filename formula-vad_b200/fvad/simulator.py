@@ -26,7 +26,7 @@ import numpy as np
 from . import EVENT_DTYPE, SEG_DTYPE, FvadError, PipelineBatch, default_machine_config  # noqa: F401
 from . import evaluator as ev
 
-REC_COMPLETED = 2          # fvad.h: FVAD_REC_COMPLETED
+REC_STARTED, REC_COMPLETED, REC_ABORTED = 1, 2, 3          # fvad.h: fvad_recording_state
 
 
 class UnsupportedAudioFormat(RuntimeError):
@@ -122,6 +122,33 @@ class Instance:
         self.audio = WavFile(os.path.normpath(os.path.join(base_path, j["audio_path"])))
         self.reference = ev.sort_by_start(ev.read_parse_audacity_segments(os.path.normpath(os.path.join(base_path, j["ref_path"]))))
         self.vad_segments = None
+        self.events = None
+
+    def recordings(self):
+        """Recorder / on_recording (src/AudioPipeline/Recorder.zig:52-146, src/AudioPipeline.zig:134-195):
+        every started -> completed pair of the main machine yields the ORIGINAL samples [start, end) of the quietest
+        channel (Recorder.findBestChannel: smallest f32 RMS, first wins ties).  A recording is delivered only once the
+        stream has reached its end sample (AudioPipeline.maybeRecordBuffer), so one still waiting at end of stream is
+        dropped, as in the reference.  Yields dicts {start, end, channel, pcm, duration_seconds}."""
+        start = None
+        for e in self.events:
+            st = int(e["recording_state"])
+            if st == REC_STARTED:
+                start = int(e["sample_number"])
+            elif st == REC_ABORTED:
+                start = None
+            elif st == REC_COMPLETED and start is not None:
+                end = int(e["sample_number"])
+                if end <= self.audio.n_frames:
+                    pcm = self.audio.read(start, end - start)
+                    vols = [rms_volume(ch) for ch in pcm]
+                    best, best_vol = 0, np.float32(9999)
+                    for c, v in enumerate(vols):
+                        if v < best_vol:
+                            best, best_vol = c, v
+                    yield dict(start=start, end=end, channel=best, pcm=pcm[best],
+                               duration_seconds=float(np.float32(end - start) / np.float32(self.audio.sample_rate)))
+                start = None
 
 
 class Simulation:
@@ -166,7 +193,9 @@ class Simulation:
                     b.push_samples(pcm)
                 b.sync()
                 for s, inst in enumerate(insts):
-                    inst.vad_segments = keep_decided_inside(b.segments(s, 0), b.events(s), inst.audio.n_frames, self.fft_size)
+                    events = b.events(s)
+                    inst.vad_segments = keep_decided_inside(b.segments(s, 0), events, inst.audio.n_frames, self.fft_size)
+                    inst.events = events[events["at_index"] < frames_decided(inst.audio.n_frames, self.fft_size) * self.fft_size]
 
     # -- statistics, Audacity text, report (simulator.zig:108-139,230-256) ------------------------------------------
     def results(self, device=-1):
@@ -191,7 +220,23 @@ class Simulation:
                 f.write(txt)
         with open(os.path.join(self.out_path, "report.txt"), "w") as f:
             f.write(report)
+        # PipelineContext.onRecording (SimulationInstance.zig:26-56): `{count:0>3}-{name}` per instance directory; the
+        # reference encodes Ogg/Vorbis through libsndfile, which this build does not have, so the clips are float WAVs
+        for inst in self.instances:
+            d = os.path.join(self.out_path, inst.name)
+            os.makedirs(d, exist_ok=True)
+            for k, rec in enumerate(inst.recordings()):
+                write_wav_f32(os.path.join(d, f"{k:03d}-{inst.name}.wav"), rec["pcm"][None, :], inst.audio.sample_rate)
         return True
+
+
+def rms_volume(x):
+    """audio_utils.rmsVolume (src/audio_utils.zig:14-24): in-order f32 sum of squares, / n, sqrt."""
+    x = np.asarray(x, np.float32)
+    if x.size == 0:
+        return np.float32(np.nan)
+    total = np.add.accumulate(x * x, dtype=np.float32)[-1]
+    return np.float32(np.sqrt(np.float32(total / np.float32(x.size))))
 
 
 def frames_decided(n_samples, fft_size=2048, rn_frame=480):

@@ -57,5 +57,20 @@ def test_plan_with_ragged_streams(fv, checker, tmp_path):
             g, w = stats[i][k], np.float32(wstats[k])
             assert (np.isnan(g) and np.isnan(w)) or g.tobytes() == w.tobytes(), (i, k, g, w)
         assert open(os.path.join(s.out_path, f"{inst.name}-audacity.txt")).read() == texts[inst.name]
+        # recordings (Recorder.zig): one clip per started -> completed pair whose end the stream reaches
+        oev = checker.run_pipeline([pcm[0]], main_cfg=cfg, trace=True)["events"]
+        want_clips, start = [], None
+        for (_, state, sample) in oev:
+            if state == 1: start = sample
+            elif state == 3: start = None
+            elif state == 2 and start is not None:
+                if sample <= lengths[i]: want_clips.append((start, sample))
+                else: dropped += 1
+                start = None
+        clips = list(inst.recordings())
+        assert [(c["start"], c["end"]) for c in clips] == want_clips
+        for c in clips:
+            assert c["channel"] == 0 and np.array_equal(c["pcm"], pcm[0, c["start"]:c["end"]])
+        assert len(os.listdir(os.path.join(s.out_path, inst.name))) == len(clips)
     assert total > 0
     assert "=> Performance Report" in report and "car3" in report and os.path.isfile(os.path.join(s.out_path, "report.txt"))

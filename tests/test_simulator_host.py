@@ -74,3 +74,12 @@ def test_plan_parsing_and_tail_bookkeeping(fv, tmp_path):
     evs["at_index"] = [0, 2048 * 5, 2048 * 22, 2048 * 22, 2048 * 23]
     kept = sim.keep_decided_inside(seg, evs, 48000)
     assert list(kept["sample_to"]) == [10, 20]                                      # frame 23 lies in the padding
+
+
+def test_rms_volume_is_the_in_order_f32_sum(fv):
+    from fvad import simulator as sim
+    x = np.random.default_rng(2).uniform(-1, 1, 4801).astype(np.float32)
+    s = np.float32(0)
+    for v in x:
+        s = np.float32(s + np.float32(v * v))                                       # audio_utils.zig:16-21
+    assert sim.rms_volume(x) == np.float32(np.sqrt(np.float32(s / np.float32(x.size))))
