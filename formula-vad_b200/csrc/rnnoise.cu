@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(64) k_rn_biquad(const float *__restrict__ in, 
     if (threadIdx.x == 0) { persist[n].biq[0] = m0; persist[n].biq[1] = m1; }
 }
 
-constexpr int kWarpsPerCta = 8;
+constexpr int kWarpsPerCta = 4;     // 4 warps x <= 12 KB scratch: such a CTA still fits beside the RNN CTA (174 KB of weights) on an SM
 
 __global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_analysis(Tables t, const float *__restrict__ hp, size_t hp_stride,
                                                                    size_t N, int Q, size_t Qcap, cpx *X, float *Ex,
