@@ -110,7 +110,8 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    S, secs = args.streams, args.ref_sample_seconds
+    # the WHOLE job's streams (weak scaling: streams-per-GPU x N), on the host cores of the box, by rank 0 alone
+    S, secs = args.streams * max(1, args.gpus), args.ref_sample_seconds
     for _ in range(args.warmup):
         cpu_run(S, max(10, secs // 8))
     walls, segs = [], 0
@@ -125,8 +126,9 @@ def reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * wall, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic (seeded generator, same streams as the b200 arm)",
-        "config": {"workload": f"configs[1]: {S} synthetic 48 kHz mono streams x 2 h, RNNoise denoiser + VAD, default plan",
-                   "streams": S, "sample_seconds_per_stream": secs, "push": 48000},
+        "config": {"workload": f"configs[1]: {args.streams} synthetic 48 kHz mono streams x 2 h per GPU, RNNoise denoiser + VAD, "
+                               f"default plan" + ("" if args.gpus <= 1 else f"; {S} streams, the {args.gpus}-GPU job's whole workload (configs[3] at N=8)"),
+                   "streams": S, "streams_per_gpu": args.streams, "sample_seconds_per_stream": secs, "push": 48000},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample,
                          "compiler": "gcc -O2 -ffp-contract=off (zig ReleaseFast unavailable on this box)"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
