@@ -64,7 +64,11 @@ int rn_emu_tile(void *h, const float *in, size_t in_stride, int Tn, float *out, 
     std::vector<float> scr(4096);
     // k_rn_analysis / k_rn_pitch: warp per frame
     for (int q = 0; q < Q; q++) analysis_warp(t, hp.data(), q, &X[(size_t)q * kFreq], &Ex[q * kNB], &ceps[q * kNB], &sil[q], scr.data());
-    for (int q = 0; q < Q; q++) pitch_warp(t, hp.data(), q, &cand[q], scr.data());
+    for (int q = 0; q < Q; q++) {
+        const float *xs[1] = {hp.data() + (size_t)q * kFrame};
+        PitchCand *outs[1] = {&cand[q]};
+        pitch_blk<1>(xs, outs, scr.data());
+    }
     // k_rn_pitch_seq
     for (int q = 0; q < Q; q++) {
         float g;

@@ -278,12 +278,12 @@ struct PitchCand {                 // per frame
     float g[kMaxCand], xy[kMaxCand], yy[kMaxCand];
 };
 
+// find_best_pitch, pitch.c:46-104.  Syy0 = 1 + sum_{j<len} y(j)^2, accumulated in that order by the caller.
 template <class YF>
-RN_HD void best_pitch2(const float *xcorr, YF y, int len, int max_pitch, int *best) {   // find_best_pitch, pitch.c:46-104
-    float Syy = 1;
+RN_HD void best_pitch2(const float *xcorr, YF y, int len, int max_pitch, float Syy0, int *best) {
+    float Syy = Syy0;
     float best_num0 = -1, best_num1 = -1, best_den0 = 0, best_den1 = 0;
     best[0] = 0; best[1] = 1;
-    for (int j = 0; j < len; j++) Syy = Syy + y(j) * y(j);
     for (int i = 0; i < max_pitch; i++) {
         if (xcorr[i] > 0) {
             float x16 = xcorr[i];
@@ -307,29 +307,53 @@ RN_HD float pitch_gain(float xy, float xx, float yy) {     // compute_pitch_gain
     return (float)(xy / sqrt((double)(1 + xx * yy)));
 }
 
-RN_HD void pitch_warp(const Tables &t, const float *hpb, int q, PitchCand *out, float *scr) {
-    float *xlp = scr, *xc = scr + 864, *yyl = xc + 296, *ip = yyl + 388;
-    int *list = reinterpret_cast<int *>(ip + 388);
-    float *misc = reinterpret_cast<float *>(list + 64);    // [0..4] ac, [8..12] num, ints below
-    int *imisc = reinterpret_cast<int *>(misc + 16);       // [0] best0 [1] best1 [2] T0 [3] nlist [4] ncand; [5..] candT, candTb
-    const float *x = hpb + (size_t)q * kFrame;             // pitch_buf of frame q (1728 samples)
-    (void)t;
-    RN_PHASE   // pitch_downsample, pitch.c:171-173
+// A block of NT = 32*F threads analyses F frames together.  Work that fills a warp (down-sampling, the FIR, the
+// coarse correlation) stays "warp f owns frame f"; the chains that occupy only a few lanes per frame (5 autocorrelation
+// lags, the best-pitch scans, 10 fine lags, the energy recurrences, the decision prep) are gathered from all F frames
+// onto as few warps as possible, and independent chains share a phase -- a warp costs issue slots for its longest lane
+// however few lanes are active.  Every chain is still one lane running the reference's order.  F = 1 on the host.
+#if defined(__CUDA_ARCH__)
+#define RN_BLK_PHASE(NT) { const int tid = threadIdx.x;
+#define RN_BLK_END } __syncthreads();
+#else
+#define RN_BLK_PHASE(NT) for (int tid = 0; tid < (NT); tid++) {
+#define RN_BLK_END }
+#endif
+
+template <int F>
+RN_HD void pitch_blk(const float *const *xs, PitchCand *const *outs, float *scr0) {
+    constexpr int NT = 32 * F;
+    // per frame f (scr = scr0 + f*kScrPitch): xlp 864 | xc 296 | yyl 388 | ip 388 | list 64 ints | misc 16 | imisc 48 ints
+    // misc: [0..4] ac, [8..12] num, [13] Syy of the coarse scan, [14] Syy of the fine scan
+    // imisc: [0] best0 [1] best1 [2] T0 [3] nlist [4] ncand; [5..] candT, candTb
+#define RN_SCR(f) (scr0 + (size_t)(f) * kScrPitch)
+#define RN_XC(f) (RN_SCR(f) + 864)
+#define RN_YYL(f) (RN_SCR(f) + 864 + 296)
+#define RN_IP(f) (RN_SCR(f) + 864 + 296 + 388)
+#define RN_LIST(f) (reinterpret_cast<int *>(RN_SCR(f) + 864 + 296 + 388 + 388))
+#define RN_MISC(f) (RN_SCR(f) + 864 + 296 + 388 + 388 + 64)
+#define RN_IMISC(f) (reinterpret_cast<int *>(RN_SCR(f) + 864 + 296 + 388 + 388 + 64 + 16))
+    RN_BLK_PHASE(NT)   // pitch_downsample, pitch.c:171-173 (warp f owns frame f)
+        const int f = tid >> 5, lane = tid & 31;
+        const float *x = xs[f];                            // pitch_buf of the frame (1728 samples)
+        float *xlp = RN_SCR(f);
         for (int i = lane; i < 864; i += 32)
             xlp[i] = (i == 0) ? .5f * (.5f * x[1] + x[0]) : .5f * (.5f * (x[2 * i - 1] + x[2 * i + 1]) + x[2 * i]);
-    RN_END
-    RN_PHASE   // _celt_autocorr lag 0..4: fastN = 860 in-order chain, then the tail (celt_lpc.c:261-267)
-        if (lane < 5) {
-            const int k = lane;
+    RN_BLK_END
+    RN_BLK_PHASE(NT)   // _celt_autocorr lag 0..4: fastN = 860 in-order chain, then the tail (celt_lpc.c:261-267)
+        if (tid < 5 * F) {
+            const int f = tid / 5, k = tid - 5 * f;
+            const float *xlp = RN_SCR(f);
             float a = 0;
             for (int j = 0; j < 860; j++) a = a + xlp[j] * xlp[j + k];
             float d = 0;
             for (int i = k + 860; i < 864; i++) d = d + xlp[i] * xlp[i - k];
-            misc[k] = a + d;
+            RN_MISC(f)[k] = a + d;
         }
-    RN_END
-    RN_PHASE
-        if (lane == 0) {
+    RN_BLK_END
+    RN_BLK_PHASE(NT)
+        if (tid < F) {
+            float *misc = RN_MISC(tid);
             float ac[5];
             for (int i = 0; i < 5; i++) ac[i] = misc[i];
             ac[0] *= 1.0001f;                              // pitch.c:187
@@ -361,16 +385,18 @@ RN_HD void pitch_warp(const Tables &t, const float *hpb, int q, PitchCand *out, 
             misc[11] = lpc[3] + c1 * lpc[2];
             misc[12] = c1 * lpc[3];
         }
-    RN_END
+    RN_BLK_END
     // celt_fir5 (pitch.c:106-145) in place: taps read the ORIGINAL x_lp, so compute all, then store.
 #if defined(__CUDA_ARCH__)
     float yv[27];
 #define RN_YV(r) yv[r]
 #else
-    static thread_local float yv_all[32][27];
-#define RN_YV(r) yv_all[lane][r]
+    static thread_local float yv_all[NT][27];
+#define RN_YV(r) yv_all[tid][r]
 #endif
-    RN_PHASE
+    RN_BLK_PHASE(NT)
+        const int f = tid >> 5, lane = tid & 31;
+        const float *xlp = RN_SCR(f), *misc = RN_MISC(f);
         const float n0 = misc[8], n1 = misc[9], n2 = misc[10], n3 = misc[11], n4 = misc[12];
 #pragma unroll
         for (int r = 0; r < 27; r++) {
@@ -383,44 +409,80 @@ RN_HD void pitch_warp(const Tables &t, const float *hpb, int q, PitchCand *out, 
             sum = sum + n4 * (i >= 5 ? xlp[i - 5] : 0.0f);
             RN_YV(r) = sum;
         }
-    RN_END
-    RN_PHASE
+    RN_BLK_END
+    RN_BLK_PHASE(NT)
+        const int f = tid >> 5, lane = tid & 31;
+        float *xlp = RN_SCR(f);
 #pragma unroll
         for (int r = 0; r < 27; r++) xlp[lane + 32 * r] = RN_YV(r);
-    RN_END
+    RN_BLK_END
 #undef RN_YV
-    RN_PHASE   // coarse search, 4x decimation: celt_pitch_xcorr(x_lp4, y_lp4, xcorr, 240, 147) (pitch.c:335)
-        for (int i = lane; i < 147; i += 32) {
-            float s = 0;
-            for (int j = 0; j < 240; j++) s = s + xlp[384 + 2 * j] * xlp[2 * (i + j)];
-            xc[i] = s;
+    RN_BLK_PHASE(NT)   // coarse search, 4x decimation: celt_pitch_xcorr(x_lp4, y_lp4, xcorr, 240, 147) (pitch.c:335)
+        const int f = tid >> 5, lane = tid & 31;
+        const float *xlp = RN_SCR(f);
+        float *xc = RN_XC(f);
+        // Lane l owns lags l, l+32, .., l+128 and walks j once for all five: one broadcast load of x feeds five chains
+        // (each still accumulated over j in order), and the coarse scan's Syy (pitch.c:57-58) rides along.
+        float s[5] = {0, 0, 0, 0, 0}, Syy = 1;
+        for (int j = 0; j < 240; j++) {
+            const float xv = xlp[384 + 2 * j];
+            const float *y = xlp + 2 * (lane + j);
+#pragma unroll
+            for (int r = 0; r < 5; r++) s[r] = s[r] + xv * y[64 * r];   // lags >= 147 (r = 4, lane >= 19) read in bounds, unused
+            const float y0 = xlp[2 * j];
+            Syy = Syy + y0 * y0;
         }
-    RN_END
-    RN_PHASE
-        if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < 5; r++)
+            if (lane + 32 * r < 147) xc[lane + 32 * r] = s[r];
+        if (lane == 31) RN_MISC(f)[13] = Syy;
+    RN_BLK_END
+    RN_BLK_PHASE(NT)
+        if (tid < F) {
+            const float *xlp = RN_SCR(tid);
             int best[2];
-            best_pitch2(xc, [&](int j) { return xlp[2 * j]; }, 240, 147, best);
-            imisc[0] = best[0]; imisc[1] = best[1];
+            best_pitch2(RN_XC(tid), [&](int j) { return xlp[2 * j]; }, 240, 147, RN_MISC(tid)[13], best);
+            RN_IMISC(tid)[0] = best[0]; RN_IMISC(tid)[1] = best[1];
         }
-    RN_END
-    RN_PHASE
+    RN_BLK_END
+    RN_BLK_PHASE(NT)
+        const int f = tid >> 5, lane = tid & 31;
+        float *xc = RN_XC(f);
         for (int i = lane; i < 294; i += 32) xc[i] = 0;    // pitch.c:352
-    RN_END
-    RN_PHASE   // fine search, 2x decimation (pitch.c:349-366): only lags within 2 of a coarse best
-        if (lane < 10) {
-            const int b0 = imisc[0], b1 = imisc[1];
-            const int i = lane < 5 ? 2 * b0 + lane - 2 : 2 * b1 + lane - 7;
+    RN_BLK_END
+    RN_BLK_PHASE(NT)   // fine search, 2x decimation (pitch.c:349-366): only lags within 2 of a coarse best
+        if (tid < 10 * F) {
+            const int f = tid / 10, l = tid - 10 * f;
+            const float *xlp = RN_SCR(f);
+            const int b0 = RN_IMISC(f)[0], b1 = RN_IMISC(f)[1];
+            const int i = l < 5 ? 2 * b0 + l - 2 : 2 * b1 + l - 7;
             if (i >= 0 && i < 294) {
                 float s = 0;
                 for (int j = 0; j < 480; j++) s = s + xlp[384 + j] * xlp[i + j];
-                xc[i] = s < -1 ? -1 : s;
+                RN_XC(f)[i] = s < -1 ? -1 : s;
             }
+        } else if (tid < 11 * F) {                         // the fine scan's Syy (pitch.c:57-58), same length of chain
+            const int f = tid - 10 * F;
+            const float *xlp = RN_SCR(f);
+            float Syy = 1;
+            for (int j = 0; j < 480; j++) Syy = Syy + xlp[j] * xlp[j];
+            RN_MISC(f)[14] = Syy;
+        } else if (tid < 12 * F) {                         // dual_inner_prod's xx, pitch.c:446
+            const int f = tid - 11 * F;
+            const float *xlp = RN_SCR(f);
+            float xx = 0;
+            for (int i = 0; i < 480; i++) xx = xx + xlp[384 + i] * xlp[384 + i];
+            RN_IP(f)[0] = xx;
+            RN_YYL(f)[0] = xx;
         }
-    RN_END
-    RN_PHASE
-        if (lane == 0) {
+    RN_BLK_END
+    RN_BLK_PHASE(NT)
+        if (tid < F) {
+            const int f = tid;
+            const float *xlp = RN_SCR(f), *xc = RN_XC(f);
+            int *imisc = RN_IMISC(f), *list = RN_LIST(f);
             int best[2] = {imisc[0], imisc[1]};
-            best_pitch2(xc, [&](int j) { return xlp[j]; }, 480, 294, best);
+            best_pitch2(xc, [&](int j) { return xlp[j]; }, 480, 294, RN_MISC(f)[14], best);
             int offset = 0;
             if (best[0] > 0 && best[0] < 294 - 1) {        // pitch.c:371-384
                 const float a = xc[best[0] - 1], b = xc[best[0]], c = xc[best[0] + 1];
@@ -450,57 +512,81 @@ RN_HD void pitch_warp(const Tables &t, const float *hpb, int q, PitchCand *out, 
             }
             imisc[4] = nc;
             int nl = 0;
-            for (int lag = 1; lag <= 384; lag++)
-                if (need[lag >> 5] & (1u << (lag & 31))) list[nl++] = lag;
+            for (int w = 0; w < 13; w++)                   // ascending lags
+                for (unsigned m = need[w]; m; m &= m - 1) {
+                    int bit = 0;
+                    for (unsigned lowest = m & (0u - m); lowest > 1; lowest >>= 1) bit++;
+                    const int lag = 32 * w + bit;
+                    if (lag >= 1 && lag <= 384) list[nl++] = lag;
+                }
             imisc[3] = nl;
-        }
-    RN_END
-    RN_PHASE   // inner products by lag: ip[lag] = sum_i x[i]*x[i-lag], x = x_lp + 384, N = 480
-        if (lane == 0) {
-            float xx = 0;                                  // dual_inner_prod's xx, pitch.c:446
-            for (int i = 0; i < 480; i++) xx = xx + xlp[384 + i] * xlp[384 + i];
-            ip[0] = xx;
-            yyl[0] = xx;
-            float yy = xx;
-            for (int i = 1; i <= 384; i++) {               // pitch.c:449-453
+        } else if (tid >= NT - F) {                        // pitch.c:449-453, on the last warp while warp 0 scans
+            const int f = NT - 1 - tid;
+            const float *xlp = RN_SCR(f);
+            float *yyl = RN_YYL(f);
+            float yy = yyl[0];
+            for (int i = 1; i <= 384; i++) {
                 yy = yy + xlp[384 - i] * xlp[384 - i] - xlp[384 + 480 - i] * xlp[384 + 480 - i];
                 yyl[i] = yy < 0 ? 0 : yy;
             }
-        } else {
-            const int nl = imisc[3];
-            for (int idx = lane - 1; idx < nl; idx += 31) {
-                const int lag = list[idx];
-                float s = 0;
-                for (int i = 0; i < 480; i++) s = s + xlp[384 + i] * xlp[384 + i - lag];
-                ip[lag] = s;
-            }
         }
-    RN_END
-    RN_PHASE
-        const int nc = imisc[4];
-        if (lane < nc) {
-            const int T0 = imisc[2];
-            const float xx = ip[0];
-            int T; float xy, yy;
-            if (lane == 0) { T = T0; xy = ip[T0]; yy = yyl[T0]; }
-            else {
-                const int T1 = imisc[5 + 2 * lane], T1b = imisc[6 + 2 * lane];
-                T = T1;
-                xy = .5f * (ip[T1] + ip[T1b]);             // pitch.c:479-480
-                yy = .5f * (yyl[T1] + yyl[T1b]);
+    RN_BLK_END
+    RN_BLK_PHASE(NT)   // inner products by lag: ip[lag] = sum_i x[i]*x[i-lag], x = x_lp + 384, N = 480; all frames' lags pooled
+        int total = 0;
+#pragma unroll
+        for (int f = 0; f < F; f++) total += RN_IMISC(f)[3];
+        for (int item = tid; item < total; item += NT) {
+            int f = 0, idx = item;
+#pragma unroll
+            for (int g = 0; g < F - 1; g++) {
+                const int nl = RN_IMISC(g)[3];
+                if (f == g && idx >= nl) { idx -= nl; f = g + 1; }
             }
-            out->T[lane] = (short)T;
-            out->xy[lane] = xy; out->yy[lane] = yy;
-            out->g[lane] = pitch_gain(xy, xx, yy);
-            const float x0 = ip[T - 1], x1 = ip[T], x2 = ip[T + 1];       // pitch.c:509-517
-            int off;
-            if ((x2 - x0) > .7f * (x1 - x0)) off = 1;
-            else if ((x0 - x2) > .7f * (x1 - x2)) off = -1;
-            else off = 0;
-            out->off[lane] = (signed char)off;
+            const float *xlp = RN_SCR(f);
+            const int lag = RN_LIST(f)[idx];
+            float s = 0;
+            for (int i = 0; i < 480; i++) s = s + xlp[384 + i] * xlp[384 + i - lag];
+            RN_IP(f)[lag] = s;
         }
-        if (lane == 0) out->n = nc;
-    RN_END
+    RN_BLK_END
+    RN_BLK_PHASE(NT)
+        if (tid < 16 * F) {
+            const int f = tid >> 4, c = tid & 15;
+            const int *imisc = RN_IMISC(f);
+            const float *ip = RN_IP(f), *yyl = RN_YYL(f);
+            PitchCand *out = outs[f];
+            const int nc = imisc[4];
+            if (out != nullptr && c < nc) {
+                const int T0 = imisc[2];
+                const float xx = ip[0];
+                int T; float xy, yy;
+                if (c == 0) { T = T0; xy = ip[T0]; yy = yyl[T0]; }
+                else {
+                    const int T1 = imisc[5 + 2 * c], T1b = imisc[6 + 2 * c];
+                    T = T1;
+                    xy = .5f * (ip[T1] + ip[T1b]);             // pitch.c:479-480
+                    yy = .5f * (yyl[T1] + yyl[T1b]);
+                }
+                out->T[c] = (short)T;
+                out->xy[c] = xy; out->yy[c] = yy;
+                out->g[c] = pitch_gain(xy, xx, yy);
+                const float x0 = ip[T - 1], x1 = ip[T], x2 = ip[T + 1];       // pitch.c:509-517
+                int off;
+                if ((x2 - x0) > .7f * (x1 - x0)) off = 1;
+                else if ((x0 - x2) > .7f * (x1 - x2)) off = -1;
+                else off = 0;
+                out->off[c] = (signed char)off;
+            }
+            if (out != nullptr && c == 0) out->n = nc;
+        }
+    RN_BLK_END
+#undef RN_SCR
+#undef RN_XC
+#undef RN_YYL
+#undef RN_IP
+#undef RN_LIST
+#undef RN_MISC
+#undef RN_IMISC
 }
 
 // The sequential part of remove_doubling (pitch.c:459-525): walks the candidate table with the

@@ -243,11 +243,19 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_analysis(Tables t, con
 __global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_pitch(Tables t, const float *__restrict__ hp, size_t hp_stride, size_t N,
                                                                 int Q, size_t Qcap, PitchCand *cand) {
     extern __shared__ float smem[];
-    const int w = threadIdx.x >> 5;
-    const size_t id = (size_t)blockIdx.x * kWarpsPerCta + w;
-    if (id >= N * (size_t)Q) return;
-    const size_t n = id / Q; const int q = (int)(id - n * Q);
-    pitch_warp(t, hp + n * hp_stride, q, cand + n * Qcap + q, smem + (size_t)w * kScrPitch);
+    (void)t;
+    const float *xs[kWarpsPerCta];
+    PitchCand *outs[kWarpsPerCta];
+    const size_t id0 = (size_t)blockIdx.x * kWarpsPerCta, total = N * (size_t)Q;
+#pragma unroll
+    for (int f = 0; f < kWarpsPerCta; f++) {                // a block past the end re-analyses its first frame, unwritten
+        const bool ok = id0 + f < total;
+        const size_t id = ok ? id0 + f : id0;
+        const size_t n = id / Q; const int q = (int)(id - n * Q);
+        xs[f] = hp + n * hp_stride + (size_t)q * kFrame;
+        outs[f] = ok ? cand + n * Qcap + q : nullptr;
+    }
+    pitch_blk<kWarpsPerCta>(xs, outs, smem);
 }
 
 __global__ void k_rn_pitch_seq(const PitchCand *__restrict__ cand, size_t N, int Q, size_t Qcap, RnPersist *persist, int *pidx) {
