@@ -183,7 +183,7 @@ RN_HD int band_of_bin(int k) {          // band index i with 4*eband[i] <= k < 4
     const int e = k >> 2;
     int i = 0;
 #pragma unroll
-    for (int j = 1; j < kNB - 1; j++) i += (e >= eband(j)) ? 1 : 0;
+    for (int j = 1; j < kNB - 1; j++) i += (e >= eband(j)) ? 1 : 0;      // (a branchy decision tree measured slower)
     return i;
 }
 RN_HD float band_interp_bin(const Tables &t, const float *bandE, int k) {
@@ -229,7 +229,7 @@ constexpr int kScrPitch = 864 + 296 + 388 + 388 + 64 + 64; // xlp, xc, yyl, ip, 
 RN_HD void analysis_warp(const Tables &t, const float *hpb, int q, cpx *Xq, float *Exq, float *cepsq, int *silq,
                          float *scr) {
     cpx *buf = reinterpret_cast<cpx *>(scr);
-    float *misc = scr + kScrFft;                           // [0..21] Ex, [32..53] Ly, [60] E
+    float *misc = scr + kScrFft;                           // [0..21] Ex, [32..53] Ly, [64..85] log10(.01 + Ex)
     const float *x0 = hpb + (kPHist - kFrame) + (size_t)q * kFrame;   // analysis_mem | in
     load_windowed(t, buf, [&](int i) { return x0[i]; });
     fft960_warp(buf, t.tw);
@@ -237,12 +237,14 @@ RN_HD void analysis_warp(const Tables &t, const float *hpb, int q, cpx *Xq, floa
         for (int k = lane; k < kFreq; k += 32) Xq[k] = buf[s960(k)];
         if (lane < kNB) misc[lane] = band_chain<SlotSpec, SlotSpec, false>(t, SlotSpec{buf}, SlotSpec{buf}, lane);
     RN_END
+    RN_PHASE   // the logarithms are independent per band: 22 lanes, not one (only the follow/logMax scan is sequential)
+        if (lane < kNB) { Exq[lane] = misc[lane]; misc[64 + lane] = (float)log10(1e-2 + misc[lane]); }
+    RN_END
     RN_PHASE
-        if (lane < kNB) Exq[lane] = misc[lane];
         if (lane == 0) {
             float logMax = -2, follow = -2, E = 0;
             for (int i = 0; i < kNB; i++) {                // denoise.c:351-357
-                float ly = (float)log10(1e-2 + misc[i]);
+                float ly = misc[64 + i];
                 double a = follow - 1.5;
                 double inner_max = a > ly ? a : (double)ly;
                 float lm7 = logMax - 7;
