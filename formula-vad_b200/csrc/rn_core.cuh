@@ -178,12 +178,32 @@ RN_HD float band_chain(const Tables &t, SX X, SP P, int b) {
     return s;
 }
 
+// The same chain over per-bin products e[k] (= |X[k]|^2 or Re(X[k] conj P[k]), denoise.c:112-113,137-138) that all
+// 32 lanes formed beforehand: only the weighted in-order accumulation stays on the band's lane.
+RN_HD float band_chain_pre(const Tables &t, const float *e, int b) {
+    float s = 0;
+    if (b > 0) {
+        const int lo = eband(b - 1) << 2, hi = eband(b) << 2;
+        for (int k = lo; k < hi; k++) s += t.frac[k] * e[k];
+    }
+    if (b < kNB - 1) {
+        const int lo = eband(b) << 2, hi = eband(b + 1) << 2;
+        for (int k = lo; k < hi; k++) s += t.omf[k] * e[k];
+    }
+    if (b == 0 || b == kNB - 1) s *= 2;
+    return s;
+}
+// per-bin products live in the upper half of the FFT buffer: bins 0..480 occupy slots <= 510, floats from 1040 on are free
+constexpr int kBandE = 1040;
+
 // interp_band_gain (denoise.c:150-163) for one bin < 400
-RN_HD int band_of_bin(int k) {          // band index i with 4*eband[i] <= k < 4*eband[i+1]
-    const int e = k >> 2;
-    int i = 0;
-#pragma unroll
-    for (int j = 1; j < kNB - 1; j++) i += (e >= eband(j)) ? 1 : 0;      // (a branchy decision tree measured slower)
+RN_HD int band_of_bin(int k) {          // band index i with 4*eband[i] <= k < 4*eband[i+1], k < 400: eband's piecewise-regular
+    const int e = k >> 2;               // spacing (1, 2, 4, 6, then 8/12/18/22) as selects -- no branches, no 20 compares
+    int i = e;
+    i = e >= 8 ? 8 + ((e - 8) >> 1) : i;
+    i = e >= 16 ? 12 + ((e - 16) >> 2) : i;
+    i = e >= 28 ? 15 + (e >= 34 ? 1 : 0) : i;
+    i = e >= 40 ? 17 + (e >= 48 ? 1 : 0) + (e >= 60 ? 1 : 0) + (e >= 78 ? 1 : 0) : i;
     return i;
 }
 RN_HD float band_interp_bin(const Tables &t, const float *bandE, int k) {
@@ -233,9 +253,16 @@ RN_HD void analysis_warp(const Tables &t, const float *hpb, int q, cpx *Xq, floa
     const float *x0 = hpb + (kPHist - kFrame) + (size_t)q * kFrame;   // analysis_mem | in
     load_windowed(t, buf, [&](int i) { return x0[i]; });
     fft960_warp(buf, t.tw);
+    float *be = scr + kBandE;
     RN_PHASE
-        for (int k = lane; k < kFreq; k += 32) Xq[k] = buf[s960(k)];
-        if (lane < kNB) misc[lane] = band_chain<SlotSpec, SlotSpec, false>(t, SlotSpec{buf}, SlotSpec{buf}, lane);
+        for (int k = lane; k < kFreq; k += 32) {
+            const cpx x = buf[s960(k)];
+            Xq[k] = x;
+            if (k < 400) { float tmp = x.r * x.r; tmp += x.i * x.i; be[k] = tmp; }
+        }
+    RN_END
+    RN_PHASE
+        if (lane < kNB) misc[lane] = band_chain_pre(t, be, lane);
     RN_END
     RN_PHASE   // the logarithms are independent per band: 22 lanes, not one (only the follow/logMax scan is sequential)
         if (lane < kNB) { Exq[lane] = misc[lane]; misc[64 + lane] = (float)log10(1e-2 + misc[lane]); }
@@ -635,11 +662,22 @@ RN_HD void pfeat_warp(const Tables &t, const float *hpb, int q, int pitch_index,
     const float *p0 = hpb + (size_t)q * kFrame + (kPBuf - kWin - pitch_index);   // denoise.c:337-338
     load_windowed(t, buf, [&](int i) { return p0[i]; });
     fft960_warp(buf, t.tw);
+    float *be = scr + kBandE, *bc = be + 400;
     RN_PHASE
-        for (int k = lane; k < kFreq; k += 32) Pq[k] = buf[s960(k)];
+        for (int k = lane; k < kFreq; k += 32) {
+            const cpx pv = buf[s960(k)];
+            Pq[k] = pv;
+            if (k < 400) {
+                const cpx x = Xq[k];
+                float tmp = pv.r * pv.r; tmp += pv.i * pv.i; be[k] = tmp;
+                tmp = x.r * pv.r; tmp += x.i * pv.i; bc[k] = tmp;
+            }
+        }
+    RN_END
+    RN_PHASE
         if (lane < kNB) {
-            const float ep = band_chain<SlotSpec, SlotSpec, false>(t, SlotSpec{buf}, SlotSpec{buf}, lane);
-            float exp_ = band_chain<LinSpec, SlotSpec, true>(t, LinSpec{Xq}, SlotSpec{buf}, lane);
+            const float ep = band_chain_pre(t, be, lane);
+            float exp_ = band_chain_pre(t, bc, lane);
             exp_ = (float)(exp_ / sqrt(.001 + Exq[lane] * ep));        // denoise.c:343
             misc[lane] = ep; misc[32 + lane] = exp_;
             Epq[lane] = ep; Expq[lane] = exp_;
@@ -741,9 +779,12 @@ RN_HD void synth_warp(const Tables &t, const cpx *Xq, const cpx *Pq, const float
                 X[k].i += rf * p.i;
             }
         RN_END
+        RN_PHASE   // per-bin |X|^2 of the pitch-filtered spectrum (the FFT buffer is idle until the inverse transform's load)
+            for (int k = lane; k < 400; k += 32) { const cpx x = X[k]; float tmp = x.r * x.r; tmp += x.i * x.i; scr[k] = tmp; }
+        RN_END
         RN_PHASE
             if (lane < kNB) {
-                const float ne = band_chain<LinSpec, LinSpec, false>(t, LinSpec{X}, LinSpec{X}, lane);
+                const float ne = band_chain_pre(t, scr, lane);
                 misc[32 + lane] = (float)sqrt(Exq[lane] / (1e-8 + ne));
             }
         RN_END
