@@ -820,13 +820,20 @@ RN_HD void synth_warp(const Tables &t, const cpx *Xq, const cpx *Pq, const float
 // ------------------------------------------------------------------------------------------
 // activations (rnn.c:41-72)
 // ------------------------------------------------------------------------------------------
+// The reference goes through double in two places; both are replaced by float operations that give the same bits:
+//  * floor((double)(.5f + 25*x)) -- the argument is already a float in [0.5, 200.5] (x in [0, 8) here), its conversion to
+//    double is exact and floor of a non-negative value is truncation: (int)(.5f + 25*x).
+//  * (float)(.5 + .5*t), t a float in [-1, 1], and (float)(.5*x): halving is exact, so the only rounding is that of
+//    .5 + .5t.  For |.5t| >= 2^-30 the exact sum fits in 53 bits (the double is exact, one rounding either way); below that
+//    both roundings give exactly .5f.  Hence .5f + .5f*t, and .5f*x, in float.
+// tests/test_kernel_emulation.py holds the emulation (this code) against the oracle, which keeps the double form.
 RN_HD float tansig_approx(const float *table, float x) {
     float y, dy, sign = 1;
     if (!(x < 8)) return 1;
     if (!(x > -8)) return -1;
     if (x != x) return 0;
     if (x < 0) { x = -x; sign = -1; }
-    const int i = (int)floor((double)(.5f + 25 * x));
+    const int i = (int)(.5f + 25 * x);
     x -= .04f * i;
     y = table[i];
     dy = 1 - y * y;
@@ -834,7 +841,7 @@ RN_HD float tansig_approx(const float *table, float x) {
     return sign * y;
 }
 RN_HD float sigmoid_approx(const float *table, float x) {
-    return (float)(.5 + .5 * tansig_approx(table, (float)(.5 * x)));
+    return .5f + .5f * tansig_approx(table, .5f * x);
 }
 
 
