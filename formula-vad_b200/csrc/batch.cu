@@ -189,11 +189,11 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
         // Stage A carries the chain that sets the pace, so its stream gets the highest priority: without it the tile's
         // small stage-A kernels queue behind the ten-thousands of CTAs stage B of the previous tile has just launched
         // (measured: ~5 ms per tile, 6 % of the step).  C before B before D for the same reason, in chain-length order.
-        // Only in the latency regime (few chains): with hundreds of streams everything is throughput and favouring one
-        // stage costs 7 %.
+        // Only in the latency regime (common.cu: latency_regime): with hundreds of streams everything is throughput and
+        // favouring one stage costs 7 %.
         int lo = 0, hi = 0;
         if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess) lo = hi = 0;      // hi = numerically lowest = most urgent
-        if (2 * n_streams > (size_t)device_sm_count(b->device)) hi = lo;
+        if (!latency_regime(n_streams, b->device)) hi = lo;
         auto prio = [&](int rank) { const int p = hi + rank; return p > lo ? lo : p; };
         if (cudaStreamCreateWithPriority(&b->sA, cudaStreamNonBlocking, prio(0)) != cudaSuccess ||
             cudaStreamCreateWithPriority(&b->sC, cudaStreamNonBlocking, prio(1)) != cudaSuccess ||

@@ -39,6 +39,13 @@ void profile_end(cudaStream_t stream) {
     if (!g_prof.empty()) cudaEventRecord(g_prof.back().b, stream);
 }
 
+bool latency_regime(size_t n_chains, int device) {
+    if (const char *e = getenv("FVAD_LATENCY_MODE")) return atoi(e) != 0;
+    // measured on B200 (148 SMs), x real-time latency / throughput rule: 40 chains 28.0k / 22.0k, 80: 47.5k / 37.7k,
+    // 110: 48.9k / 47.7k, 148: 49.8k / 54.5k -- the crossover sits near three quarters of the SM count
+    return 4 * n_chains <= 3 * (size_t)device_sm_count(device);
+}
+
 int device_sm_count(int device) {
     static int cache[64];
     if (device >= 0 && device < 64 && cache[device]) return cache[device];

@@ -64,5 +64,8 @@ inline size_t ceil_div(size_t a, size_t b) { return (a + b - 1) / b; }
 
 // Device properties cached per device.
 int device_sm_count(int device);
+// Latency regime = few enough sequential chains that each can own an SM (biquad SM reservation, stage-stream priorities);
+// otherwise throughput regime.  FVAD_LATENCY_MODE=0/1 overrides the default rule (n_chains <= latency_chain_limit).
+bool latency_regime(size_t n_chains, int device);
 
 }  // namespace fvad

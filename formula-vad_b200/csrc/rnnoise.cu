@@ -582,7 +582,7 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
     // the chain's SM -- the chain lane is issue-latency bound and loses ~13 % when frame-parallel kernels of other
     // stages share its scheduler.  Many chains (throughput regime): no reservation, so several chains and the
     // other stages' CTAs share an SM; reserving it there serialises the biquad against everything else.
-    const size_t hog = 2 * N <= (size_t)device_sm_count(r->device) ? kBiquadSmemHog : 0;
+    const size_t hog = latency_regime(N, r->device) ? kBiquadSmemHog : 0;
     FVAD_LAUNCH(k_rn_biquad, (unsigned)N, 64, hog, st, d_in, in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
     FVAD_LAUNCH(k_rn_hp_save, (unsigned)N, 256, 0, st, s.hp, r->hp_stride(), r->hp_hist, (int)Qs);
     FVAD_CUDA_TRY(cudaGetLastError());
