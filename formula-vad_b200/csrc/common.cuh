@@ -46,7 +46,7 @@ void profile_end(cudaStream_t stream);
         ::fvad::g_launch_count.fetch_add(1, std::memory_order_relaxed);     \
     } while (0)
 
-struct cpx { float r, i; };
+struct __align__(8) cpx { float r, i; };      // 8-byte aligned: one 64-bit load or store per complex value
 
 __host__ __device__ inline cpx c_mul(cpx a, cpx b) {
     cpx m;

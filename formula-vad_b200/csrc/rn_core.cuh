@@ -223,9 +223,14 @@ template <class SRC>
 RN_HD void load_windowed(const Tables &t, cpx *buf, SRC src) {
     RN_PHASE
         const float scale = 1.f / kWin;
-        for (int i = lane; i < kWin; i += 32) {
+        float xr[kWin / 32];                                // the lane's 30 samples: every load in flight before the first use
+#pragma unroll
+        for (int u = 0; u < kWin / 32; u++) xr[u] = src(lane + 32 * u);
+#pragma unroll
+        for (int u = 0; u < kWin / 32; u++) {
+            const int i = lane + 32 * u;
             const float w = t.half_window[i < kFrame ? i : kWin - 1 - i];
-            float x = src(i);
+            float x = xr[u];
             x *= w;
             cpx v; v.r = scale * x; v.i = scale * 0.0f;
             buf[s960(t.rev[i])] = v;
@@ -332,6 +337,15 @@ RN_HD void best_pitch2(const float *xcorr, YF y, int len, int max_pitch, float S
     }
 }
 
+RN_HD void ld4(const float *p, float *v) {                 // four consecutive floats, p 16-byte aligned
+#if defined(__CUDA_ARCH__)
+    const float4 q = *reinterpret_cast<const float4 *>(p);
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+#else
+    v[0] = p[0]; v[1] = p[1]; v[2] = p[2]; v[3] = p[3];
+#endif
+}
+
 RN_HD float pitch_gain(float xy, float xx, float yy) {     // compute_pitch_gain, pitch.c:416-419
     return (float)(xy / sqrt((double)(1 + xx * yy)));
 }
@@ -374,7 +388,12 @@ RN_HD void pitch_blk(const float *const *xs, PitchCand *const *outs, float *scr0
             const int f = tid / 5, k = tid - 5 * f;
             const float *xlp = RN_SCR(f);
             float a = 0;
-            for (int j = 0; j < 860; j++) a = a + xlp[j] * xlp[j + k];
+            for (int j = 0; j < 860; j += 4) {              // the lag-0 operand as one 16-byte load per four steps
+                float xv[4];
+                ld4(xlp + j, xv);
+#pragma unroll
+                for (int u = 0; u < 4; u++) a = a + xv[u] * xlp[j + u + k];
+            }
             float d = 0;
             for (int i = k + 860; i < 864; i++) d = d + xlp[i] * xlp[i - k];
             RN_MISC(f)[k] = a + d;
@@ -439,32 +458,50 @@ RN_HD void pitch_blk(const float *const *xs, PitchCand *const *outs, float *scr0
             RN_YV(r) = sum;
         }
     RN_BLK_END
+    // ... and the 4x-decimated signal of the coarse search (x_lp4 = y_lp4 = every second sample, pitch.c:322-325) goes to a
+    // contiguous copy x4[0..431] in the still unused yyl|ip area: the coarse correlation then reads consecutive floats
+    // (stride-2 reads of xlp were 2-way bank conflicts on every load).
     RN_BLK_PHASE(NT)
         const int f = tid >> 5, lane = tid & 31;
-        float *xlp = RN_SCR(f);
+        float *xlp = RN_SCR(f), *x4 = RN_YYL(f);
 #pragma unroll
-        for (int r = 0; r < 27; r++) xlp[lane + 32 * r] = RN_YV(r);
+        for (int r = 0; r < 27; r++) {
+            xlp[lane + 32 * r] = RN_YV(r);
+            if (!(lane & 1)) x4[(lane >> 1) + 16 * r] = RN_YV(r);
+        }
     RN_BLK_END
 #undef RN_YV
     RN_BLK_PHASE(NT)   // coarse search, 4x decimation: celt_pitch_xcorr(x_lp4, y_lp4, xcorr, 240, 147) (pitch.c:335)
         const int f = tid >> 5, lane = tid & 31;
-        const float *xlp = RN_SCR(f);
+        const float *x4 = RN_YYL(f);
         float *xc = RN_XC(f);
-        // Lane l owns lags l, l+32, .., l+128 and walks j once for all five: one broadcast load of x feeds five chains
-        // (each still accumulated over j in order), and the coarse scan's Syy (pitch.c:57-58) rides along.
-        float s[5] = {0, 0, 0, 0, 0}, Syy = 1;
-        for (int j = 0; j < 240; j++) {
-            const float xv = xlp[384 + 2 * j];
-            const float *y = xlp + 2 * (lane + j);
+        // Lane l < 30 owns the five CONSECUTIVE lags 5l..5l+4 (147 needed) and walks j once for all five, each chain still
+        // accumulated over j in order: the five y values of step j+1 are four of step j's plus one new load (a register
+        // window), x arrives as one broadcast 16-byte load per four steps.  Lane 31 runs the coarse scan's
+        // Syy = 1 + sum y(j)^2 (pitch.c:57-58) in the same instruction stream: its window starts at lag 0 and its "x" is
+        // the window's own first element, so s[0] += y(j)*y(j).
+        const int base = lane == 31 ? 0 : 5 * lane;
+        float s[5] = {lane == 31 ? 1.0f : 0.0f, 0, 0, 0, 0}, w[5];
 #pragma unroll
-            for (int r = 0; r < 5; r++) s[r] = s[r] + xv * y[64 * r];   // lags >= 147 (r = 4, lane >= 19) read in bounds, unused
-            const float y0 = xlp[2 * j];
-            Syy = Syy + y0 * y0;
+        for (int r = 0; r < 5; r++) w[r] = x4[base + r];
+        for (int j0 = 0; j0 < 240; j0 += 20) {
+            float xv[20];
+#pragma unroll
+            for (int q = 0; q < 5; q++) ld4(x4 + 192 + j0 + 4 * q, xv + 4 * q);
+#pragma unroll
+            for (int u = 0; u < 20; u++) {
+                const float xl = lane == 31 ? w[0] : xv[u];
+#pragma unroll
+                for (int r = 0; r < 5; r++) s[r] = s[r] + xl * w[r];
+#pragma unroll
+                for (int r = 0; r < 4; r++) w[r] = w[r + 1];
+                w[4] = x4[base + j0 + u + 5];                // <= 154 + 244 < 432: in bounds for every lane
+            }
         }
 #pragma unroll
         for (int r = 0; r < 5; r++)
-            if (lane + 32 * r < 147) xc[lane + 32 * r] = s[r];
-        if (lane == 31) RN_MISC(f)[13] = Syy;
+            if (lane < 30 && 5 * lane + r < 147) xc[5 * lane + r] = s[r];
+        if (lane == 31) RN_MISC(f)[13] = s[0];
     RN_BLK_END
     RN_BLK_PHASE(NT)
         if (tid < F) {
@@ -487,7 +524,12 @@ RN_HD void pitch_blk(const float *const *xs, PitchCand *const *outs, float *scr0
             const int i = l < 5 ? 2 * b0 + l - 2 : 2 * b1 + l - 7;
             if (i >= 0 && i < 294) {
                 float s = 0;
-                for (int j = 0; j < 480; j++) s = s + xlp[384 + j] * xlp[i + j];
+                for (int j = 0; j < 480; j += 4) {
+                    float xv[4];
+                    ld4(xlp + 384 + j, xv);
+#pragma unroll
+                    for (int u = 0; u < 4; u++) s = s + xv[u] * xlp[i + j + u];
+                }
                 RN_XC(f)[i] = s < -1 ? -1 : s;
             }
         } else if (tid < 11 * F) {                         // the fine scan's Syy (pitch.c:57-58), same length of chain
@@ -574,7 +616,12 @@ RN_HD void pitch_blk(const float *const *xs, PitchCand *const *outs, float *scr0
             const float *xlp = RN_SCR(f);
             const int lag = RN_LIST(f)[idx];
             float s = 0;
-            for (int i = 0; i < 480; i++) s = s + xlp[384 + i] * xlp[384 + i - lag];
+            for (int i = 0; i < 480; i += 4) {
+                float xv[4];
+                ld4(xlp + 384 + i, xv);
+#pragma unroll
+                for (int u = 0; u < 4; u++) s = s + xv[u] * xlp[384 + i + u - lag];
+            }
             RN_IP(f)[lag] = s;
         }
     RN_BLK_END
@@ -664,13 +711,20 @@ RN_HD void pfeat_warp(const Tables &t, const float *hpb, int q, int pitch_index,
     fft960_warp(buf, t.tw);
     float *be = scr + kBandE, *bc = be + 400;
     RN_PHASE
-        for (int k = lane; k < kFreq; k += 32) {
-            const cpx pv = buf[s960(k)];
-            Pq[k] = pv;
-            if (k < 400) {
-                const cpx x = Xq[k];
-                float tmp = pv.r * pv.r; tmp += pv.i * pv.i; be[k] = tmp;
-                tmp = x.r * pv.r; tmp += x.i * pv.i; bc[k] = tmp;
+        cpx xr[13];                                         // bins < 400 of X (from global memory), all loads in flight at once
+#pragma unroll
+        for (int u = 0; u < 13; u++) { const int k = lane + 32 * u; if (k < 400) xr[u] = Xq[k]; }
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            const int k = lane + 32 * u;
+            if (k < kFreq) {
+                const cpx pv = buf[s960(k)];
+                Pq[k] = pv;
+                if (u < 13 && k < 400) {
+                    const cpx x = xr[u < 13 ? u : 0];
+                    float tmp = pv.r * pv.r; tmp += pv.i * pv.i; be[k] = tmp;
+                    tmp = x.r * pv.r; tmp += x.i * pv.i; bc[k] = tmp;
+                }
             }
         }
     RN_END
@@ -755,8 +809,22 @@ RN_HD void synth_warp(const Tables &t, const cpx *Xq, const cpx *Pq, const float
     cpx *buf = reinterpret_cast<cpx *>(scr);
     cpx *X = reinterpret_cast<cpx *>(scr + kScrFft);
     float *misc = scr + kScrFft + 2 * kFreq + 2;           // [0..21] r, [32..53] norm, [64..85] g_sm copy
+    cpx *Pl = buf + 256;                                   // P staged in the idle FFT buffer (floats 512..1473; |X|^2 uses 0..399)
     RN_PHASE
-        for (int k = lane; k < kFreq; k += 32) X[k] = Xq[k];
+        {
+            cpx xr[16];            // 16 loads in flight, then the stores (a load-store loop exposes the memory latency 16 times)
+#pragma unroll
+            for (int u = 0; u < 16; u++) { const int k = lane + 32 * u; if (k < kFreq) xr[u] = Xq[k]; }
+#pragma unroll
+            for (int u = 0; u < 16; u++) { const int k = lane + 32 * u; if (k < kFreq) X[k] = xr[u]; }
+        }
+        if (!silence) {
+            cpx pr[16];
+#pragma unroll
+            for (int u = 0; u < 16; u++) { const int k = lane + 32 * u; if (k < kFreq) pr[u] = Pq[k]; }
+#pragma unroll
+            for (int u = 0; u < 16; u++) { const int k = lane + 32 * u; if (k < kFreq) Pl[k] = pr[u]; }
+        }
         if (!silence && lane < kNB) {
             const float e = Expq[lane], g = g_rnn[lane];
             float r;
@@ -774,7 +842,7 @@ RN_HD void synth_warp(const Tables &t, const cpx *Xq, const cpx *Pq, const float
         RN_PHASE
             for (int k = lane; k < kFreq; k += 32) {
                 const float rf = k < 400 ? band_interp_bin(t, misc, k) : 0.0f;
-                const cpx p = Pq[k];
+                const cpx p = Pl[k];
                 X[k].r += rf * p.r;
                 X[k].i += rf * p.i;
             }
@@ -855,9 +923,12 @@ RN_HD float sigmoid_approx(const float *table, float x) {
 // by the R states, and R independent FADD chains fill each other's latency slots.  Every chain is still evaluated
 // in the reference's order on one thread.
 // ------------------------------------------------------------------------------------------
+// A CTA may hold several independent GROUPS of kRnnThreads threads (each walking its own states, sharing the weights
+// in shared memory): phases end at a barrier of the group only (named barrier 1 + group), so the groups drift apart
+// and one group's thin phases (a layer narrower than the group) are filled by the other groups' wide ones.
 #if defined(__CUDA_ARCH__)
-#define RN_CTA_PHASE { const int tid = threadIdx.x;
-#define RN_CTA_END } __syncthreads();
+#define RN_CTA_PHASE { const int tid = (int)(threadIdx.x % ::fvad::rn::kRnnThreads);
+#define RN_CTA_END } ::fvad::rn::rnn_group_sync();
 #else
 #define RN_CTA_PHASE for (int tid = 0; tid < ::fvad::rn::kRnnThreads; tid++) {
 #define RN_CTA_END }
@@ -865,6 +936,17 @@ RN_HD float sigmoid_approx(const float *table, float x) {
 
 constexpr int kRnnThreads = 288;
 constexpr int kRnnMaxR = 4;
+#if defined(__CUDACC__)
+__device__ __forceinline__ void rnn_group_sync() {
+#if defined(__CUDA_ARCH__)
+    // literal barrier numbers: with a register operand ptxas reserves all 16 barriers for the CTA
+    const unsigned g = threadIdx.x / kRnnThreads;
+    if (g == 0) asm volatile("bar.sync 1, %0;" ::"n"(kRnnThreads) : "memory");
+    else if (g == 1) asm volatile("bar.sync 2, %0;" ::"n"(kRnnThreads) : "memory");
+    else asm volatile("bar.sync 3, %0;" ::"n"(kRnnThreads) : "memory");
+#endif
+}
+#endif
 struct RnnLayer { int J, M, cols, w_off, b_off; };        // J = chain length, M = inputs before the recurrent part
 constexpr int kL_in = 0, kL_vad = 1, kL_vout = 2, kL_noise = 3, kL_den = 4, kL_out = 5;
 __host__ __device__ constexpr RnnLayer rnn_layer(int l) {

@@ -325,25 +325,28 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_cepsfeat(const float *
     cepsfeat_warp(cepsc + (n * (8 + Qcap) + 8 + j) * kNB, rank[f], featB + f * 8, feat + f * kNFeat, smem + w * 80);
 }
 
-// One CTA walks the non-silent frames of R states in lock-step (round j = the j-th non-silent frame of each state; a
-// state with fewer frames idles).  Weights (row-paired bf16, 174 KB) stay in shared memory, so there is one CTA per SM:
-// R > 1 is what lets more than one state per SM make progress.  The frame index and the 42 features of the NEXT round
-// are fetched while this round computes.
-template <int R>
-__global__ void __launch_bounds__(kRnnThreads) k_rn_rnn(const unsigned *__restrict__ weights2, const float *__restrict__ bias,
-                                                        const float *__restrict__ tansig, const float *__restrict__ feat,
-                                                        const int *__restrict__ nzlist, const int *__restrict__ nz_tile,
-                                                        RnPersist *persist, size_t Qcap, size_t N, float *gains, float *vad) {
+// One CTA = G independent groups of kRnnThreads threads; a group walks the non-silent frames of its R states in
+// lock-step (round j = the j-th non-silent frame of each state; a state with fewer frames idles).  Weights (row-paired
+// bf16, 174 KB) stay in shared memory, so there is one CTA per SM: G x R > 1 is what lets more than one state per SM make
+// progress.  R states of a group share every weight fetch and unpack (fewer instructions per frame); G groups share only
+// the weights and meet at no barrier after the start, so the narrow layers of one group (24..96 of its 288 threads busy)
+// overlap the wide layers of another.  The frame index and the 42 features of the NEXT round are fetched while this
+// round computes.
+template <int R, int G>
+__global__ void __launch_bounds__(kRnnThreads * G) k_rn_rnn(const unsigned *__restrict__ weights2, const float *__restrict__ bias,
+                                                            const float *__restrict__ tansig, const float *__restrict__ feat,
+                                                            const int *__restrict__ nzlist, const int *__restrict__ nz_tile,
+                                                            RnPersist *persist, size_t Qcap, size_t N, float *gains, float *vad) {
     extern __shared__ __align__(16) unsigned char smraw[];
     unsigned *W2 = reinterpret_cast<unsigned *>(smraw);
     float *b = reinterpret_cast<float *>(smraw + ((kRnnWeights * 2 + 15) & ~15));
     float *ts = b + 560;
-    float *scr = ts + 208;
-    const int tid = threadIdx.x;
-    const size_t n0 = (size_t)blockIdx.x * R;
-    for (int i = tid; i < kRnnWeights / 2; i += kRnnThreads) W2[i] = weights2[i];
-    for (int i = tid; i < kRnnBiases; i += kRnnThreads) b[i] = bias[i];
-    for (int i = tid; i < 201; i += kRnnThreads) ts[i] = tansig[i];
+    const int grp = threadIdx.x / kRnnThreads, tid = threadIdx.x % kRnnThreads;
+    float *scr = ts + 208 + (size_t)grp * R * kRv_end;
+    const size_t n0 = ((size_t)blockIdx.x * G + grp) * R;
+    for (int i = threadIdx.x; i < kRnnWeights / 2; i += kRnnThreads * G) W2[i] = weights2[i];
+    for (int i = threadIdx.x; i < kRnnBiases; i += kRnnThreads * G) b[i] = bias[i];
+    for (int i = threadIdx.x; i < 201; i += kRnnThreads * G) ts[i] = tansig[i];
     int nz[R], nzmax = 0;
 #pragma unroll
     for (int r = 0; r < R; r++) {
@@ -361,7 +364,7 @@ __global__ void __launch_bounds__(kRnnThreads) k_rn_rnn(const unsigned *__restri
         qb[r] = 1 < nz[r] ? nzlist[(n0 + r) * Qcap + 1] : 0;
         fnext[r] = (tid < kNFeat && 0 < nz[r]) ? feat[((n0 + r) * Qcap + qa[r]) * kNFeat + tid] : 0.f;
     }
-    __syncthreads();
+    __syncthreads();                                        // the only CTA-wide barrier: weights are in place
     for (int j = 0; j < nzmax; j++) {
         unsigned act = 0;
         RnnOut<R> out;
@@ -374,7 +377,7 @@ __global__ void __launch_bounds__(kRnnThreads) k_rn_rnn(const unsigned *__restri
             out.vad[r] = vad + f;
             if (tid < kNFeat && on) scr[r * kRv_end + kRv_feat + tid] = fnext[r];
         }
-        __syncthreads();
+        rnn_group_sync();
 #pragma unroll
         for (int r = 0; r < R; r++) {                       // prefetch for the next two rounds
             if (tid < kNFeat && j + 1 < nz[r]) fnext[r] = feat[((n0 + r) * Qcap + qb[r]) * kNFeat + tid];
@@ -482,11 +485,12 @@ __global__ void __launch_bounds__(256) k_rn_tail_carry(float *tail, int Q, size_
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
+#define FVAD_RNN_VARIANTS(X) X(1, 1) X(1, 2) X(1, 3) X(2, 1) X(2, 2) X(2, 3) X(4, 1) X(4, 2) X(4, 3)
 constexpr size_t kBiquadSmemHog = 200 * 1024;
 constexpr size_t kSmemAna = (size_t)kWarpsPerCta * kScrAna * sizeof(float);
 constexpr size_t kSmemPitch = (size_t)kWarpsPerCta * kScrPitch * sizeof(float);
 constexpr size_t kSmemSyn = (size_t)kWarpsPerCta * kScrSyn * sizeof(float);
-constexpr size_t smem_rnn(int R) { return ((kRnnWeights * 2 + 15) & ~15) + (560 + 208 + (size_t)R * kRv_end) * sizeof(float); }
+constexpr size_t smem_rnn(int states) { return ((kRnnWeights * 2 + 15) & ~15) + (560 + 208 + (size_t)states * kRv_end) * sizeof(float); }
 
 template <class T> static int rn_alloc(RnnoiseBatch *r, T **p, size_t n) {
     void *q = nullptr;
@@ -547,9 +551,10 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_pfeat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemAna);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_pitch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemPitch);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_synth, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemSyn);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(1));
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(2));
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(4));
+#define FVAD_RNN_ATTR(RR, GG)                                                                                            \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<RR, GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(RR * GG));
+        FVAD_RNN_VARIANTS(FVAD_RNN_ATTR)
+#undef FVAD_RNN_ATTR
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBiquadSmemHog);
         if (e != cudaSuccess) rc = set_error(FVAD_ECUDA, "cudaFuncSetAttribute: %s (is this an sm_100 device?)", cudaGetErrorString(e));
     }
@@ -616,16 +621,24 @@ int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     FVAD_TRY(rn_check(r, slot, Qs));
     if (Qs == 0) return FVAD_OK;
     RnSlot &s = r->slots[slot];
-    // States per CTA: 1 while every state can have an SM of its own (shortest chain), then 2, then 4.
-    // FVAD_RNN_R overrides (tests exercise every variant on a handful of states).
+    // States per SM decide the shape: R states share a group's weight fetches, G groups fill each other's narrow layers.
+    // One state per SM: the shortest chain wins (R = G = 1).  FVAD_RNN_R / FVAD_RNN_G override (tests exercise every
+    // variant on a handful of states).
     const size_t sms = (size_t)device_sm_count(r->device);
-    int R = r->N <= sms ? 1 : r->N <= 2 * sms ? 2 : 4;
+    const size_t per_sm = ceil_div(r->N, sms);
+    int R = per_sm <= 3 ? 1 : per_sm <= 6 ? 2 : 4;
+    int G = per_sm <= 1 ? 1 : per_sm == 2 || per_sm == 4 || per_sm == 7 || per_sm == 8 ? 2 : 3;
     if (const char *e = getenv("FVAD_RNN_R")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) R = v; }
-    const unsigned grid = (unsigned)ceil_div(r->N, (size_t)R);
-#define FVAD_RNN_GO(RR)                                                                                                  \
-    FVAD_LAUNCH_NAMED("k_rn_rnn", k_rn_rnn<RR>, grid, kRnnThreads, smem_rnn(RR), st, r->tab.weights2, r->tab.bias,        \
-                      r->tab.t.tansig, s.feat, s.nzlist, s.nz_tile, r->persist, r->Qcap, r->N, s.gains, s.vad)
-    if (R == 1) FVAD_RNN_GO(1); else if (R == 2) FVAD_RNN_GO(2); else FVAD_RNN_GO(4);
+    if (const char *e = getenv("FVAD_RNN_G")) { const int v = atoi(e); if (v >= 1 && v <= 3) G = v; }
+    const unsigned grid = (unsigned)ceil_div(r->N, (size_t)R * G);
+    bool launched = false;
+#define FVAD_RNN_GO(RR, GG)                                                                                              \
+    if (!launched && R == RR && G == GG) {                                                                               \
+        launched = true;                                                                                                 \
+        FVAD_LAUNCH_NAMED("k_rn_rnn", (k_rn_rnn<RR, GG>), grid, kRnnThreads * GG, smem_rnn(RR * GG), st, r->tab.weights2,  \
+                          r->tab.bias, r->tab.t.tansig, s.feat, s.nzlist, s.nz_tile, r->persist, r->Qcap, r->N, s.gains, s.vad); \
+    }
+    FVAD_RNN_VARIANTS(FVAD_RNN_GO)
 #undef FVAD_RNN_GO
     FVAD_CUDA_TRY(cudaGetLastError());
     return FVAD_OK;

@@ -10,13 +10,14 @@ from conftest import synth, assert_segments_equal
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("rnn_r", [None, 2, 4])
-def test_denoiser_batch_bit_exact(fv, checker, rnn_r, monkeypatch):
-    """rnn_r forces the RNN kernel variant that walks 2 / 4 states per CTA in lock-step (chosen by itself only beyond
-    148 states); 5 states leave the last CTA partly filled and the streams' silent frames make the states' frame counts
-    differ, so idle states are exercised."""
-    if rnn_r:
-        monkeypatch.setenv("FVAD_RNN_R", str(rnn_r))
+@pytest.mark.parametrize("rnn_rg", [None, (2, 1), (4, 1), (1, 2), (1, 3), (2, 2), (2, 3), (4, 2), (4, 3)])
+def test_denoiser_batch_bit_exact(fv, checker, rnn_rg, monkeypatch):
+    """rnn_rg forces the RNN kernel shape: G independent thread groups per CTA, each walking R states in lock-step
+    (chosen by itself only beyond 148 states); 5 states leave the last group / CTA partly filled or empty and the
+    streams' silent frames make the states' frame counts differ, so idle states and idle groups are exercised."""
+    if rnn_rg:
+        monkeypatch.setenv("FVAD_RNN_R", str(rnn_rg[0]))
+        monkeypatch.setenv("FVAD_RNN_G", str(rnn_rg[1]))
     S, secs = 5, 8
     pcm = np.stack([synth(fv, 20 + s, secs) for s in range(S)])
     d = fv.DenoiserBatch(S)
