@@ -21,12 +21,18 @@ struct fvad_batch {
     std::vector<fvad_vad_machine_config> machine_cfgs;   // [0] main, [1..] alt
     size_t S = 0, C = 0, rows = 0;
     int device = 0;
-    // Four stage streams (wavefront over tiles): sA biquad, sB analysis/pitch/features, sC RNN, stream (= stage D)
-    // synthesis + STFT + VADMachine.  `stream` is the batch's main stream: results become visible in its order.
-    cudaStream_t stream = nullptr, sA = nullptr, sB = nullptr, sC = nullptr;
+    // Six stage streams (wavefront over tiles): sA biquad, sB analysis/pitch, sB2 pitch decision scan + features, sC RNN,
+    // stream (= stage D) synthesis + STFT, sE VADMachine.  The latency-bound scans (pitch decision, VADMachine: one thread
+    // per stream walking the tile's frames) have stages of their own so that the frame-parallel kernels of the next tile
+    // run beside them instead of behind them.  `stream` is the batch's main stream: it joins sE at the end of every push,
+    // so results become visible in its order.
+    cudaStream_t stream = nullptr, sA = nullptr, sB = nullptr, sB2 = nullptr, sC = nullptr, sE = nullptr;
     static constexpr int kMaxSlots = 8;
     int n_slots = 1;
-    cudaEvent_t evA[kMaxSlots] = {}, evB[kMaxSlots] = {}, evC[kMaxSlots] = {}, evD[kMaxSlots] = {};
+    cudaEvent_t evA[kMaxSlots] = {}, evB1[kMaxSlots] = {}, evB[kMaxSlots] = {}, evC[kMaxSlots] = {}, evD[kMaxSlots] = {};
+    cudaEvent_t evS[2] = {}, evE[2] = {};   // per parity of the STFT-rate buffers: produced (stage D) / consumed (stage E)
+    unsigned long long stft_tile_no = 0;    // tiles that reached the machines: parity = stft_tile_no & 1
+    int e_pending = -1;                     // parity whose evE the main stream has not joined yet
     unsigned long long tile_no = 0;
     float *d_ratio_slot[kMaxSlots] = {};   // [S][tile_frames] channel-volume ratio per 480-frame, stage A -> D
     bool use_denoiser = true;
@@ -54,8 +60,8 @@ struct fvad_batch {
     const StftTables *tabs = nullptr;
     StftBands bands{};
     size_t max_stft = 0;           // STFT frames per row per tile
-    float *d_band = nullptr;       // [n_bands][rows][max_stft]
-    float *d_ratio_stft = nullptr, *d_vad_stft = nullptr;   // [S][max_stft]
+    float *d_band = nullptr;       // [2][n_bands][rows][max_stft]   (two parities: stage D writes one while stage E reads the other)
+    float *d_ratio_stft = nullptr, *d_vad_stft = nullptr;   // [2][S][max_stft]
     float *d_spectra = nullptr;    // trace only: [rows][max_stft][1025]
     int n_machines = 0;
     VadmParams *d_params = nullptr;
@@ -129,18 +135,19 @@ extern "C" void fvad_batch_destroy(fvad_batch *b) {
     if (!b) return;
     {
         DeviceGuard g(b->device);
-        for (cudaStream_t st : {b->sA, b->sB, b->sC, b->stream}) if (st) cudaStreamSynchronize(st);
+        for (cudaStream_t st : {b->sA, b->sB, b->sB2, b->sC, b->sE, b->stream}) if (st) cudaStreamSynchronize(st);
         if (b->rn) rnnoise_batch_destroy(b->rn);
         for (int i = 0; i < fvad_batch::kMaxSlots; i++) {
             cudaFree(b->d_ratio_slot[i]);
-            for (cudaEvent_t e : {b->evA[i], b->evB[i], b->evC[i], b->evD[i]}) if (e) cudaEventDestroy(e);
+            for (cudaEvent_t e : {b->evA[i], b->evB1[i], b->evB[i], b->evC[i], b->evD[i]}) if (e) cudaEventDestroy(e);
         }
+        for (cudaEvent_t e : {b->evS[0], b->evS[1], b->evE[0], b->evE[1]}) if (e) cudaEventDestroy(e);
         cudaFree(b->d_work); cudaFree(b->d_carry); cudaFree(b->d_den); cudaFree(b->d_den_carry);
         cudaFree(b->d_ratio480); cudaFree(b->d_vad480); cudaFree(b->d_band); cudaFree(b->d_ratio_stft);
         cudaFree(b->d_vad_stft); cudaFree(b->d_spectra); cudaFree(b->d_params); cudaFree(b->d_states);
         cudaFree(b->d_rings); cudaFree(b->d_segs); cudaFree(b->d_seg_count); cudaFree(b->d_events);
         cudaFree(b->d_event_count); cudaFree(b->d_trace);
-        for (cudaStream_t st : {b->sA, b->sB, b->sC}) if (st && st != b->stream) cudaStreamDestroy(st);
+        for (cudaStream_t st : {b->sA, b->sB, b->sB2, b->sC, b->sE}) if (st && st != b->stream) cudaStreamDestroy(st);
         if (b->stream) cudaStreamDestroy(b->stream);
     }
     delete b;
@@ -184,7 +191,7 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
         return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
     if (getenv("FVAD_SERIAL_STAGES")) {
         // measurement aid: all four stages on one stream, so the per-kernel event times are free of overlap
-        b->sA = b->sB = b->sC = b->stream;
+        b->sA = b->sB = b->sB2 = b->sC = b->sE = b->stream;
     } else {
         // Stage A carries the chain that sets the pace, so its stream gets the highest priority: without it the tile's
         // small stage-A kernels queue behind the ten-thousands of CTAs stage B of the previous tile has just launched
@@ -197,7 +204,9 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
         auto prio = [&](int rank) { const int p = hi + rank; return p > lo ? lo : p; };
         if (cudaStreamCreateWithPriority(&b->sA, cudaStreamNonBlocking, prio(0)) != cudaSuccess ||
             cudaStreamCreateWithPriority(&b->sC, cudaStreamNonBlocking, prio(1)) != cudaSuccess ||
-            cudaStreamCreateWithPriority(&b->sB, cudaStreamNonBlocking, prio(2)) != cudaSuccess)
+            cudaStreamCreateWithPriority(&b->sB, cudaStreamNonBlocking, prio(2)) != cudaSuccess ||
+            cudaStreamCreateWithPriority(&b->sB2, cudaStreamNonBlocking, prio(2)) != cudaSuccess ||
+            cudaStreamCreateWithPriority(&b->sE, cudaStreamNonBlocking, prio(2)) != cudaSuccess)
             return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
     }
     {
@@ -205,9 +214,12 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
         int ns = es ? atoi(es) : 3;
         b->n_slots = ns < 1 ? 1 : ns > fvad_batch::kMaxSlots ? fvad_batch::kMaxSlots : ns;
         for (int i = 0; i < b->n_slots; i++)
-            for (cudaEvent_t *e : {&b->evA[i], &b->evB[i], &b->evC[i], &b->evD[i]})
+            for (cudaEvent_t *e : {&b->evA[i], &b->evB1[i], &b->evB[i], &b->evC[i], &b->evD[i]})
                 if (cudaEventCreateWithFlags(e, cudaEventDisableTiming) != cudaSuccess)
                     return fail(set_error(FVAD_ECUDA, "cudaEventCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
+        for (cudaEvent_t *e : {&b->evS[0], &b->evS[1], &b->evE[0], &b->evE[1]})
+            if (cudaEventCreateWithFlags(e, cudaEventDisableTiming) != cudaSuccess)
+                return fail(set_error(FVAD_ECUDA, "cudaEventCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
     }
     if ((rc = stft_tables_get(device, &b->tabs)) != FVAD_OK) return fail(rc);
 
@@ -270,9 +282,9 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
     } else {
         b->max_stft = tf;
     }
-    if ((rc = dmalloc(&b->d_band, (size_t)b->bands.n_bands * b->rows * b->max_stft)) != FVAD_OK) return fail(rc);
-    if ((rc = dmalloc(&b->d_ratio_stft, b->S * b->max_stft)) != FVAD_OK) return fail(rc);
-    if ((rc = dmalloc(&b->d_vad_stft, b->S * b->max_stft)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_band, 2 * (size_t)b->bands.n_bands * b->rows * b->max_stft)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_ratio_stft, 2 * b->S * b->max_stft)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_vad_stft, 2 * b->S * b->max_stft)) != FVAD_OK) return fail(rc);
     if ((rc = dmalloc(&b->d_params, (size_t)b->n_machines)) != FVAD_OK) return fail(rc);
     if ((rc = dmalloc(&b->d_states, b->h_states0.size())) != FVAD_OK) return fail(rc);
     if ((rc = dmalloc(&b->d_rings, b->h_rings0.size())) != FVAD_OK) return fail(rc);
@@ -304,6 +316,7 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
 // ------------------------------------------------------------------------------------------
 static int trace_tile(fvad_batch *b, size_t F, size_t J, size_t den_before) {
     FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
+    if (b->sE) FVAD_CUDA_TRY(cudaStreamSynchronize(b->sE));   // the records trace is written by the machines
     if ((b->trace_flags & FVAD_TRACE_RECORDS) && J) {
         std::vector<fvad_stft_record> tmp(J);
         for (size_t s = 0; s < b->S; s++) {
@@ -337,17 +350,21 @@ static int trace_tile(fvad_batch *b, size_t F, size_t J, size_t den_before) {
     return FVAD_OK;
 }
 
-static int run_machines(fvad_batch *b, const float *d_vad, unsigned long long first_index, size_t J) {
+static float *band_buf(fvad_batch *b, int par) { return b->d_band + (size_t)par * b->bands.n_bands * b->rows * b->max_stft; }
+static float *ratio_buf(fvad_batch *b, int par) { return b->d_ratio_stft + (size_t)par * b->S * b->max_stft; }
+static float *vad_buf(fvad_batch *b, int par) { return b->d_vad_stft + (size_t)par * b->S * b->max_stft; }
+
+static int run_machines(fvad_batch *b, int par, bool with_vad, unsigned long long first_index, size_t J, cudaStream_t st) {
     VadmIo io{};
-    io.band = b->d_band; io.band_rows = b->rows; io.band_frame_stride = b->max_stft;
-    io.vol_ratio = b->d_ratio_stft; io.vad = d_vad; io.ratio_stride = b->max_stft;
+    io.band = band_buf(b, par); io.band_rows = b->rows; io.band_frame_stride = b->max_stft;
+    io.vol_ratio = ratio_buf(b, par); io.vad = with_vad ? vad_buf(b, par) : nullptr; io.ratio_stride = b->max_stft;
     io.n_channels = (int)b->C;
     io.first_index = first_index; io.index_step = (unsigned long long)b->fft_size; io.n_frames = J;
     io.segs = b->d_segs; io.seg_count = b->d_seg_count; io.seg_cap = b->seg_cap;
     io.events = b->d_events; io.event_count = b->d_event_count; io.event_cap = b->event_cap;
     io.trace = (b->trace_flags & FVAD_TRACE_RECORDS) ? b->d_trace : nullptr;
     io.trace_stride = b->max_stft; io.trace_offset = 0;
-    return vadm_launch(b->d_params, b->d_states, b->d_rings, b->S, b->n_machines, io, b->stream);
+    return vadm_launch(b->d_params, b->d_states, b->d_rings, b->S, b->n_machines, io, st);
 }
 
 static int process_tile(fvad_batch *b, size_t m) {
@@ -362,7 +379,7 @@ static int process_tile(fvad_batch *b, size_t m) {
             FVAD_TRY(rms_ratio_launch(b->d_work, b->work_cap, b->S, (int)b->C, F, b->fft_size, b->d_ratio_stft, b->max_stft, 0, sD));
             FVAD_TRY(stft_launch(*b->tabs, b->d_work, b->rows, b->work_cap, F, b->fft_size, b->bands, b->d_band, b->max_stft, 0,
                                  spec, nullptr, 0.f, b->device, sD));
-            FVAD_TRY(run_machines(b, nullptr, b->read_count, J));
+            FVAD_TRY(run_machines(b, 0, false, b->read_count, J, sD));
         } else {
             // ---- wavefront: stage X of this tile follows stage X of the previous tile (stream order) and
             // stage X-1 of this tile (event); a slot is reused only after its previous tile left stage D.
@@ -373,10 +390,14 @@ static int process_tile(fvad_batch *b, size_t m) {
             FVAD_TRY(rms_ratio_launch(b->d_work, b->work_cap, b->S, (int)b->C, F, kRnFrame, b->d_ratio_slot[slot], b->tile_frames, 0, sA));
             FVAD_TRY(rnnoise_stage_a(b->rn, slot, b->d_work, b->work_cap, (int)b->C, F, sA));
             FVAD_CUDA_TRY(cudaEventRecord(b->evA[slot], sA));
-            // stage B (sB)
+            // stage B1 (sB): analysis + pitch correlations, frame-parallel
             FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sB, b->evA[slot], 0));
-            FVAD_TRY(rnnoise_stage_b(b->rn, slot, F * b->C, b->sB));
-            FVAD_CUDA_TRY(cudaEventRecord(b->evB[slot], b->sB));
+            FVAD_TRY(rnnoise_stage_b1(b->rn, slot, F * b->C, b->sB));
+            FVAD_CUDA_TRY(cudaEventRecord(b->evB1[slot], b->sB));
+            // stage B2 (sB2): pitch decision scan, pitch features, cepstral features
+            FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sB2, b->evB1[slot], 0));
+            FVAD_TRY(rnnoise_stage_b2(b->rn, slot, F * b->C, b->sB2));
+            FVAD_CUDA_TRY(cudaEventRecord(b->evB[slot], b->sB2));
             // stage C (sC)
             FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sC, b->evB[slot], 0));
             FVAD_TRY(rnnoise_stage_c(b->rn, slot, F * b->C, b->sC));
@@ -390,11 +411,18 @@ static int process_tile(fvad_batch *b, size_t m) {
             const size_t den_avail = b->den_carry + F * kRnFrame;
             J = den_avail / b->fft_size;
             if (J > 0) {
+                // stage E (sE): the machines read this parity's STFT-rate buffers while stage D of the next tile fills the other
+                const int par = (int)(b->stft_tile_no++ & 1);
+                FVAD_CUDA_TRY(cudaStreamWaitEvent(sD, b->evE[par], 0));        // the machines of two tiles ago are done with them
                 FVAD_TRY(reframe_launch(b->d_ratio480, b->d_vad480, b->stride480, b->base480, fvad_batch::kHist480, b->S,
-                                        b->stft_done, J, b->fft_size, b->d_ratio_stft, b->d_vad_stft, b->max_stft, sD));
-                FVAD_TRY(stft_launch(*b->tabs, b->d_den, b->rows, b->den_cap, J, b->fft_size, b->bands, b->d_band, b->max_stft, 0,
+                                        b->stft_done, J, b->fft_size, ratio_buf(b, par), vad_buf(b, par), b->max_stft, sD));
+                FVAD_TRY(stft_launch(*b->tabs, b->d_den, b->rows, b->den_cap, J, b->fft_size, b->bands, band_buf(b, par), b->max_stft, 0,
                                      spec, nullptr, 0.f, b->device, sD));
-                FVAD_TRY(run_machines(b, b->d_vad_stft, b->stft_done * (unsigned long long)b->fft_size, J));
+                FVAD_CUDA_TRY(cudaEventRecord(b->evS[par], sD));
+                FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sE, b->evS[par], 0));
+                FVAD_TRY(run_machines(b, par, true, b->stft_done * (unsigned long long)b->fft_size, J, b->sE));
+                FVAD_CUDA_TRY(cudaEventRecord(b->evE[par], b->sE));
+                b->e_pending = par;
             }
             if (b->trace_flags) FVAD_TRY(trace_tile(b, F, J, den_before));
             const size_t tail = den_avail - J * b->fft_size;
@@ -423,6 +451,14 @@ static int process_tile(fvad_batch *b, size_t m) {
     return FVAD_OK;
 }
 
+// The main stream waits for the machines of the last tile (stage E): whoever synchronises with, or records an event on,
+// the batch's stream after a push sees every segment that push produced.
+static int join_machines(fvad_batch *b) {
+    if (b->e_pending >= 0 && b->sE != b->stream) FVAD_CUDA_TRY(cudaStreamWaitEvent(b->stream, b->evE[b->e_pending], 0));
+    b->e_pending = -1;
+    return FVAD_OK;
+}
+
 static int ensure_trace_buffers(fvad_batch *b) {
     if ((b->trace_flags & FVAD_TRACE_RECORDS) && !b->d_trace) FVAD_TRY(dmalloc(&b->d_trace, b->S * b->max_stft));
     if ((b->trace_flags & FVAD_TRACE_SPECTRA) && !b->d_spectra) FVAD_TRY(dmalloc(&b->d_spectra, b->rows * b->max_stft * (size_t)kBins));
@@ -444,6 +480,7 @@ extern "C" int fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n,
         FVAD_TRY(process_tile(b, m));
         off += m;
     }
+    FVAD_TRY(join_machines(b));
     b->total_write_count += n;
     // input is borrowed only until return (AudioPipeline.pushSamples copies into its ring): wait for the
     // input-side stream only; the later stages keep running behind the caller's back until fvad_batch_sync
@@ -466,6 +503,7 @@ extern "C" int fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t 
         FVAD_TRY(process_tile(b, m));
         off += m;
     }
+    FVAD_TRY(join_machines(b));
     b->total_write_count += n;
     return FVAD_OK;
 }
@@ -512,14 +550,14 @@ extern "C" int fvad_batch_sync(fvad_batch *b) {
 extern "C" int fvad_batch_reset(fvad_batch *b) {
     if (!b) return set_error(FVAD_EINVALID_ARGUMENT, "null batch");
     DeviceGuard g(b->device);
-    for (cudaStream_t st : {b->sA, b->sB, b->sC, b->stream}) FVAD_CUDA_TRY(cudaStreamSynchronize(st));
+    for (cudaStream_t st : {b->sA, b->sB, b->sB2, b->sC, b->sE, b->stream}) FVAD_CUDA_TRY(cudaStreamSynchronize(st));
     FVAD_TRY(upload_machine_state(b));
     if (b->use_denoiser) {
         FVAD_TRY(rnnoise_batch_reset(b->rn, b->stream));
         FVAD_CUDA_TRY(cudaMemsetAsync(b->d_ratio480, 0, sizeof(float) * b->S * b->stride480, b->stream));
         FVAD_CUDA_TRY(cudaMemsetAsync(b->d_vad480, 0, sizeof(float) * b->S * b->stride480, b->stream));
     }
-    b->carry_len = 0; b->den_carry = 0; b->base480 = 0; b->tile_no = 0;
+    b->carry_len = 0; b->den_carry = 0; b->base480 = 0; b->tile_no = 0; b->stft_tile_no = 0; b->e_pending = -1;
     b->total_write_count = b->read_count = b->stft_done = 0;
     for (auto &v : b->segs) v.clear();
     for (auto &v : b->events) v.clear();

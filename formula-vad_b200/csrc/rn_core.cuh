@@ -46,6 +46,25 @@ __host__ __device__ constexpr int eband(int i) {          // denoise.c:73-76
          : i == 17 ? 40 : i == 18 ? 48 : i == 19 ? 60 : i == 20 ? 78 : 100;
 }
 
+// The same table for a run-time index without branches (a switch over a lane's band index compiles to a jump table whose
+// 22 targets the lanes of a warp visit one after the other).
+__host__ __device__ constexpr int eband_rt(int i) {
+    int e = i;
+    e = i > 8 ? 2 * i - 8 : e;
+    e = i > 12 ? 4 * i - 32 : e;
+    e = i > 15 ? 6 * i - 62 : e;
+    e = i == 18 ? 48 : e;
+    e = i == 19 ? 60 : e;
+    e = i == 20 ? 78 : e;
+    e = i == 21 ? 100 : e;
+    return e;
+}
+constexpr bool eband_rt_ok() {
+    for (int i = 0; i < 22; i++) if (eband_rt(i) != eband(i)) return false;
+    return true;
+}
+static_assert(eband_rt_ok(), "eband_rt must reproduce eband5ms");
+
 // ------------------------------------------------------------------------------------------
 // 960-point Opus FFT (kiss_fft.c:518-586) on a warp; data in scratch at padded slots
 // ------------------------------------------------------------------------------------------
@@ -155,7 +174,7 @@ template <class SX, class SP, bool CORR>
 RN_HD float band_chain(const Tables &t, SX X, SP P, int b) {
     float s = 0;
     if (b > 0) {
-        const int lo = eband(b - 1) << 2, hi = eband(b) << 2;
+        const int lo = eband_rt(b - 1) << 2, hi = eband_rt(b) << 2;
         for (int k = lo; k < hi; k++) {
             cpx x = X[k];
             float tmp;
@@ -165,7 +184,7 @@ RN_HD float band_chain(const Tables &t, SX X, SP P, int b) {
         }
     }
     if (b < kNB - 1) {
-        const int lo = eband(b) << 2, hi = eband(b + 1) << 2;
+        const int lo = eband_rt(b) << 2, hi = eband_rt(b + 1) << 2;
         for (int k = lo; k < hi; k++) {
             cpx x = X[k];
             float tmp;
@@ -183,15 +202,30 @@ RN_HD float band_chain(const Tables &t, SX X, SP P, int b) {
 RN_HD float band_chain_pre(const Tables &t, const float *e, int b) {
     float s = 0;
     if (b > 0) {
-        const int lo = eband(b - 1) << 2, hi = eband(b) << 2;
+        const int lo = eband_rt(b - 1) << 2, hi = eband_rt(b) << 2;
         for (int k = lo; k < hi; k++) s += t.frac[k] * e[k];
     }
     if (b < kNB - 1) {
-        const int lo = eband(b) << 2, hi = eband(b + 1) << 2;
+        const int lo = eband_rt(b) << 2, hi = eband_rt(b + 1) << 2;
         for (int k = lo; k < hi; k++) s += t.omf[k] * e[k];
     }
     if (b == 0 || b == kNB - 1) s *= 2;
     return s;
+}
+// Two such chains over the same bins (band energy of P and band correlation X.P) walked together: the weights, the
+// indices and the loop are shared, each sum is still its own in-order chain.
+RN_HD void band_chain_pre2(const Tables &t, const float *e0, const float *e1, int b, float &s0, float &s1) {
+    float a = 0, c = 0;
+    if (b > 0) {
+        const int lo = eband_rt(b - 1) << 2, hi = eband_rt(b) << 2;
+        for (int k = lo; k < hi; k++) { const float w = t.frac[k]; a += w * e0[k]; c += w * e1[k]; }
+    }
+    if (b < kNB - 1) {
+        const int lo = eband_rt(b) << 2, hi = eband_rt(b + 1) << 2;
+        for (int k = lo; k < hi; k++) { const float w = t.omf[k]; a += w * e0[k]; c += w * e1[k]; }
+    }
+    if (b == 0 || b == kNB - 1) { a *= 2; c *= 2; }
+    s0 = a; s1 = c;
 }
 // per-bin products live in the upper half of the FFT buffer: bins 0..480 occupy slots <= 510, floats from 1040 on are free
 constexpr int kBandE = 1040;
@@ -730,8 +764,8 @@ RN_HD void pfeat_warp(const Tables &t, const float *hpb, int q, int pitch_index,
     RN_END
     RN_PHASE
         if (lane < kNB) {
-            const float ep = band_chain_pre(t, be, lane);
-            float exp_ = band_chain_pre(t, bc, lane);
+            float ep, exp_;
+            band_chain_pre2(t, be, bc, lane, ep, exp_);
             exp_ = (float)(exp_ / sqrt(.001 + Exq[lane] * ep));        // denoise.c:343
             misc[lane] = ep; misc[32 + lane] = exp_;
             Epq[lane] = ep; Expq[lane] = exp_;

@@ -240,22 +240,25 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_analysis(Tables t, con
     analysis_warp(t, hp + n * hp_stride, q, X + f * kFreq, Ex + f * kNB, ceps + f * kNB, sil + f, smem + (size_t)w * kScrAna);
 }
 
-__global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_pitch(Tables t, const float *__restrict__ hp, size_t hp_stride, size_t N,
-                                                                int Q, size_t Qcap, PitchCand *cand) {
+// F frames per CTA (F warps): the few-lane chains of the F frames are pooled (rn_core.cuh pitch_blk), so a larger F fills
+// the pooled warps better -- 5F autocorrelation lanes, F scan lanes, 12F fine-search lanes.
+template <int F>
+__global__ void __launch_bounds__(32 * F) k_rn_pitch(Tables t, const float *__restrict__ hp, size_t hp_stride, size_t N,
+                                                     int Q, size_t Qcap, PitchCand *cand) {
     extern __shared__ float smem[];
     (void)t;
-    const float *xs[kWarpsPerCta];
-    PitchCand *outs[kWarpsPerCta];
-    const size_t id0 = (size_t)blockIdx.x * kWarpsPerCta, total = N * (size_t)Q;
+    const float *xs[F];
+    PitchCand *outs[F];
+    const size_t id0 = (size_t)blockIdx.x * F, total = N * (size_t)Q;
 #pragma unroll
-    for (int f = 0; f < kWarpsPerCta; f++) {                // a block past the end re-analyses its first frame, unwritten
+    for (int f = 0; f < F; f++) {                           // a block past the end re-analyses its first frame, unwritten
         const bool ok = id0 + f < total;
         const size_t id = ok ? id0 + f : id0;
         const size_t n = id / Q; const int q = (int)(id - n * Q);
         xs[f] = hp + n * hp_stride + (size_t)q * kFrame;
         outs[f] = ok ? cand + n * Qcap + q : nullptr;
     }
-    pitch_blk<kWarpsPerCta>(xs, outs, smem);
+    pitch_blk<F>(xs, outs, smem);
 }
 
 __global__ void k_rn_pitch_seq(const PitchCand *__restrict__ cand, size_t N, int Q, size_t Qcap, RnPersist *persist, int *pidx) {
@@ -488,7 +491,8 @@ __global__ void __launch_bounds__(256) k_rn_tail_carry(float *tail, int Q, size_
 #define FVAD_RNN_VARIANTS(X) X(1, 1) X(1, 2) X(1, 3) X(2, 1) X(2, 2) X(2, 3) X(4, 1) X(4, 2) X(4, 3)
 constexpr size_t kBiquadSmemHog = 200 * 1024;
 constexpr size_t kSmemAna = (size_t)kWarpsPerCta * kScrAna * sizeof(float);
-constexpr size_t kSmemPitch = (size_t)kWarpsPerCta * kScrPitch * sizeof(float);
+constexpr size_t smem_pitch(int F) { return (size_t)F * kScrPitch * sizeof(float); }
+#define FVAD_PITCH_VARIANTS(X) X(4) X(6) X(8)
 constexpr size_t kSmemSyn = (size_t)kWarpsPerCta * kScrSyn * sizeof(float);
 constexpr size_t smem_rnn(int states) { return ((kRnnWeights * 2 + 15) & ~15) + (560 + 208 + (size_t)states * kRv_end) * sizeof(float); }
 
@@ -549,7 +553,10 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
     if (rc == FVAD_OK) {
         cudaError_t e = cudaFuncSetAttribute(k_rn_analysis, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemAna);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_pfeat, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemAna);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_pitch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemPitch);
+#define FVAD_PITCH_ATTR(FF)                                                                                              \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_pitch<FF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_pitch(FF));
+        FVAD_PITCH_VARIANTS(FVAD_PITCH_ATTR)
+#undef FVAD_PITCH_ATTR
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_synth, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemSyn);
 #define FVAD_RNN_ATTR(RR, GG)                                                                                            \
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<RR, GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(RR * GG));
@@ -594,8 +601,12 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
     return FVAD_OK;
 }
 
-// Stage B: frame-parallel analysis, pitch and features (+ the two tiny sequential scans they need).
-int rnnoise_stage_b(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
+// Frames per pitch CTA.  Measured at 592 streams: F = 4 95.2k, 6 93.9k, 8 92.4k x real time -- the fuller pooled warps of
+// a larger F do not pay for the longer barrier waits and the coarser shared-memory granularity (FVAD_PITCH_F overrides).
+static int pitch_frames_per_cta(size_t, int) { return 4; }
+
+// Stage B1: frame-parallel analysis and pitch correlations (no carry between tiles).
+int rnnoise_stage_b1(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     FVAD_TRY(rn_check(r, slot, Qs));
     if (Qs == 0) return FVAD_OK;
     RnSlot &s = r->slots[slot];
@@ -604,7 +615,33 @@ int rnnoise_stage_b(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     const Tables &t = r->tab.t;
     const unsigned warp_grid = (unsigned)ceil_div(NQ, kWarpsPerCta);
     FVAD_LAUNCH(k_rn_analysis, warp_grid, 32 * kWarpsPerCta, kSmemAna, st, t, s.hp, r->hp_stride(), N, Q, Qcap, s.X, s.Ex, s.ceps, s.sil);
-    FVAD_LAUNCH(k_rn_pitch, warp_grid, 32 * kWarpsPerCta, kSmemPitch, st, t, s.hp, r->hp_stride(), N, Q, Qcap, s.cand);
+    {
+        int F = pitch_frames_per_cta(NQ, r->device);
+        if (const char *e = getenv("FVAD_PITCH_F")) { const int v = atoi(e); if (v == 4 || v == 6 || v == 8) F = v; }
+        bool launched = false;
+#define FVAD_PITCH_GO(FF)                                                                                                \
+        if (!launched && F == FF) {                                                                                      \
+            launched = true;                                                                                             \
+            FVAD_LAUNCH_NAMED("k_rn_pitch", k_rn_pitch<FF>, (unsigned)ceil_div(NQ, (size_t)FF), 32 * FF, smem_pitch(FF), st, t, s.hp, \
+                              r->hp_stride(), N, Q, Qcap, s.cand);                                                       \
+        }
+        FVAD_PITCH_VARIANTS(FVAD_PITCH_GO)
+#undef FVAD_PITCH_GO
+    }
+    FVAD_CUDA_TRY(cudaGetLastError());
+    return FVAD_OK;
+}
+
+// Stage B2: the pitch decision scan (frame-sequential, tiny) and what depends on it: pitch-lagged spectrum and features,
+// the non-silent frame ranks and the cepstral-ring features.  Carries: last_period/last_gain, nz_total, cepstral_mem.
+int rnnoise_stage_b2(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
+    FVAD_TRY(rn_check(r, slot, Qs));
+    if (Qs == 0) return FVAD_OK;
+    RnSlot &s = r->slots[slot];
+    const int Q = (int)Qs;
+    const size_t N = r->N, Qcap = r->Qcap, NQ = N * Qs;
+    const Tables &t = r->tab.t;
+    const unsigned warp_grid = (unsigned)ceil_div(NQ, kWarpsPerCta);
     FVAD_LAUNCH(k_rn_pitch_seq, (unsigned)ceil_div(N, 32), 32, 0, st, s.cand, N, Q, Qcap, r->persist, s.pidx);
     FVAD_LAUNCH(k_rn_pfeat, warp_grid, 32 * kWarpsPerCta, kSmemAna, st, t, s.hp, r->hp_stride(), N, Q, Qcap, s.pidx, s.X, s.Ex, s.P,
                 s.Ep, s.Exp, s.featB);
@@ -614,6 +651,11 @@ int rnnoise_stage_b(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     FVAD_LAUNCH(k_rn_ceps_carry, (unsigned)N, 256, 0, st, r->cepsc, s.nz_tile, Qcap);
     FVAD_CUDA_TRY(cudaGetLastError());
     return FVAD_OK;
+}
+
+int rnnoise_stage_b(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
+    FVAD_TRY(rnnoise_stage_b1(r, slot, Qs, st));
+    return rnnoise_stage_b2(r, slot, Qs, st);
 }
 
 // Stage C: the RNN, frame-sequential per state.

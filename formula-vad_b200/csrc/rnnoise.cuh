@@ -31,7 +31,9 @@ int rnnoise_batch_process(RnnoiseBatch *r, const float *d_in, size_t in_stride, 
 //   C: RNN (frame-sequential)               D: gains, synthesis, overlap-add, VAD minimum
 int rnnoise_n_slots(const RnnoiseBatch *r);
 int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stride, int n_channels, size_t n_tframes, cudaStream_t st);
-int rnnoise_stage_b(RnnoiseBatch *r, int slot, size_t n_vframes, cudaStream_t st);
+int rnnoise_stage_b(RnnoiseBatch *r, int slot, size_t n_vframes, cudaStream_t st);    // = b1 then b2 on one stream
+int rnnoise_stage_b1(RnnoiseBatch *r, int slot, size_t n_vframes, cudaStream_t st);   // analysis + pitch correlations
+int rnnoise_stage_b2(RnnoiseBatch *r, int slot, size_t n_vframes, cudaStream_t st);   // pitch decision scan + features
 int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t n_vframes, cudaStream_t st);
 int rnnoise_stage_d(RnnoiseBatch *r, int slot, int n_channels, size_t n_tframes, float *d_out, size_t out_stride, size_t out_off,
                     float *d_vad_min, float *d_vad_all, size_t vad_stride, size_t vad_off, cudaStream_t st);
