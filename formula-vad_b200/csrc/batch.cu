@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -187,26 +188,34 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
 
     int rc = FVAD_OK;
     auto fail = [&](int code) { fvad_batch_destroy(b); return code; };
-    if (cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess)
-        return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
-    if (getenv("FVAD_SERIAL_STAGES")) {
-        // measurement aid: all four stages on one stream, so the per-kernel event times are free of overlap
-        b->sA = b->sB = b->sB2 = b->sC = b->sE = b->stream;
-    } else {
-        // Stage A carries the chain that sets the pace, so its stream gets the highest priority: without it the tile's
-        // small stage-A kernels queue behind the ten-thousands of CTAs stage B of the previous tile has just launched
-        // (measured: ~5 ms per tile, 6 % of the step).  C before B before D for the same reason, in chain-length order.
-        // Only in the latency regime (common.cu: latency_regime): with hundreds of streams everything is throughput and
-        // favouring one stage costs 7 %.
+    {
+        // Stream priorities decide whose CTAs the block scheduler places first when SM resources free up; rank 0 = most urgent.
+        // Latency regime (few chains): stage A carries the chain that sets the pace, so it goes first -- without that the
+        // tile's small stage-A kernels queue behind the ten-thousands of CTAs stage B of the previous tile has just launched
+        // (measured: ~5 ms per tile, 6 % of the step); then C, then B, then D in chain-length order.
+        // Throughput regime (SMs saturated): what matters is that the SMALL kernels between the big ones (history copies,
+        // scans, carries: a few CTAs each) do not wait for a 30 000-CTA grid to be dispatched -- measured with
+        // FVAD_TIMELINE: a 10 us copy took 3 ms -- and that older tiles drain first, so later stages outrank earlier ones.
+        // FVAD_PRIO="a,b1,b2,c,d,e" overrides the ranks.
         int lo = 0, hi = 0;
         if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess) lo = hi = 0;      // hi = numerically lowest = most urgent
-        if (!latency_regime(n_streams, b->device)) hi = lo;
-        auto prio = [&](int rank) { const int p = hi + rank; return p > lo ? lo : p; };
-        if (cudaStreamCreateWithPriority(&b->sA, cudaStreamNonBlocking, prio(0)) != cudaSuccess ||
-            cudaStreamCreateWithPriority(&b->sC, cudaStreamNonBlocking, prio(1)) != cudaSuccess ||
-            cudaStreamCreateWithPriority(&b->sB, cudaStreamNonBlocking, prio(2)) != cudaSuccess ||
-            cudaStreamCreateWithPriority(&b->sB2, cudaStreamNonBlocking, prio(2)) != cudaSuccess ||
-            cudaStreamCreateWithPriority(&b->sE, cudaStreamNonBlocking, prio(2)) != cudaSuccess)
+        int rank[6] = {0, 2, 2, 1, 99, 2};                                               // A, B1, B2, C, D, E
+        if (!latency_regime(n_streams, b->device)) { const int thr[6] = {0, 5, 4, 3, 2, 1}; for (int i = 0; i < 6; i++) rank[i] = thr[i]; }
+        if (const char *e = getenv("FVAD_PRIO")) {
+            int v[6];
+            if (sscanf(e, "%d,%d,%d,%d,%d,%d", &v[0], &v[1], &v[2], &v[3], &v[4], &v[5]) == 6) for (int i = 0; i < 6; i++) rank[i] = v[i];
+        }
+        auto prio = [&](int r) { const int p = hi + (r < 0 ? 0 : r); return p > lo ? lo : p; };
+        if (cudaStreamCreateWithPriority(&b->stream, cudaStreamNonBlocking, prio(rank[4])) != cudaSuccess)
+            return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
+        if (getenv("FVAD_SERIAL_STAGES")) {
+            // measurement aid: all stages on one stream, so the per-kernel event times are free of overlap
+            b->sA = b->sB = b->sB2 = b->sC = b->sE = b->stream;
+        } else if (cudaStreamCreateWithPriority(&b->sA, cudaStreamNonBlocking, prio(rank[0])) != cudaSuccess ||
+                   cudaStreamCreateWithPriority(&b->sB, cudaStreamNonBlocking, prio(rank[1])) != cudaSuccess ||
+                   cudaStreamCreateWithPriority(&b->sB2, cudaStreamNonBlocking, prio(rank[2])) != cudaSuccess ||
+                   cudaStreamCreateWithPriority(&b->sC, cudaStreamNonBlocking, prio(rank[3])) != cudaSuccess ||
+                   cudaStreamCreateWithPriority(&b->sE, cudaStreamNonBlocking, prio(rank[5])) != cudaSuccess)
             return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
     }
     {

@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -104,6 +105,19 @@ int fvad_profile_report(char *buf, size_t cap) {
     std::map<std::string, std::pair<long, double>> agg;
     {
         std::lock_guard<std::mutex> lk(g_prof_mu);
+        // measurement aid: FVAD_TIMELINE=<file> writes every launch's start / end (ms since the first recorded launch),
+        // which shows how the stages of the wavefront overlap
+        if (const char *tl = getenv("FVAD_TIMELINE")) {
+            if (FILE *f = (buf && cap && !g_prof.empty()) ? fopen(tl, "w") : nullptr) {
+                fprintf(f, "kernel,start_ms,end_ms\n");
+                for (auto &r : g_prof) {
+                    float t0 = 0, t1 = 0;
+                    if (cudaEventElapsedTime(&t0, g_prof[0].a, r.a) == cudaSuccess && cudaEventElapsedTime(&t1, g_prof[0].a, r.b) == cudaSuccess)
+                        fprintf(f, "%s,%.4f,%.4f\n", r.name.c_str(), t0, t1);
+                }
+                fclose(f);
+            }
+        }
         for (auto &r : g_prof) {
             float ms = 0;
             if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) { agg[r.name].first++; agg[r.name].second += ms; }

@@ -109,8 +109,10 @@ static int rn_tables_get(int device, RnDevTables *out) {
 // the dependent chain.  A hazardous block is replayed by lane 0 with the reference's double arithmetic from
 // the recorded state; the replay reproduces the fast result unless the fast step was really wrong (a
 // ~2^-29 event per sample), in which case the block in flight is recomputed as well.
-constexpr int kBqBlock = 32, kBqBlocksPerFrame = kFrame / kBqBlock;
-__global__ void __launch_bounds__(64) k_rn_biquad(const float *__restrict__ in, size_t in_stride, int C, int Q,
+constexpr int kBqBlock = 48, kBqBlocksPerFrame = kFrame / kBqBlock;   // 48: the per-block costs (two barriers, input preload, verdict)
+constexpr int kBqThreads = 32 + ((kBqBlock + 31) / 32) * 32;          // are paid 10 instead of 15 times per frame
+static_assert(kFrame % kBqBlock == 0 && kBqBlock % 4 == 0, "blocks tile the frame");
+__global__ void __launch_bounds__(kBqThreads) k_rn_biquad(const float *__restrict__ in, size_t in_stride, int C, int Q,
                                                   RnPersist *persist, float *__restrict__ hp, size_t hp_stride, size_t N) {
     const size_t n = blockIdx.x;
     if (n >= N) return;
@@ -123,7 +125,7 @@ __global__ void __launch_bounds__(64) k_rn_biquad(const float *__restrict__ in, 
     float *dst = hp + n * hp_stride + kPHist;
     auto src = [&](int q) { return in + (n * C + (q % C)) * in_stride + (size_t)(q / C) * kFrame; };
     if (threadIdx.x < 2) FINAL[threadIdx.x] = 0;
-    if (Q > 0) for (int i = threadIdx.x; i < kFrame; i += 64) sx[0][i] = src(0)[i];
+    if (Q > 0) for (int i = threadIdx.x; i < kFrame; i += kBqThreads) sx[0][i] = src(0)[i];
     __syncthreads();
     const int G = Q * kBqBlocksPerFrame;
     float pf[kFrame / 32]; int pf_buf = -1;                        // warp 1: a frame in flight from global memory
@@ -169,23 +171,24 @@ __global__ void __launch_bounds__(64) k_rn_biquad(const float *__restrict__ in, 
                 for (int i = 0; i < kBqBlock; i++) xr[i] = xn[i];
             }
         } else {
-            if (pf_buf >= 0) {                                     // ---- the frame fetched one iteration ago lands in shared memory
+            const int v = (int)threadIdx.x - 32;                   // verification: one sample of the block per thread of warps >= 1
+            if (warp == 1 && pf_buf >= 0) {                        // ---- the frame fetched one iteration ago lands in shared memory
 #pragma unroll
                 for (int k = 0; k < kFrame / 32; k++) sx[pf_buf][lane + 32 * k] = pf[k];
                 pf_buf = -1;
             }
-            if (g >= 1 && g - 1 < G) {                             // ---- verification of block g-1
+            if (g >= 1 && g - 1 < G && v < kBqBlock) {             // ---- verification of block g-1
                 const int gv = g - 1, q = gv / kBqBlocksPerFrame, b0 = (gv - q * kBqBlocksPerFrame) * kBqBlock, par = gv & 1;
                 if (!FINAL[par]) {
-                    const float2 pre = P[par][lane], post = P[par][lane + 1];
+                    const float2 pre = P[par][v], post = P[par][v + 1];
                     float a = pre.x, b = pre.y;
-                    const float yv = biquad_step_eft(sx[q & 1][b0 + lane], a, b, hz);
+                    const float yv = biquad_step_eft(sx[q & 1][b0 + v], a, b, hz);
                     hz |= (__float_as_uint(a) != __float_as_uint(post.x)) |
                           (__float_as_uint(b) != __float_as_uint(post.y)) |
-                          (__float_as_uint(yv) != __float_as_uint(sy[q & 1][b0 + lane]));
+                          (__float_as_uint(yv) != __float_as_uint(sy[q & 1][b0 + v]));
                 }
             }
-            if (g >= 2) {                                          // ---- block g-2 is final: frame I/O at frame edges
+            if (warp == 1 && g >= 2) {                             // ---- block g-2 is final: frame I/O at frame edges
                 const int gf = g - 2, q = gf / kBqBlocksPerFrame;
                 if (gf - q * kBqBlocksPerFrame == kBqBlocksPerFrame - 1) {
                     for (int i = lane; i < kFrame; i += 32) dst[(size_t)q * kFrame + i] = sy[q & 1][i];
@@ -199,7 +202,7 @@ __global__ void __launch_bounds__(64) k_rn_biquad(const float *__restrict__ in, 
                     }
                 }
             }
-            if (g == 0 && Q > 1) {
+            if (warp == 1 && g == 0 && Q > 1) {
                 const float *s1 = src(1);
 #pragma unroll
                 for (int k = 0; k < kFrame / 32; k++) pf[k] = s1[lane + 32 * k];
@@ -224,6 +227,137 @@ __global__ void __launch_bounds__(64) k_rn_biquad(const float *__restrict__ in, 
         __syncthreads();                                           // replay results visible before anyone moves on
     }
     if (threadIdx.x == 0) { persist[n].biq[0] = m0; persist[n].biq[1] = m1; }
+}
+
+// Throughput regime (many states): the same protocol with a state per LANE.  Warp 0 walks the chains of 32 states in
+// lock-step (the fast step costs the warp the same instructions for 32 chains as for one -- with one chain per CTA the
+// biquad was a quarter of all instructions the GPU issued at 592 streams), warps 1..7 verify the previous block (state =
+// lane, the block's 32 samples dealt round-robin to the warps), store the block before that and fetch the next one.
+// A state whose block raised a hazard replays it on its own lane with the reference's double arithmetic while the other
+// lanes wait; the replay reproduces the fast result unless the fast step was really wrong, in which case that lane's
+// block in flight is recomputed as well.  Blocks sit in shared memory as [state][36] floats (16-byte rows: the chain lane
+// moves its 32 samples as eight 16-byte accesses, quarter-warp conflict-free); states before every sample as [sample][state].
+constexpr int kBqlStates = 32, kBqlWarps = 8, kBqlStride = 36, kBqlVer = kBqlWarps - 1;
+constexpr int kBqlBlock = 32, kBqlBlocksPerFrame = kFrame / kBqlBlock;
+__global__ void __launch_bounds__(32 * kBqlWarps) k_rn_biquad_lanes(const float *__restrict__ in, size_t in_stride, int C, int Q,
+                                                                    RnPersist *persist, float *__restrict__ hp, size_t hp_stride,
+                                                                    size_t N) {
+    __shared__ __align__(16) float sx[3][kBqlStates * kBqlStride];
+    __shared__ __align__(16) float sy[3][kBqlStates * kBqlStride];
+    __shared__ __align__(16) float2 P[2][(kBqlBlock + 1) * kBqlStates];
+    __shared__ int HZ[kBqlStates];
+    __shared__ int FINAL[2][kBqlStates];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t n0 = (size_t)blockIdx.x * kBqlStates;
+    const int G = Q * kBqlBlocksPerFrame;
+    const size_t n = n0 + lane;
+    float m0 = 0.0f, m1 = 0.0f;                                    // meaningful on warp 0: lane l carries state n0 + l
+    if (warp == 0 && n < N) { m0 = persist[n].biq[0]; m1 = persist[n].biq[1]; }
+    if (warp == 0) { HZ[lane] = 0; FINAL[0][lane] = 0; FINAL[1][lane] = 0; }
+    auto src = [&](size_t ns, int g) {
+        const int q = g / kBqlBlocksPerFrame, b0 = (g - q * kBqlBlocksPerFrame) * kBqlBlock;
+        return in + (ns * C + (q % C)) * in_stride + (size_t)(q / C) * kFrame + b0;
+    };
+    auto dst = [&](size_t ns, int g) {
+        const int q = g / kBqlBlocksPerFrame, b0 = (g - q * kBqlBlocksPerFrame) * kBqlBlock;
+        return hp + ns * hp_stride + kPHist + (size_t)q * kFrame + b0;
+    };
+    for (int s = warp; s < kBqlStates; s += kBqlWarps) sx[0][s * kBqlStride + lane] = (G > 0 && n0 + s < N) ? src(n0 + s, 0)[lane] : 0.0f;
+    __syncthreads();
+    for (int g = 0; g <= G + 1; g++) {
+        if (warp == 0) {
+            if (g < G) {                                           // ---- the chains: block g of 32 states
+                const int par = g & 1;
+                const float *xb = sx[g % 3] + lane * kBqlStride;
+                float *yb = sy[g % 3] + lane * kBqlStride;
+                float2 *Pb = P[par];
+                float xr[kBqlBlock];
+#pragma unroll
+                for (int i = 0; i < kBqlBlock; i += 4) {
+                    const float4 v = *reinterpret_cast<const float4 *>(xb + i);
+                    xr[i] = v.x; xr[i + 1] = v.y; xr[i + 2] = v.z; xr[i + 3] = v.w;
+                }
+                const float a0 = fabsf(m0), a1 = fabsf(m1);
+                if ((a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f)) {
+                    for (int i = 0; i < kBqlBlock; i++) yb[i] = biquad_step(xb[i], m0, m1);   // denormal tail of a silence
+                    FINAL[par][lane] = 1;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < kBqlBlock; i += 4) {
+                        float4 yy;
+                        Pb[(i + 0) * kBqlStates + lane] = make_float2(m0, m1); yy.x = biquad_step_fast(xr[i], m0, m1);
+                        Pb[(i + 1) * kBqlStates + lane] = make_float2(m0, m1); yy.y = biquad_step_fast(xr[i + 1], m0, m1);
+                        Pb[(i + 2) * kBqlStates + lane] = make_float2(m0, m1); yy.z = biquad_step_fast(xr[i + 2], m0, m1);
+                        Pb[(i + 3) * kBqlStates + lane] = make_float2(m0, m1); yy.w = biquad_step_fast(xr[i + 3], m0, m1);
+                        *reinterpret_cast<float4 *>(yb + i) = yy;
+                    }
+                    Pb[kBqlBlock * kBqlStates + lane] = make_float2(m0, m1);
+                    FINAL[par][lane] = 0;
+                }
+            }
+        } else {
+            const int vw = warp - 1;
+            constexpr int kPer = (kBqlStates + kBqlVer - 1) / kBqlVer;
+            float pre[kPer];                                        // block g+1 of this warp's states, in flight from global memory
+            const bool fetch = g + 1 < G;
+#pragma unroll
+            for (int k = 0; k < kPer; k++) {
+                const int s = vw + k * kBqlVer;
+                pre[k] = (fetch && s < kBqlStates && n0 + s < N) ? src(n0 + s, g + 1)[lane] : 0.0f;
+            }
+            if (g >= 1 && g - 1 < G) {                              // ---- verification of block g-1: state = lane
+                const int par = (g - 1) & 1;
+                if (!FINAL[par][lane]) {
+                    const float *xb = sx[(g - 1) % 3] + lane * kBqlStride, *yb = sy[(g - 1) % 3] + lane * kBqlStride;
+                    bool hz = false;
+                    for (int i = vw; i < kBqlBlock; i += kBqlVer) {
+                        const float2 pre_s = P[par][i * kBqlStates + lane], post = P[par][(i + 1) * kBqlStates + lane];
+                        float a = pre_s.x, b = pre_s.y;
+                        const float yv = biquad_step_eft(xb[i], a, b, hz);
+                        hz |= (__float_as_uint(a) != __float_as_uint(post.x)) | (__float_as_uint(b) != __float_as_uint(post.y)) |
+                              (__float_as_uint(yv) != __float_as_uint(yb[i]));
+                    }
+                    if (hz) HZ[lane] = 1;
+                }
+            }
+            if (g >= 2) {                                           // ---- block g-2 is final: out it goes
+                const float *yb = sy[(g - 2) % 3];
+                for (int s = vw; s < kBqlStates; s += kBqlVer)
+                    if (n0 + s < N) dst(n0 + s, g - 2)[lane] = yb[s * kBqlStride + lane];
+            }
+            if (fetch) {
+#pragma unroll
+                for (int k = 0; k < kPer; k++) {
+                    const int s = vw + k * kBqlVer;
+                    if (s < kBqlStates) sx[(g + 1) % 3][s * kBqlStride + lane] = pre[k];
+                }
+            }
+        }
+        __syncthreads();
+        if (warp == 0) {
+            if (g >= 1 && g - 1 < G && HZ[lane]) {                  // ---- replay of a hazardous block g-1, lane by lane
+                const int par = (g - 1) & 1;
+                float r0 = P[par][lane].x, r1 = P[par][lane].y;
+                const float *xb = sx[(g - 1) % 3] + lane * kBqlStride;
+                float *yb = sy[(g - 1) % 3] + lane * kBqlStride;
+                for (int i = 0; i < kBqlBlock; i++) yb[i] = biquad_step(xb[i], r0, r1);
+                const float2 end = P[par][kBqlBlock * kBqlStates + lane];
+                if (__float_as_uint(r0) != __float_as_uint(end.x) || __float_as_uint(r1) != __float_as_uint(end.y)) {
+                    // the fast step was wrong: block g (computed from its end state) is void, redo it from the true state
+                    m0 = r0; m1 = r1;
+                    if (g < G) {
+                        const float *xc = sx[g % 3] + lane * kBqlStride;
+                        float *yc = sy[g % 3] + lane * kBqlStride;
+                        for (int i = 0; i < kBqlBlock; i++) yc[i] = biquad_step(xc[i], m0, m1);
+                        FINAL[g & 1][lane] = 1;
+                    }
+                }
+            }
+            HZ[lane] = 0;
+        }
+        __syncthreads();
+    }
+    if (warp == 0 && n < N) { persist[n].biq[0] = m0; persist[n].biq[1] = m1; }
 }
 
 constexpr int kWarpsPerCta = 4;     // 4 warps x <= 12 KB scratch: such a CTA still fits beside the RNN CTA (174 KB of weights) on an SM
@@ -594,8 +728,19 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
     // the chain's SM -- the chain lane is issue-latency bound and loses ~13 % when frame-parallel kernels of other
     // stages share its scheduler.  Many chains (throughput regime): no reservation, so several chains and the
     // other stages' CTAs share an SM; reserving it there serialises the biquad against everything else.
-    const size_t hog = latency_regime(N, r->device) ? kBiquadSmemHog : 0;
-    FVAD_LAUNCH(k_rn_biquad, (unsigned)N, 64, hog, st, d_in, in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
+    const bool lat = latency_regime(N, r->device);
+    // A state per lane (k_rn_biquad_lanes) is opt-in: exact, and 8 x fewer instructions per sample, but measured no faster
+    // (592 streams: 76.7k vs 104.0k, 1184: 103.8k vs 102.9k x real time) -- a lane in the denormal tail of a silence or in
+    // a hazard replay holds up the 31 other chains of its warp, and the synthetic streams' silences overlap most of the time.
+    bool lanes = false;
+    if (const char *e = getenv("FVAD_BIQUAD_LANES")) lanes = atoi(e) != 0;
+    if (lanes) {
+        FVAD_LAUNCH_NAMED("k_rn_biquad", k_rn_biquad_lanes, (unsigned)ceil_div(N, (size_t)kBqlStates), 32 * kBqlWarps, 0, st, d_in,
+                          in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
+    } else {
+        const size_t hog = lat ? kBiquadSmemHog : 0;
+        FVAD_LAUNCH(k_rn_biquad, (unsigned)N, kBqThreads, hog, st, d_in, in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
+    }
     FVAD_LAUNCH(k_rn_hp_save, (unsigned)N, 256, 0, st, s.hp, r->hp_stride(), r->hp_hist, (int)Qs);
     FVAD_CUDA_TRY(cudaGetLastError());
     return FVAD_OK;

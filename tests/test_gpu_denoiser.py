@@ -35,6 +35,27 @@ def test_denoiser_batch_bit_exact(fv, checker, rnn_rg, monkeypatch):
     assert silent > 0 and voiced > 0, "input must exercise silent and voiced frames"
 
 
+def test_denoiser_biquad_state_per_lane(fv, checker, monkeypatch):
+    """The throughput-regime biquad (a state per lane, 32 states per CTA; chosen by itself only beyond 3/4 of the SM count)
+    forced on 37 states: the second CTA has 5 live lanes, the streams' digital silences exercise the denormal path and the
+    hazard replays are lane-divergent.  A second call continues from the carried filter state."""
+    monkeypatch.setenv("FVAD_BIQUAD_LANES", "1")
+    S, secs = 37, 6
+    pcm = np.stack([synth(fv, 60 + s, secs) for s in range(S)])
+    d = fv.DenoiserBatch(S)
+    out, vad = d.run(pcm)
+    pcm2 = np.stack([synth(fv, 60 + s, 1, first=secs * 48000) for s in range(S)])
+    out2, vad2 = d.run(pcm2)
+    silent = 0
+    for s in range(S):
+        wo, wv = checker.denoise_stream(np.concatenate([pcm[s], pcm2[s]]))
+        go, gv = np.concatenate([out[s], out2[s]]), np.concatenate([vad[s], vad2[s]])
+        assert np.array_equal(gv, wv), (s, np.nonzero(gv != wv)[0][:5])
+        assert np.array_equal(go, wo), (s, np.abs(go - wo).max())
+        silent += int((wv == 0).sum())
+    assert silent > 0, "input must exercise digital silence"
+
+
 def test_denoiser_single_frame_api(fv, checker):
     x = synth(fv, 33, 1.0)
     d = fv.Denoiser()
