@@ -109,52 +109,57 @@ static int rn_tables_get(int device, RnDevTables *out) {
 // the dependent chain.  A hazardous block is replayed by lane 0 with the reference's double arithmetic from
 // the recorded state; the replay reproduces the fast result unless the fast step was really wrong (a
 // ~2^-29 event per sample), in which case the block in flight is recomputed as well.
-constexpr int kBqBlock = 48, kBqBlocksPerFrame = kFrame / kBqBlock;   // 48: the per-block costs (two barriers, input preload, verdict)
-constexpr int kBqThreads = 32 + ((kBqBlock + 31) / 32) * 32;          // are paid 10 instead of 15 times per frame
-static_assert(kFrame % kBqBlock == 0 && kBqBlock % 4 == 0, "blocks tile the frame");
-__global__ void __launch_bounds__(kBqThreads) k_rn_biquad(const float *__restrict__ in, size_t in_stride, int C, int Q,
+// BQ = samples per block.  The per-block costs (two barriers, input preload, verdict) shrink with BQ, the chain lane's
+// registers (two blocks of inputs) and its unrolled loop body grow with it.  Measured, 20 streams, ms per 60 s tile: BQ = 32: 74.3,
+// 48: 69.6, 60: 77.7, 80: 86.6 (the unrolled body outgrows the instruction cache).  FVAD_BQ_BLOCK overrides.
+__host__ __device__ constexpr int bq_threads(int BQ) { return 32 + ((BQ + 31) / 32) * 32; }
+#define FVAD_BQ_VARIANTS(X) X(32) X(48) X(60)
+template <int BQ>
+__global__ void __launch_bounds__(bq_threads(BQ)) k_rn_biquad(const float *__restrict__ in, size_t in_stride, int C, int Q,
                                                   RnPersist *persist, float *__restrict__ hp, size_t hp_stride, size_t N) {
+    constexpr int kBPF = kFrame / BQ, kThreads = bq_threads(BQ);
+    static_assert(kFrame % BQ == 0 && BQ % 4 == 0, "blocks tile the frame");
     const size_t n = blockIdx.x;
     if (n >= N) return;
     __shared__ __align__(16) float sx[2][kFrame];
     __shared__ __align__(16) float sy[2][kFrame];
-    __shared__ __align__(16) float2 P[2][kBqBlock + 2];          // (m0, m1) before every sample of the block, + the end state
+    __shared__ __align__(16) float2 P[2][BQ + 2];          // (m0, m1) before every sample of the block, + the end state
     __shared__ int FINAL[2];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float m0 = persist[n].biq[0], m1 = persist[n].biq[1];         // meaningful on thread 0
     float *dst = hp + n * hp_stride + kPHist;
     auto src = [&](int q) { return in + (n * C + (q % C)) * in_stride + (size_t)(q / C) * kFrame; };
     if (threadIdx.x < 2) FINAL[threadIdx.x] = 0;
-    if (Q > 0) for (int i = threadIdx.x; i < kFrame; i += kBqThreads) sx[0][i] = src(0)[i];
+    if (Q > 0) for (int i = threadIdx.x; i < kFrame; i += kThreads) sx[0][i] = src(0)[i];
     __syncthreads();
-    const int G = Q * kBqBlocksPerFrame;
+    const int G = Q * kBPF;
     float pf[kFrame / 32]; int pf_buf = -1;                        // warp 1: a frame in flight from global memory
-    float xr[kBqBlock];                                            // thread 0: the block's input, fetched one block ahead
+    float xr[BQ];                                            // thread 0: the block's input, fetched one block ahead
     if (threadIdx.x == 0 && G > 0) {
 #pragma unroll
-        for (int i = 0; i < kBqBlock; i++) xr[i] = sx[0][i];
+        for (int i = 0; i < BQ; i++) xr[i] = sx[0][i];
     }
     for (int g = 0; g <= G + 1; g++) {
         bool hz = false;
         if (warp == 0) {
             if (lane == 0 && g < G) {                              // ---- the chain: block g
-                const int q = g / kBqBlocksPerFrame, b0 = (g - q * kBqBlocksPerFrame) * kBqBlock, par = g & 1;
+                const int q = g / kBPF, b0 = (g - q * kBPF) * BQ, par = g & 1;
                 float *yout = &sy[q & 1][b0];
-                float xn[kBqBlock];                                // next block's input: loaded before this block's stores queue up
+                float xn[BQ];                                // next block's input: loaded before this block's stores queue up
                 if (g + 1 < G) {
-                    const int q1 = (g + 1) / kBqBlocksPerFrame, b1 = (g + 1 - q1 * kBqBlocksPerFrame) * kBqBlock;
+                    const int q1 = (g + 1) / kBPF, b1 = (g + 1 - q1 * kBPF) * BQ;
 #pragma unroll
-                    for (int i = 0; i < kBqBlock; i++) xn[i] = sx[q1 & 1][b1 + i];
+                    for (int i = 0; i < BQ; i++) xn[i] = sx[q1 & 1][b1 + i];
                 }
                 const float a0 = fabsf(m0), a1 = fabsf(m1);
                 if ((a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f)) {
 #pragma unroll
-                    for (int i = 0; i < kBqBlock; i++) yout[i] = biquad_step(xr[i], m0, m1);   // denormal tail of a silence
+                    for (int i = 0; i < BQ; i++) yout[i] = biquad_step(xr[i], m0, m1);   // denormal tail of a silence
                     FINAL[par] = 1;
                 } else {
                     // one lane issues every shared-memory store of the block: pack 4 samples per store
 #pragma unroll
-                    for (int i = 0; i < kBqBlock; i += 4) {
+                    for (int i = 0; i < BQ; i += 4) {
                         float4 sa, sb, yy;
                         sa.x = m0; sa.y = m1; yy.x = biquad_step_fast(xr[i], m0, m1);
                         sa.z = m0; sa.w = m1; yy.y = biquad_step_fast(xr[i + 1], m0, m1);
@@ -164,11 +169,11 @@ __global__ void __launch_bounds__(kBqThreads) k_rn_biquad(const float *__restric
                         *reinterpret_cast<float4 *>(&P[par][i + 2]) = sb;
                         *reinterpret_cast<float4 *>(&yout[i]) = yy;
                     }
-                    P[par][kBqBlock] = make_float2(m0, m1);
+                    P[par][BQ] = make_float2(m0, m1);
                     FINAL[par] = 0;
                 }
 #pragma unroll
-                for (int i = 0; i < kBqBlock; i++) xr[i] = xn[i];
+                for (int i = 0; i < BQ; i++) xr[i] = xn[i];
             }
         } else {
             const int v = (int)threadIdx.x - 32;                   // verification: one sample of the block per thread of warps >= 1
@@ -177,8 +182,8 @@ __global__ void __launch_bounds__(kBqThreads) k_rn_biquad(const float *__restric
                 for (int k = 0; k < kFrame / 32; k++) sx[pf_buf][lane + 32 * k] = pf[k];
                 pf_buf = -1;
             }
-            if (g >= 1 && g - 1 < G && v < kBqBlock) {             // ---- verification of block g-1
-                const int gv = g - 1, q = gv / kBqBlocksPerFrame, b0 = (gv - q * kBqBlocksPerFrame) * kBqBlock, par = gv & 1;
+            if (g >= 1 && g - 1 < G && v < BQ) {             // ---- verification of block g-1
+                const int gv = g - 1, q = gv / kBPF, b0 = (gv - q * kBPF) * BQ, par = gv & 1;
                 if (!FINAL[par]) {
                     const float2 pre = P[par][v], post = P[par][v + 1];
                     float a = pre.x, b = pre.y;
@@ -189,8 +194,8 @@ __global__ void __launch_bounds__(kBqThreads) k_rn_biquad(const float *__restric
                 }
             }
             if (warp == 1 && g >= 2) {                             // ---- block g-2 is final: frame I/O at frame edges
-                const int gf = g - 2, q = gf / kBqBlocksPerFrame;
-                if (gf - q * kBqBlocksPerFrame == kBqBlocksPerFrame - 1) {
+                const int gf = g - 2, q = gf / kBPF;
+                if (gf - q * kBPF == kBPF - 1) {
                     for (int i = lane; i < kFrame; i += 32) dst[(size_t)q * kFrame + i] = sy[q & 1][i];
                     // sx[q & 1] is free once frame q is final: fetch frame q + 2 (frame q + 1 was fetched a frame ago)
                     // (into registers now, into shared memory next iteration: the load latency never meets the barrier)
@@ -211,15 +216,15 @@ __global__ void __launch_bounds__(kBqThreads) k_rn_biquad(const float *__restric
         }
         const int verdict = __syncthreads_or(hz ? 1 : 0);          // the verdict on block g-1 travels with the barrier
         if (threadIdx.x == 0 && verdict) {                         // ---- replay of a hazardous block g-1
-            const int gv = g - 1, q = gv / kBqBlocksPerFrame, b0 = (gv - q * kBqBlocksPerFrame) * kBqBlock, par = gv & 1;
+            const int gv = g - 1, q = gv / kBPF, b0 = (gv - q * kBPF) * BQ, par = gv & 1;
             float r0 = P[par][0].x, r1 = P[par][0].y;
-            for (int i = 0; i < kBqBlock; i++) sy[q & 1][b0 + i] = biquad_step(sx[q & 1][b0 + i], r0, r1);
-            if (__float_as_uint(r0) != __float_as_uint(P[par][kBqBlock].x) || __float_as_uint(r1) != __float_as_uint(P[par][kBqBlock].y)) {
+            for (int i = 0; i < BQ; i++) sy[q & 1][b0 + i] = biquad_step(sx[q & 1][b0 + i], r0, r1);
+            if (__float_as_uint(r0) != __float_as_uint(P[par][BQ].x) || __float_as_uint(r1) != __float_as_uint(P[par][BQ].y)) {
                 // the fast step was wrong: block g (computed from its end state) is void, redo it from the true state
                 m0 = r0; m1 = r1;
                 if (g < G) {
-                    const int q2 = g / kBqBlocksPerFrame, c0 = (g - q2 * kBqBlocksPerFrame) * kBqBlock;
-                    for (int i = 0; i < kBqBlock; i++) sy[q2 & 1][c0 + i] = biquad_step(sx[q2 & 1][c0 + i], m0, m1);
+                    const int q2 = g / kBPF, c0 = (g - q2 * kBPF) * BQ;
+                    for (int i = 0; i < BQ; i++) sy[q2 & 1][c0 + i] = biquad_step(sx[q2 & 1][c0 + i], m0, m1);
                     FINAL[g & 1] = 1;
                 }
             }
@@ -696,7 +701,10 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<RR, GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(RR * GG));
         FVAD_RNN_VARIANTS(FVAD_RNN_ATTR)
 #undef FVAD_RNN_ATTR
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBiquadSmemHog);
+#define FVAD_BQ_ATTR(BB)                                                                                                 \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad<BB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBiquadSmemHog);
+        FVAD_BQ_VARIANTS(FVAD_BQ_ATTR)
+#undef FVAD_BQ_ATTR
         if (e != cudaSuccess) rc = set_error(FVAD_ECUDA, "cudaFuncSetAttribute: %s (is this an sm_100 device?)", cudaGetErrorString(e));
     }
     if (rc == FVAD_OK) rc = rnnoise_batch_reset(r, 0);
@@ -739,7 +747,18 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
                           in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
     } else {
         const size_t hog = lat ? kBiquadSmemHog : 0;
-        FVAD_LAUNCH(k_rn_biquad, (unsigned)N, kBqThreads, hog, st, d_in, in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
+        int BQ = 48;
+        if (const char *e = getenv("FVAD_BQ_BLOCK")) BQ = atoi(e);
+        bool launched = false;
+#define FVAD_BQ_GO(BB)                                                                                                   \
+        if (!launched && BQ == BB) {                                                                                     \
+            launched = true;                                                                                             \
+            FVAD_LAUNCH_NAMED("k_rn_biquad", k_rn_biquad<BB>, (unsigned)N, bq_threads(BB), hog, st, d_in, in_stride, C, (int)Qs,   \
+                              r->persist, s.hp, r->hp_stride(), N);                                                      \
+        }
+        FVAD_BQ_VARIANTS(FVAD_BQ_GO)
+#undef FVAD_BQ_GO
+        if (!launched) return set_error(FVAD_EINVALID_ARGUMENT, "FVAD_BQ_BLOCK=%d: no such biquad variant", BQ);
     }
     FVAD_LAUNCH(k_rn_hp_save, (unsigned)N, 256, 0, st, s.hp, r->hp_stride(), r->hp_hist, (int)Qs);
     FVAD_CUDA_TRY(cudaGetLastError());

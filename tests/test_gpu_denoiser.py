@@ -35,6 +35,21 @@ def test_denoiser_batch_bit_exact(fv, checker, rnn_rg, monkeypatch):
     assert silent > 0 and voiced > 0, "input must exercise silent and voiced frames"
 
 
+@pytest.mark.parametrize("bq", [32, 60])
+def test_denoiser_biquad_block_sizes(fv, checker, bq, monkeypatch):
+    """The biquad kernel's block length (samples between two verdicts of the verifying warps; 48 by default) changes how
+    the chain is cut into verified pieces, never the result."""
+    monkeypatch.setenv("FVAD_BQ_BLOCK", str(bq))
+    S, secs = 3, 6
+    pcm = np.stack([synth(fv, 40 + s, secs) for s in range(S)])
+    d = fv.DenoiserBatch(S)
+    out, vad = d.run(pcm)
+    for s in range(S):
+        wo, wv = checker.denoise_stream(pcm[s])
+        assert np.array_equal(vad[s], wv), (s, np.nonzero(vad[s] != wv)[0][:5])
+        assert np.array_equal(out[s], wo), (s, np.abs(out[s] - wo).max())
+
+
 def test_denoiser_biquad_state_per_lane(fv, checker, monkeypatch):
     """The throughput-regime biquad (a state per lane, 32 states per CTA; chosen by itself only beyond 3/4 of the SM count)
     forced on 37 states: the second CTA has 5 live lanes, the streams' digital silences exercise the denormal path and the

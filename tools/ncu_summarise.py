@@ -74,7 +74,8 @@ with open(os.path.join(out, f"{tag}_ncu_full_metrics.txt"), "w") as f:
                 tb = nbytes("dram__bytes_read.sum") + nbytes("dram__bytes_write.sum")
                 if k.startswith("k_stft2048") and tb > 1e10:
                     k += "@4096x1406"                      # the stft leg's launch (configs[2] chunk), not a pipeline tile
-                traffic[k] = tb
+                if rep.startswith("prof_"):                # t_*: throughput-regime captures (592 streams), not the bench's launch shapes
+                    traffic[k] = tb
             except (KeyError, ValueError):
                 pass
             f.write("\n")
