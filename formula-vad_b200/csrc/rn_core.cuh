@@ -279,7 +279,8 @@ RN_HD void load_windowed(const Tables &t, cpx *buf, SRC src) {
 constexpr int kScrFft = 2 * kSlots960;                     // cpx buf[1020]
 constexpr int kScrAna = kScrFft + 96;                      // + misc
 constexpr int kScrSyn = kScrFft + 2 * kFreq + 2 + 96;      // + linear X[481] + misc
-constexpr int kScrPitch = 864 + 296 + 388 + 388 + 64 + 64; // xlp, xc, yyl, ip, list, misc
+constexpr int kScrPitch = 864 + 296 + 388 + 388 + 64 + 64 + 8;   // xlp, xc, yyl, ip, list, misc, pad: the stride is 24 mod 32 banks,
+                                                                    // so the pooled chains of a CTA's four frames start 8 banks apart
 
 // frame_analysis + the energy half of compute_frame_features (denoise.c:295-308, 349-362, 363-365):
 // X, Ex, E<0.04 silence flag and the cepstrum dct(Ly) with its -12/-4 offsets.
@@ -1296,8 +1297,13 @@ RN_HD float biquad_step_fast(float in_norm, float &m0, float &m1) {
     const float p = A0 * y, pl = fma_rn(A0, y, -p);
     // error term of w = p + dh by Fast2Sum on the magnitude-ordered pair (2 dependent operations after w
     // instead of TwoSum's 4; the ordering is decided while w is being computed)
+    // The ordering is decided from y, not from p = A0*y: |y| >= |dh|/A0 is known one multiply earlier, so the compare and
+    // the two selects run beside p and w instead of between w and (hi - w) -- one operation less on the dependent chain.
+    // Near |p| == |dh| the two tests can disagree; Fast2Sum is then still exact unless the operands straddle a binade,
+    // and ANY difference from the verified step (biquad_step_eft uses the branch-free TwoSum) is caught by the verifying
+    // warp's comparison and replayed -- the fast step only has to be right almost always.
     const float w = p + dh;
-    const bool pbig = fabsf(p) >= fabsf(dh);
+    const bool pbig = fabsf(y) >= fabsf(dh) * (1.0f / 1.99599f);
     const float hi = pbig ? p : dh, lo = pbig ? dh : p;
     const float f = (hi - w) + lo;
     const float th = pl + dl;

@@ -35,11 +35,12 @@ def test_denoiser_batch_bit_exact(fv, checker, rnn_rg, monkeypatch):
     assert silent > 0 and voiced > 0, "input must exercise silent and voiced frames"
 
 
-@pytest.mark.parametrize("bq", [32, 60])
-def test_denoiser_biquad_block_sizes(fv, checker, bq, monkeypatch):
-    """The biquad kernel's block length (samples between two verdicts of the verifying warps; 48 by default) changes how
-    the chain is cut into verified pieces, never the result."""
+@pytest.mark.parametrize("bq,roll", [(32, 0), (48, 0), (60, 0), (48, 1), (160, 1)])
+def test_denoiser_biquad_block_sizes(fv, checker, bq, roll, monkeypatch):
+    """The biquad kernel's block length (samples between two verdicts of the verifying warps; 96 by default) and the form
+    of the chain lane's loop (unrolled / rolled) change how the chain is cut into verified pieces, never the result."""
     monkeypatch.setenv("FVAD_BQ_BLOCK", str(bq))
+    monkeypatch.setenv("FVAD_BQ_ROLL", str(roll))
     S, secs = 3, 6
     pcm = np.stack([synth(fv, 40 + s, secs) for s in range(S)])
     d = fv.DenoiserBatch(S)
