@@ -43,7 +43,14 @@ struct fvad_batch {
     // tiling
     size_t tile_frames = 0;        // frames of frame_len per row per tile
     size_t work_cap = 0;           // floats per work row
-    float *d_work = nullptr;       // [rows][work_cap]: carry + new input of the tile
+    float *d_work = nullptr;       // [rows][work_cap]: carry + new input of the tile (= one of d_work_buf)
+    // Host pushes double-buffer the work rows: the next tile's PCM is copied (stream sH) into one buffer while stage A
+    // reads the other, so the host-to-device copy of tile t+1 hides behind the biquad chain of tile t.
+    float *d_work_buf[2] = {nullptr, nullptr};
+    float *d_work_next = nullptr;  // where this tile's unconsumed tail goes (the other buffer on host pushes)
+    int work_par = 0;
+    cudaStream_t sH = nullptr;
+    cudaEvent_t evH[2] = {}, evW[2] = {};   // per work buffer: input copied in (sH) / last reader done (input-side stream)
     float *d_carry = nullptr;      // [rows][frame_len]
     size_t carry_len = 0;
 
@@ -143,7 +150,9 @@ extern "C" void fvad_batch_destroy(fvad_batch *b) {
             for (cudaEvent_t e : {b->evA[i], b->evB1[i], b->evB[i], b->evC[i], b->evD[i]}) if (e) cudaEventDestroy(e);
         }
         for (cudaEvent_t e : {b->evS[0], b->evS[1], b->evE[0], b->evE[1]}) if (e) cudaEventDestroy(e);
-        cudaFree(b->d_work); cudaFree(b->d_carry); cudaFree(b->d_den); cudaFree(b->d_den_carry);
+        if (b->sH) { cudaStreamSynchronize(b->sH); cudaStreamDestroy(b->sH); }
+        for (cudaEvent_t e : {b->evH[0], b->evH[1], b->evW[0], b->evW[1]}) if (e) cudaEventDestroy(e);
+        cudaFree(b->d_work_buf[0]); cudaFree(b->d_work_buf[1]); cudaFree(b->d_carry); cudaFree(b->d_den); cudaFree(b->d_den_carry);
         cudaFree(b->d_ratio480); cudaFree(b->d_vad480); cudaFree(b->d_band); cudaFree(b->d_ratio_stft);
         cudaFree(b->d_vad_stft); cudaFree(b->d_spectra); cudaFree(b->d_params); cudaFree(b->d_states);
         cudaFree(b->d_rings); cudaFree(b->d_segs); cudaFree(b->d_seg_count); cudaFree(b->d_events);
@@ -275,7 +284,14 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
     b->tile_frames = tf;
     b->work_cap = tf * b->frame_len + b->frame_len;
     b->work_cap = (b->work_cap + 3) & ~(size_t)3;
-    if ((rc = dmalloc(&b->d_work, b->rows * b->work_cap)) != FVAD_OK) return fail(rc);
+    for (int i = 0; i < 2; i++)
+        if ((rc = dmalloc(&b->d_work_buf[i], b->rows * b->work_cap)) != FVAD_OK) return fail(rc);
+    b->d_work = b->d_work_next = b->d_work_buf[0];
+    if (cudaStreamCreateWithFlags(&b->sH, cudaStreamNonBlocking) != cudaSuccess)
+        return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
+    for (cudaEvent_t *e : {&b->evH[0], &b->evH[1], &b->evW[0], &b->evW[1]})
+        if (cudaEventCreateWithFlags(e, cudaEventDisableTiming) != cudaSuccess)
+            return fail(set_error(FVAD_ECUDA, "cudaEventCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
     if ((rc = dmalloc(&b->d_carry, b->rows * (size_t)b->frame_len)) != FVAD_OK) return fail(rc);
     if (b->use_denoiser) {
         b->den_cap = (tf * kRnFrame + b->fft_size + 3) & ~(size_t)3;
@@ -454,7 +470,7 @@ static int process_tile(fvad_batch *b, size_t m) {
     const size_t tail = avail - consumed;
     if (consumed > 0 && tail > 0) {
         FVAD_TRY(copy_rows_launch(b->d_carry, b->frame_len, 0, b->d_work, b->work_cap, consumed, b->rows, tail, sA));
-        FVAD_TRY(copy_rows_launch(b->d_work, b->work_cap, 0, b->d_carry, b->frame_len, 0, b->rows, tail, sA));
+        FVAD_TRY(copy_rows_launch(b->d_work_next, b->work_cap, 0, b->d_carry, b->frame_len, 0, b->rows, tail, sA));
     }
     b->carry_len = tail;
     return FVAD_OK;
@@ -481,19 +497,31 @@ extern "C" int fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n,
     if (first_index) *first_index = b->total_write_count;
     FVAD_TRY(ensure_trace_buffers(b));
     const size_t m_max = b->tile_frames * (size_t)b->frame_len;
+    cudaStream_t sIn = b->use_denoiser ? b->sA : b->stream;
     for (size_t off = 0; off < n;) {
         const size_t m = std::min(m_max, n - off);
+        const int cur = b->work_par;
+        // a tile that completes no frame leaves everything in place: its successor appends to the same buffer
+        const bool moves_on = b->cfg.skip_processing || (b->carry_len + m) / b->frame_len > 0;
+        b->d_work = b->d_work_buf[cur];
+        b->d_work_next = b->d_work_buf[moves_on ? cur ^ 1 : cur];
+        FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sH, b->evW[cur], 0));             // the buffer's previous tile has been read
         for (size_t r = 0; r < b->rows; r++)
             FVAD_CUDA_TRY(cudaMemcpyAsync(b->d_work + r * b->work_cap + b->carry_len, pcm[r] + off, sizeof(float) * m,
-                                          cudaMemcpyHostToDevice, b->use_denoiser ? b->sA : b->stream));
+                                          cudaMemcpyHostToDevice, b->sH));
+        FVAD_CUDA_TRY(cudaEventRecord(b->evH[cur], b->sH));
+        FVAD_CUDA_TRY(cudaStreamWaitEvent(sIn, b->evH[cur], 0));
         FVAD_TRY(process_tile(b, m));
+        FVAD_CUDA_TRY(cudaEventRecord(b->evW[cur], sIn));
+        if (moves_on) b->work_par = cur ^ 1;
         off += m;
     }
+    b->d_work = b->d_work_next = b->d_work_buf[b->work_par];
     FVAD_TRY(join_machines(b));
     b->total_write_count += n;
-    // input is borrowed only until return (AudioPipeline.pushSamples copies into its ring): wait for the
-    // input-side stream only; the later stages keep running behind the caller's back until fvad_batch_sync
-    FVAD_CUDA_TRY(cudaStreamSynchronize(b->use_denoiser ? b->sA : b->stream));
+    // input is borrowed only until return (AudioPipeline.pushSamples copies into its ring): wait for the copies
+    // only; the stages keep running behind the caller's back until fvad_batch_sync
+    FVAD_CUDA_TRY(cudaStreamSynchronize(b->sH));
     return FVAD_OK;
 }
 
@@ -510,6 +538,7 @@ extern "C" int fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t 
         FVAD_TRY(gather_rows_launch(b->d_work, b->work_cap, b->carry_len, d_pcm, stream_stride, channel_stride, off, b->S,
                                     (int)b->C, m, b->use_denoiser ? b->sA : b->stream));
         FVAD_TRY(process_tile(b, m));
+        FVAD_CUDA_TRY(cudaEventRecord(b->evW[b->work_par], b->use_denoiser ? b->sA : b->stream));   // a later host push waits for it
         off += m;
     }
     FVAD_TRY(join_machines(b));
@@ -559,7 +588,7 @@ extern "C" int fvad_batch_sync(fvad_batch *b) {
 extern "C" int fvad_batch_reset(fvad_batch *b) {
     if (!b) return set_error(FVAD_EINVALID_ARGUMENT, "null batch");
     DeviceGuard g(b->device);
-    for (cudaStream_t st : {b->sA, b->sB, b->sB2, b->sC, b->sE, b->stream}) FVAD_CUDA_TRY(cudaStreamSynchronize(st));
+    for (cudaStream_t st : {b->sH, b->sA, b->sB, b->sB2, b->sC, b->sE, b->stream}) FVAD_CUDA_TRY(cudaStreamSynchronize(st));
     FVAD_TRY(upload_machine_state(b));
     if (b->use_denoiser) {
         FVAD_TRY(rnnoise_batch_reset(b->rn, b->stream));
@@ -567,6 +596,7 @@ extern "C" int fvad_batch_reset(fvad_batch *b) {
         FVAD_CUDA_TRY(cudaMemsetAsync(b->d_vad480, 0, sizeof(float) * b->S * b->stride480, b->stream));
     }
     b->carry_len = 0; b->den_carry = 0; b->base480 = 0; b->tile_no = 0; b->stft_tile_no = 0; b->e_pending = -1;
+    b->work_par = 0; b->d_work = b->d_work_next = b->d_work_buf[0];
     b->total_write_count = b->read_count = b->stft_done = 0;
     for (auto &v : b->segs) v.clear();
     for (auto &v : b->events) v.clear();

@@ -101,14 +101,14 @@ static int rn_tables_get(int device, RnDevTables *out) {
 // ------------------------------------------------------------------------------------------
 // kernels
 // ------------------------------------------------------------------------------------------
-// Two warps per state.  The IIR is sample-sequential, so ONE lane (warp 0, lane 0) walks the samples with
-// the fast f32 step (rn_core.cuh biquad_step_fast, 9 dependent f32 ops per sample) and records the state
-// before every sample.  Warp 1 runs one block (32 samples) behind: it re-evaluates every sample of the
-// previous block with the full hazard analysis (biquad_step_eft), compares with what lane 0 carried on, and
-// also stages frames between global and shared memory, so neither verification nor memory latency sits on
-// the dependent chain.  A hazardous block is replayed by lane 0 with the reference's double arithmetic from
-// the recorded state; the replay reproduces the fast result unless the fast step was really wrong (a
-// ~2^-29 event per sample), in which case the block in flight is recomputed as well.
+// One chain lane + verifying warps per state.  The IIR is sample-sequential, so ONE lane (warp 0, lane 0) walks the
+// samples with the fast f32 step (rn_core.cuh biquad_step_fast, 7 dependent f32 ops per sample) and records the state
+// before every sample.  Warps 1.. run one block (BQ samples, a sample per thread) behind: they re-evaluate every sample
+// of the previous block with the full hazard analysis (biquad_step_eft) and compare with what lane 0 carried on; warp 1
+// also stages frames between global and shared memory, so neither verification nor memory latency sits on the
+// dependent chain.  A hazardous block is replayed by lane 0 with the reference's double arithmetic from the recorded
+// state; the replay reproduces the fast result unless the fast step was really wrong, in which case the block in
+// flight is recomputed as well.
 // BQ = samples per block, ROLL = the chain lane's loop form.  The per-block costs (two barriers, verdict) shrink with BQ.
 // Unrolled form (inputs of two blocks in registers, statically indexed): the body grows with BQ -- measured, 20 streams,
 // ms per 60 s tile: BQ = 32: 74.3, 48: 69.6, 60: 77.7, 80: 86.6, and inside the wavefront 48 costs 75.9: beyond the 32 KB
