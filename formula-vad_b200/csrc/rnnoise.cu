@@ -889,13 +889,19 @@ int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     FVAD_TRY(rn_check(r, slot, Qs));
     if (Qs == 0) return FVAD_OK;
     RnSlot &s = r->slots[slot];
-    // States per SM decide the shape: R states share a group's weight fetches, G groups fill each other's narrow layers.
-    // One state per SM: the shortest chain wins (R = G = 1).  FVAD_RNN_R / FVAD_RNN_G override (tests exercise every
-    // variant on a handful of states).
+    // Latency regime (a state per SM at most): the shortest chain wins, R = G = 1.  Throughput regime: R states share a
+    // group's weight fetches, G groups fill each other's narrow layers, and packing six states into a CTA (R, G = 2, 3)
+    // leaves the other SMs wholly to the frame-parallel kernels (an RNN CTA's 174 KB of weights keep almost everything
+    // else off its SM) -- measured, x real time: 148 streams (1,1) 81.3k, (1,3) 82.7k, (2,3) 87.8k; 296 streams (1,2)
+    // 102.2k, (2,1) 100.2k, (2,3) 103.9k.  FVAD_RNN_R / FVAD_RNN_G override (tests exercise every variant).
     const size_t sms = (size_t)device_sm_count(r->device);
     const size_t per_sm = ceil_div(r->N, sms);
-    int R = per_sm <= 3 ? 1 : per_sm <= 6 ? 2 : 4;
-    int G = per_sm <= 1 ? 1 : per_sm == 2 || per_sm == 4 || per_sm == 7 || per_sm == 8 ? 2 : 3;
+    int R = 1, G = 1;
+    if (!latency_regime(r->N, r->device)) {
+        if (per_sm <= 6) { R = 2; G = 3; }
+        else if (per_sm <= 8) { R = 4; G = 2; }
+        else { R = 4; G = 3; }
+    }
     if (const char *e = getenv("FVAD_RNN_R")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) R = v; }
     if (const char *e = getenv("FVAD_RNN_G")) { const int v = atoi(e); if (v >= 1 && v <= 3) G = v; }
     const unsigned grid = (unsigned)ceil_div(r->N, (size_t)R * G);
