@@ -329,8 +329,18 @@ __global__ void __launch_bounds__(32 * kBqlWarps) k_rn_biquad_lanes(const float 
                     xr[i] = v.x; xr[i + 1] = v.y; xr[i + 2] = v.z; xr[i + 3] = v.w;
                 }
                 const float a0 = fabsf(m0), a1 = fabsf(m1);
-                if ((a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f)) {
-                    for (int i = 0; i < kBqlBlock; i++) yb[i] = biquad_step(xb[i], m0, m1);   // denormal tail of a silence
+                const bool tiny = (a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f);
+                if (__any_sync(0xffffffffu, tiny)) {
+                    // A state in the denormal tail of a silence needs the reference's double arithmetic.  The warp would
+                    // execute both paths one after the other, so ALL its states take the double path for this block: it is the
+                    // reference's own arithmetic for every one of them, and one path (~85 cycles per sample) beats two.
+#pragma unroll
+                    for (int i = 0; i < kBqlBlock; i += 4) {
+                        float4 yy;
+                        yy.x = biquad_step(xr[i], m0, m1); yy.y = biquad_step(xr[i + 1], m0, m1);
+                        yy.z = biquad_step(xr[i + 2], m0, m1); yy.w = biquad_step(xr[i + 3], m0, m1);
+                        *reinterpret_cast<float4 *>(yb + i) = yy;
+                    }
                     FINAL[par][lane] = 1;
                 } else {
 #pragma unroll
@@ -360,15 +370,15 @@ __global__ void __launch_bounds__(32 * kBqlWarps) k_rn_biquad_lanes(const float 
                 const int par = (g - 1) & 1;
                 if (!FINAL[par][lane]) {
                     const float *xb = sx[(g - 1) % 3] + lane * kBqlStride, *yb = sy[(g - 1) % 3] + lane * kBqlStride;
-                    bool hz = false;
                     for (int i = vw; i < kBqlBlock; i += kBqlVer) {
                         const float2 pre_s = P[par][i * kBqlStates + lane], post = P[par][(i + 1) * kBqlStates + lane];
                         float a = pre_s.x, b = pre_s.y;
+                        bool hz = false;
                         const float yv = biquad_step_eft(xb[i], a, b, hz);
                         hz |= (__float_as_uint(a) != __float_as_uint(post.x)) | (__float_as_uint(b) != __float_as_uint(post.y)) |
                               (__float_as_uint(yv) != __float_as_uint(yb[i]));
+                        if (hz) atomicOr(&HZ[lane], (int)(1u << i));      // which samples of this state's block: replayed one by one
                     }
-                    if (hz) HZ[lane] = 1;
                 }
             }
             if (g >= 2) {                                           // ---- block g-2 is final: out it goes
@@ -386,21 +396,34 @@ __global__ void __launch_bounds__(32 * kBqlWarps) k_rn_biquad_lanes(const float 
         }
         __syncthreads();
         if (warp == 0) {
-            if (g >= 1 && g - 1 < G && HZ[lane]) {                  // ---- replay of a hazardous block g-1, lane by lane
+            unsigned hm = (g >= 1 && g - 1 < G) ? (unsigned)HZ[lane] : 0u;
+            if (hm) {                                               // ---- replay of the flagged samples of block g-1, lane by lane
+                // A hazard says the fast step could not be trusted at that sample; nearly always the double arithmetic
+                // reproduces it and everything after it stands, so a flagged sample is redone on its own from its recorded
+                // state (~100 cycles for the warp) and only a real difference voids the rest of the block and block g.
                 const int par = (g - 1) & 1;
-                float r0 = P[par][lane].x, r1 = P[par][lane].y;
                 const float *xb = sx[(g - 1) % 3] + lane * kBqlStride;
                 float *yb = sy[(g - 1) % 3] + lane * kBqlStride;
-                for (int i = 0; i < kBqlBlock; i++) yb[i] = biquad_step(xb[i], r0, r1);
-                const float2 end = P[par][kBqlBlock * kBqlStates + lane];
-                if (__float_as_uint(r0) != __float_as_uint(end.x) || __float_as_uint(r1) != __float_as_uint(end.y)) {
-                    // the fast step was wrong: block g (computed from its end state) is void, redo it from the true state
-                    m0 = r0; m1 = r1;
-                    if (g < G) {
-                        const float *xc = sx[g % 3] + lane * kBqlStride;
-                        float *yc = sy[g % 3] + lane * kBqlStride;
-                        for (int i = 0; i < kBqlBlock; i++) yc[i] = biquad_step(xc[i], m0, m1);
-                        FINAL[g & 1][lane] = 1;
+                while (hm) {
+                    const int v = __ffs((int)hm) - 1;
+                    hm &= hm - 1;
+                    float r0 = P[par][v * kBqlStates + lane].x, r1 = P[par][v * kBqlStates + lane].y;
+                    yb[v] = biquad_step(xb[v], r0, r1);
+                    const float2 post = P[par][(v + 1) * kBqlStates + lane];
+                    if (__float_as_uint(r0) != __float_as_uint(post.x) || __float_as_uint(r1) != __float_as_uint(post.y)) {
+                        for (int i = v + 1; i < kBqlBlock; i++) yb[i] = biquad_step(xb[i], r0, r1);
+                        hm = 0;
+                        const float2 end = P[par][kBqlBlock * kBqlStates + lane];
+                        if (__float_as_uint(r0) != __float_as_uint(end.x) || __float_as_uint(r1) != __float_as_uint(end.y)) {
+                            // the fast step was wrong: block g (computed from its end state) is void, redo it from the true state
+                            m0 = r0; m1 = r1;
+                            if (g < G) {
+                                const float *xc = sx[g % 3] + lane * kBqlStride;
+                                float *yc = sy[g % 3] + lane * kBqlStride;
+                                for (int i = 0; i < kBqlBlock; i++) yc[i] = biquad_step(xc[i], m0, m1);
+                                FINAL[g & 1][lane] = 1;
+                            }
+                        }
                     }
                 }
             }
@@ -797,10 +820,13 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
     // stages share its scheduler.  Many chains (throughput regime): no reservation, so several chains and the
     // other stages' CTAs share an SM; reserving it there serialises the biquad against everything else.
     const bool lat = latency_regime(N, r->device);
-    // A state per lane (k_rn_biquad_lanes) is opt-in: exact, and 8 x fewer instructions per sample, but measured no faster
-    // (592 streams: 76.7k vs 104.0k, 1184: 103.8k vs 102.9k x real time) -- a lane in the denormal tail of a silence or in
-    // a hazard replay holds up the 31 other chains of its warp, and the synthetic streams' silences overlap most of the time.
-    bool lanes = false;
+    // A state per lane (k_rn_biquad_lanes: 8 x fewer instructions per sample, 32 chains per warp) from 1000 states on.  Its
+    // warp advances at the pace of its slowest lane (~230 cycles per sample with the synthetic streams' overlapping
+    // silences: the whole warp takes the double path while any state is in a denormal tail), and stage A of tile t+1 follows
+    // stage A of tile t, so it only pays where the tile is short enough for that chain not to set the pace.  Measured,
+    // x real time, lanes / chain-per-CTA: 296 streams 70.1k / 103.2k, 592: 104.4k / 116.5k, 1184: 130.4k / 113.0k,
+    // 2368: 134.2k / 113.8k.
+    bool lanes = !lat && N >= 1000;
     if (const char *e = getenv("FVAD_BIQUAD_LANES")) lanes = atoi(e) != 0;
     if (lanes) {
         FVAD_LAUNCH_NAMED("k_rn_biquad", k_rn_biquad_lanes, (unsigned)ceil_div(N, (size_t)kBqlStates), 32 * kBqlWarps, 0, st, d_in,

@@ -52,7 +52,7 @@ def test_denoiser_biquad_block_sizes(fv, checker, bq, roll, monkeypatch):
 
 
 def test_denoiser_biquad_state_per_lane(fv, checker, monkeypatch):
-    """The throughput-regime biquad (a state per lane, 32 states per CTA; chosen by itself only beyond 3/4 of the SM count)
+    """The many-stream biquad (a state per lane, 32 states per CTA; chosen by itself only from 1000 states on)
     forced on 37 states: the second CTA has 5 live lanes, the streams' digital silences exercise the denormal path and the
     hazard replays are lane-divergent.  A second call continues from the carried filter state."""
     monkeypatch.setenv("FVAD_BIQUAD_LANES", "1")
