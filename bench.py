@@ -68,8 +68,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-stft", action="store_true")
     ap.add_argument("--no-batched", action="store_true", help="skip the many-stream leg")
-    ap.add_argument("--batched-streams", type=int, default=592)
-    ap.add_argument("--batched-seconds", type=int, default=300)
+    ap.add_argument("--batched-streams", type=int, default=1184)
+    ap.add_argument("--batched-seconds", type=int, default=150)
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
 
