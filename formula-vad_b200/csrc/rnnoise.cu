@@ -37,7 +37,7 @@ struct RnDevTables {
 };
 
 // Tile arrays that cross a stage boundary exist once per SLOT so that stage X of tile t+1 can run while
-// stage X+1 of tile t still reads tile t's arrays (batch.cu runs the four stages on four CUDA streams).
+// stage X+1 of tile t still reads tile t's arrays (batch.cu runs the stages on CUDA streams of their own).
 struct RnSlot {
     float *hp = nullptr;           // [N][kPHist + Qcap*480]   A -> B
     cpx *X = nullptr, *P = nullptr;          // [N][Qcap][481]  B -> D
@@ -698,9 +698,9 @@ __global__ void __launch_bounds__(256) k_rn_tail_carry(float *tail, int Q, size_
 // ------------------------------------------------------------------------------------------
 #define FVAD_RNN_VARIANTS(X) X(1, 1) X(1, 2) X(1, 3) X(2, 1) X(2, 2) X(2, 3) X(4, 1) X(4, 2) X(4, 3)
 // Dynamic shared memory a biquad CTA asks for without using it (latency regime): together with its static arrays it takes
-// the SM's whole 227 KB, so that NO other CTA fits beside the chain -- with 200 KB the kernels that need no shared memory
-// (the one-thread-per-stream scans, copies, the overlap-add) still landed there and cost the slowest chain of a launch,
-// hence the launch, 9 % (75.9 ms per tile inside the wavefront vs 69.6 ms alone).
+// the SM's whole 227 KB, so that NO other CTA fits beside the chain (a co-resident frame-parallel CTA costs the chain ~13 %;
+// with 200 KB the kernels that need no shared memory could still land there -- measured, filling the SM completely made no
+// further difference: the slowdown then seen inside the wavefront was the instruction cache, see BQ / ROLL above).
 static size_t biquad_smem_hog(size_t static_bytes) {
     const size_t per_block_max = 227 * 1024;
     return per_block_max > static_bytes ? per_block_max - static_bytes : 0;

@@ -25,7 +25,7 @@ int rnnoise_batch_process(RnnoiseBatch *r, const float *d_in, size_t in_stride, 
                           size_t vad_stride, size_t vad_off, cudaStream_t stream);
 
 
-// The same work as four stages that batch.cu issues on four CUDA streams (wavefront over tiles): arrays
+// The same work as stages that batch.cu issues on CUDA streams of their own (wavefront over tiles; B = B1 then B2): arrays
 // that cross a stage boundary exist once per slot, cross-tile carries stay inside their stage.
 //   A: biquad (sample-sequential)           B: analysis / pitch / features (frame-parallel)
 //   C: RNN (frame-sequential)               D: gains, synthesis, overlap-add, VAD minimum
