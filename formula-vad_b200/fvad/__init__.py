@@ -112,6 +112,7 @@ def lib():
         "fvad_denoiser_batch_destroy": (None, [vp]),
         "fvad_denoiser_batch_run": (C.c_int, [vp, C.POINTER(_fp), sz, C.POINTER(_fp), C.POINTER(_fp)]),
         "fvad_vadm_sweep": (C.c_int, [vp, sz, sz, C.POINTER(VadMachineConfig), sz, sz, sz, C.c_int, vp, sz, vp]),
+        "fvad_vadm_sweep_static": (C.c_int, [vp, vp, vp, sz, sz, C.c_uint64, C.POINTER(VadMachineConfig), sz, sz, sz, vp, sz, vp, vp]),
         "fvad_eval_stats_batch": (C.c_int, [vp, sz, sz, vp, vp, vp, vp, vp, sz, sz, vp, C.c_int, vp]),
         "fvad_synth_fill_host": (C.c_int, [_fp, C.c_uint64, C.c_uint64, C.c_uint64, sz]),
         "fvad_synth_fill_device": (C.c_int, [vp, sz, C.c_uint64, C.c_uint64, sz, C.c_uint64, sz, vp]),
@@ -479,6 +480,23 @@ def vadm_sweep(records, configs, sample_rate=48000, fft_size=2048, device=-1, ma
     if counts.max(initial=0) > max_segs:
         return vadm_sweep(records, configs, sample_rate, fft_size, device, int(counts.max()))
     return [[segs[s * K + k, :counts[s * K + k]].copy() for k in range(K)] for s in range(S)]
+
+
+VADM_SWEEP_STATIC_SCRATCH_BYTES = 16 << 20      # FVAD_VADM_SWEEP_STATIC_SCRATCH_BYTES
+VADM_SWEEP_STATIC_MAX_CONFIGS = 256             # FVAD_VADM_SWEEP_STATIC_MAX_CONFIGS
+
+
+def vadm_sweep_static(d_min_volume, d_vol_ratio, d_rnn_vad, n_streams, n_records, first_index, configs, d_segs, max_segs,
+                      d_counts, sample_rate=48000, fft_size=2048, cuda_stream=0):
+    """fvad_vadm_sweep_static: the sweep on DEVICE planes into DEVICE outputs with no allocation (scratch is a static
+    device array of VADM_SWEEP_STATIC_SCRATCH_BYTES).  All pointer arguments are device addresses (ints); the call is
+    asynchronous on `cuda_stream` of the current device.  No reference counterpart."""
+    K = len(configs)
+    cfgs = (VadMachineConfig * K)(*configs)
+    _check(lib().fvad_vadm_sweep_static(C.c_void_p(d_min_volume), C.c_void_p(d_vol_ratio),
+                                        C.c_void_p(d_rnn_vad) if d_rnn_vad else None, n_streams, n_records, first_index,
+                                        cfgs, K, sample_rate, fft_size, C.c_void_p(d_segs), max_segs, C.c_void_p(d_counts),
+                                        C.c_void_p(cuda_stream) if cuda_stream else None))
 
 
 def synth_host(seed, stream_id, first_sample, n):

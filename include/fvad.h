@@ -253,6 +253,29 @@ int    fvad_vadm_sweep(const fvad_stft_record *records, size_t n_streams, size_t
                        const fvad_vad_machine_config *configs, size_t n_configs, size_t sample_rate,
                        size_t fft_size, int device, fvad_segment *segs, size_t max_segs, uint32_t *counts);
 
+/* The same sweep for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Calls no cudaMalloc / cudaFree / allocating library routine: the scans' scratch (their f64 rings) is one
+ * file-scope device array of FVAD_VADM_SWEEP_STATIC_SCRATCH_BYTES that every GPU loading the library holds
+ * until exit.  Runs on the CURRENT device, asynchronously on `cuda_stream` (which must belong to it).
+ * Inputs are DEVICE planes [n_streams][n_records] of the records' fields (min_volume, vol_ratio, rnn_vad;
+ * d_rnn_vad may be NULL = fft_input.vad == null); record f has fft_result.index = first_index + f*fft_size.
+ * Outputs are DEVICE arrays in fvad_vadm_sweep's layout: d_segs[(s*n_configs+k)*max_segs ...], d_counts[s*n_configs+k]
+ * (a count may exceed max_segs: truncated).
+ * Limits: n_configs <= FVAD_VADM_SWEEP_STATIC_MAX_CONFIGS and
+ *   n_streams*n_configs * (max long + max short + max ratio ring length over the configs) * 8 B
+ *     <= FVAD_VADM_SWEEP_STATIC_SCRATCH_BYTES - 32 KiB        (default config: 4233 entries -> 494 scans);
+ * beyond them the call fails with FVAD_EOUT_OF_MEMORY and a message naming the limit.
+ * All calls share the one array, which keeps the last call's contents (the kernel rewrites what it uses first):
+ * calls that overlap on the GPU race -- serialise them on one stream or with events. */
+#define FVAD_VADM_SWEEP_STATIC_SCRATCH_BYTES (16u << 20)
+#define FVAD_VADM_SWEEP_STATIC_MAX_CONFIGS   256
+int    fvad_vadm_sweep_static(const float *d_min_volume, const float *d_vol_ratio, const float *d_rnn_vad,
+                              size_t n_streams, size_t n_records, uint64_t first_index,
+                              const fvad_vad_machine_config *configs, size_t n_configs, size_t sample_rate,
+                              size_t fft_size, fvad_segment *d_segs, size_t max_segs, uint32_t *d_counts,
+                              void *cuda_stream);
+
 /* ---- Evaluator statistics over many result sets (the sweep's consumer) ------------
  * statistics.fromEvaluator (src/Evaluator/statistics.zig:85-113) on top of Evaluator.initAndRun's overlap matching
  * (src/Evaluator.zig:90-156; SpeechSegment.findOverlapping/overlapWith, src/Evaluator/SpeechSegment.zig:22-49) with
