@@ -43,16 +43,19 @@ struct fvad_batch {
     // tiling
     size_t tile_frames = 0;        // frames of frame_len per row per tile
     size_t work_cap = 0;           // floats per work row
-    float *d_work = nullptr;       // [rows][work_cap]: carry + new input of the tile (= one of d_work_buf)
-    // Host pushes double-buffer the work rows: the next tile's PCM is copied (stream sH) into one buffer while stage A
-    // reads the other, so the host-to-device copy of tile t+1 hides behind the biquad chain of tile t.
+    // Double-buffered work rows [rows][work_cap]: the next tile's PCM is copied (stream sH) into one buffer while stage A
+    // reads the other, so the copy of tile t+1 hides behind the biquad chain of tile t.
     float *d_work_buf[2] = {nullptr, nullptr};
-    float *d_work_next = nullptr;  // where this tile's unconsumed tail goes (the other buffer on host pushes)
-    int work_par = 0;
+    // Pushes APPEND to the filling buffer (copy stream sH: one 2-D copy per push when the caller's rows are equally
+    // strided); its tile is launched when it holds tile_frames frames, or at a sync.  So the launch count depends on the
+    // audio pushed, not on the caller's push size (SimulationInstance.simulateVAD pushes one second at a time), and the
+    // copy of tile t+1 hides behind stage A of tile t.
+    int work_par = 0;              // the filling buffer
+    size_t fill_len = 0;           // valid samples per row in it (a carried partial frame included)
+    bool fill_waited = false;      // sH already waits for the buffer's previous reader
+    bool h2d_dirty = false;        // copies issued on sH since the last evH record
     cudaStream_t sH = nullptr;
     cudaEvent_t evH[2] = {}, evW[2] = {};   // per work buffer: input copied in (sH) / last reader done (input-side stream)
-    float *d_carry = nullptr;      // [rows][frame_len]
-    size_t carry_len = 0;
 
     // denoiser path
     RnnoiseBatch *rn = nullptr;
@@ -152,7 +155,7 @@ extern "C" void fvad_batch_destroy(fvad_batch *b) {
         for (cudaEvent_t e : {b->evS[0], b->evS[1], b->evE[0], b->evE[1]}) if (e) cudaEventDestroy(e);
         if (b->sH) { cudaStreamSynchronize(b->sH); cudaStreamDestroy(b->sH); }
         for (cudaEvent_t e : {b->evH[0], b->evH[1], b->evW[0], b->evW[1]}) if (e) cudaEventDestroy(e);
-        cudaFree(b->d_work_buf[0]); cudaFree(b->d_work_buf[1]); cudaFree(b->d_carry); cudaFree(b->d_den); cudaFree(b->d_den_carry);
+        cudaFree(b->d_work_buf[0]); cudaFree(b->d_work_buf[1]); cudaFree(b->d_den); cudaFree(b->d_den_carry);
         cudaFree(b->d_ratio480); cudaFree(b->d_vad480); cudaFree(b->d_band); cudaFree(b->d_ratio_stft);
         cudaFree(b->d_vad_stft); cudaFree(b->d_spectra); cudaFree(b->d_params); cudaFree(b->d_states);
         cudaFree(b->d_rings); cudaFree(b->d_segs); cudaFree(b->d_seg_count); cudaFree(b->d_events);
@@ -286,13 +289,11 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
     b->work_cap = (b->work_cap + 3) & ~(size_t)3;
     for (int i = 0; i < 2; i++)
         if ((rc = dmalloc(&b->d_work_buf[i], b->rows * b->work_cap)) != FVAD_OK) return fail(rc);
-    b->d_work = b->d_work_next = b->d_work_buf[0];
     if (cudaStreamCreateWithFlags(&b->sH, cudaStreamNonBlocking) != cudaSuccess)
         return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
     for (cudaEvent_t *e : {&b->evH[0], &b->evH[1], &b->evW[0], &b->evW[1]})
         if (cudaEventCreateWithFlags(e, cudaEventDisableTiming) != cudaSuccess)
             return fail(set_error(FVAD_ECUDA, "cudaEventCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
-    if ((rc = dmalloc(&b->d_carry, b->rows * (size_t)b->frame_len)) != FVAD_OK) return fail(rc);
     if (b->use_denoiser) {
         b->den_cap = (tf * kRnFrame + b->fft_size + 3) & ~(size_t)3;
         b->stride480 = fvad_batch::kHist480 + tf;
@@ -337,7 +338,6 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
 }
 
 // ------------------------------------------------------------------------------------------
-// one tile: d_work rows hold carry_len + m valid samples
 // ------------------------------------------------------------------------------------------
 static int trace_tile(fvad_batch *b, size_t F, size_t J, size_t den_before) {
     FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
@@ -392,8 +392,10 @@ static int run_machines(fvad_batch *b, int par, bool with_vad, unsigned long lon
     return vadm_launch(b->d_params, b->d_states, b->d_rings, b->S, b->n_machines, io, st);
 }
 
-static int process_tile(fvad_batch *b, size_t m) {
-    const size_t avail = b->carry_len + m;
+// One tile: rows of `avail` valid samples at in[row * in_stride] (a work buffer, or the caller's device rows).  Whole
+// frames are consumed; the unconsumed tail (< one frame) is copied to the front of `next` (may be null when avail is a
+// whole number of frames).
+static int process_tile(fvad_batch *b, const float *in, size_t in_stride, size_t avail, float *next, size_t *tail_out) {
     const size_t F = avail / b->frame_len, used = F * b->frame_len;
     size_t J = 0, den_before = b->den_carry;
     cudaStream_t sA = b->use_denoiser ? b->sA : b->stream, sD = b->stream;   // the input side lives on sA
@@ -401,8 +403,8 @@ static int process_tile(fvad_batch *b, size_t m) {
         float *spec = (b->trace_flags & FVAD_TRACE_SPECTRA) ? b->d_spectra : nullptr;
         if (!b->use_denoiser) {
             J = F;
-            FVAD_TRY(rms_ratio_launch(b->d_work, b->work_cap, b->S, (int)b->C, F, b->fft_size, b->d_ratio_stft, b->max_stft, 0, sD));
-            FVAD_TRY(stft_launch(*b->tabs, b->d_work, b->rows, b->work_cap, F, b->fft_size, b->bands, b->d_band, b->max_stft, 0,
+            FVAD_TRY(rms_ratio_launch(in, in_stride, b->S, (int)b->C, F, b->fft_size, b->d_ratio_stft, b->max_stft, 0, sD));
+            FVAD_TRY(stft_launch(*b->tabs, in, b->rows, in_stride, F, b->fft_size, b->bands, b->d_band, b->max_stft, 0,
                                  spec, nullptr, 0.f, b->device, sD));
             FVAD_TRY(run_machines(b, 0, false, b->read_count, J, sD));
         } else {
@@ -410,10 +412,10 @@ static int process_tile(fvad_batch *b, size_t m) {
             // stage X-1 of this tile (event); a slot is reused only after its previous tile left stage D.
             const int slot = (int)(b->tile_no % (unsigned)b->n_slots);
             b->tile_no++;
-            // stage A (sA): channel RMS ratio + biquad; the tile's PCM is already in d_work (same stream)
+            // stage A (sA): channel RMS ratio + biquad; the tile's PCM is in place (sA has waited for the copy)
             FVAD_CUDA_TRY(cudaStreamWaitEvent(sA, b->evD[slot], 0));
-            FVAD_TRY(rms_ratio_launch(b->d_work, b->work_cap, b->S, (int)b->C, F, kRnFrame, b->d_ratio_slot[slot], b->tile_frames, 0, sA));
-            FVAD_TRY(rnnoise_stage_a(b->rn, slot, b->d_work, b->work_cap, (int)b->C, F, sA));
+            FVAD_TRY(rms_ratio_launch(in, in_stride, b->S, (int)b->C, F, kRnFrame, b->d_ratio_slot[slot], b->tile_frames, 0, sA));
+            FVAD_TRY(rnnoise_stage_a(b->rn, slot, in, in_stride, (int)b->C, F, sA));
             FVAD_CUDA_TRY(cudaEventRecord(b->evA[slot], sA));
             // stage B1 (sB): analysis + pitch correlations, frame-parallel
             FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sB, b->evA[slot], 0));
@@ -468,13 +470,14 @@ static int process_tile(fvad_batch *b, size_t m) {
     b->read_count += b->cfg.skip_processing ? 0 : used;
     const size_t consumed = b->cfg.skip_processing ? avail : used;   // skip_processing: samples are only buffered by the reference
     const size_t tail = avail - consumed;
-    if (consumed > 0 && tail > 0) {
-        FVAD_TRY(copy_rows_launch(b->d_carry, b->frame_len, 0, b->d_work, b->work_cap, consumed, b->rows, tail, sA));
-        FVAD_TRY(copy_rows_launch(b->d_work_next, b->work_cap, 0, b->d_carry, b->frame_len, 0, b->rows, tail, sA));
+    if (tail > 0) {
+        if (!next) return set_error(FVAD_EINVALID_ARGUMENT, "internal: a tile with a partial frame needs a carry target");
+        FVAD_TRY(copy_rows_launch(next, b->work_cap, 0, in, in_stride, consumed, b->rows, tail, sA));
     }
-    b->carry_len = tail;
+    *tail_out = tail;
     return FVAD_OK;
 }
+
 
 // The main stream waits for the machines of the last tile (stage E): whoever synchronises with, or records an event on,
 // the batch's stream after a push sees every segment that push produced.
@@ -490,34 +493,69 @@ static int ensure_trace_buffers(fvad_batch *b) {
     return FVAD_OK;
 }
 
+// Samples per row a work buffer takes before its tile is launched.
+static size_t tile_samples(const fvad_batch *b) { return b->tile_frames * (size_t)b->frame_len; }
+
+// The filling buffer becomes a tile (stages A..E are enqueued); the other buffer becomes the filling one and starts
+// with the partial frame left over, if any.
+static int launch_tile(fvad_batch *b) {
+    const int cur = b->work_par;
+    if (!b->cfg.skip_processing && b->fill_len / b->frame_len == 0) return FVAD_OK;     // no complete frame yet
+    cudaStream_t sIn = b->use_denoiser ? b->sA : b->stream;
+    if (b->h2d_dirty) {
+        FVAD_CUDA_TRY(cudaEventRecord(b->evH[cur], b->sH));
+        FVAD_CUDA_TRY(cudaStreamWaitEvent(sIn, b->evH[cur], 0));
+        b->h2d_dirty = false;
+    }
+    size_t tail = 0;
+    FVAD_TRY(process_tile(b, b->d_work_buf[cur], b->work_cap, b->fill_len, b->d_work_buf[cur ^ 1], &tail));
+    FVAD_CUDA_TRY(cudaEventRecord(b->evW[cur], sIn));                                   // this buffer may be refilled after that
+    b->work_par = cur ^ 1;
+    b->fill_len = tail;
+    b->fill_waited = false;
+    return join_machines(b);
+}
+
+// Before the first copy into the filling buffer since it changed hands: its previous tile must have been read.
+static int fill_begin(fvad_batch *b) {
+    if (!b->fill_waited) {
+        FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sH, b->evW[b->work_par], 0));
+        b->fill_waited = true;
+    }
+    return FVAD_OK;
+}
+
 extern "C" int fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n, uint64_t *first_index) {
     if (!b || (!pcm && n)) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_push: null argument");
     DeviceGuard g(b->device);
     if (!g.ok) return set_error(FVAD_ECUDA, "cannot select device %d", b->device);
     if (first_index) *first_index = b->total_write_count;
     FVAD_TRY(ensure_trace_buffers(b));
-    const size_t m_max = b->tile_frames * (size_t)b->frame_len;
-    cudaStream_t sIn = b->use_denoiser ? b->sA : b->stream;
+    // equally strided rows (every caller that keeps its streams in one array): one 2-D copy per tile instead of one
+    // copy per row.  cudaMemcpy2DAsync limits the pitch to the device's memPitch (2 GiB - 1).
+    ptrdiff_t stride = 0;
+    bool strided = n > 0;
+    if (strided && b->rows > 1) {
+        stride = pcm[1] - pcm[0];
+        for (size_t r = 2; r < b->rows && strided; r++) strided = (pcm[r] - pcm[r - 1]) == stride;
+        strided = strided && stride >= (ptrdiff_t)n && (size_t)stride * sizeof(float) < ((size_t)1 << 31);
+    } else if (strided) stride = (ptrdiff_t)n;
     for (size_t off = 0; off < n;) {
-        const size_t m = std::min(m_max, n - off);
-        const int cur = b->work_par;
-        // a tile that completes no frame leaves everything in place: its successor appends to the same buffer
-        const bool moves_on = b->cfg.skip_processing || (b->carry_len + m) / b->frame_len > 0;
-        b->d_work = b->d_work_buf[cur];
-        b->d_work_next = b->d_work_buf[moves_on ? cur ^ 1 : cur];
-        FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sH, b->evW[cur], 0));             // the buffer's previous tile has been read
-        for (size_t r = 0; r < b->rows; r++)
-            FVAD_CUDA_TRY(cudaMemcpyAsync(b->d_work + r * b->work_cap + b->carry_len, pcm[r] + off, sizeof(float) * m,
-                                          cudaMemcpyHostToDevice, b->sH));
-        FVAD_CUDA_TRY(cudaEventRecord(b->evH[cur], b->sH));
-        FVAD_CUDA_TRY(cudaStreamWaitEvent(sIn, b->evH[cur], 0));
-        FVAD_TRY(process_tile(b, m));
-        FVAD_CUDA_TRY(cudaEventRecord(b->evW[cur], sIn));
-        if (moves_on) b->work_par = cur ^ 1;
+        const size_t m = std::min(tile_samples(b) - b->fill_len, n - off);
+        FVAD_TRY(fill_begin(b));
+        float *dst = b->d_work_buf[b->work_par] + b->fill_len;
+        if (strided) {
+            FVAD_CUDA_TRY(cudaMemcpy2DAsync(dst, b->work_cap * sizeof(float), pcm[0] + off, (size_t)stride * sizeof(float),
+                                            m * sizeof(float), b->rows, cudaMemcpyHostToDevice, b->sH));
+        } else {
+            for (size_t r = 0; r < b->rows; r++)
+                FVAD_CUDA_TRY(cudaMemcpyAsync(dst + r * b->work_cap, pcm[r] + off, sizeof(float) * m, cudaMemcpyHostToDevice, b->sH));
+        }
+        b->h2d_dirty = true;
+        b->fill_len += m;
         off += m;
+        if (b->fill_len == tile_samples(b)) FVAD_TRY(launch_tile(b));
     }
-    b->d_work = b->d_work_next = b->d_work_buf[b->work_par];
-    FVAD_TRY(join_machines(b));
     b->total_write_count += n;
     // input is borrowed only until return (AudioPipeline.pushSamples copies into its ring): wait for the copies
     // only; the stages keep running behind the caller's back until fvad_batch_sync
@@ -532,21 +570,41 @@ extern "C" int fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t 
     if (!g.ok) return set_error(FVAD_ECUDA, "cannot select device %d", b->device);
     if (first_index) *first_index = b->total_write_count;
     FVAD_TRY(ensure_trace_buffers(b));
-    const size_t m_max = b->tile_frames * (size_t)b->frame_len;
+    // rows (stream, channel) at one stride: a whole tile is read where it lies, no staging copy
+    const bool uniform = b->C == 1 || stream_stride == b->C * channel_stride;
+    const size_t row_stride = b->C == 1 ? stream_stride : channel_stride;
+    const bool pitch_ok = stream_stride * sizeof(float) < ((size_t)1 << 31);
     for (size_t off = 0; off < n;) {
-        const size_t m = std::min(m_max, n - off);
-        FVAD_TRY(gather_rows_launch(b->d_work, b->work_cap, b->carry_len, d_pcm, stream_stride, channel_stride, off, b->S,
-                                    (int)b->C, m, b->use_denoiser ? b->sA : b->stream));
-        FVAD_TRY(process_tile(b, m));
-        FVAD_CUDA_TRY(cudaEventRecord(b->evW[b->work_par], b->use_denoiser ? b->sA : b->stream));   // a later host push waits for it
+        if (b->fill_len == 0 && uniform && n - off >= tile_samples(b)) {
+            size_t tail = 0;
+            FVAD_TRY(process_tile(b, d_pcm + off, row_stride, tile_samples(b), nullptr, &tail));
+            FVAD_TRY(join_machines(b));
+            off += tile_samples(b);
+            continue;
+        }
+        const size_t m = std::min(tile_samples(b) - b->fill_len, n - off);
+        FVAD_TRY(fill_begin(b));
+        float *dst = b->d_work_buf[b->work_par] + b->fill_len;
+        if (pitch_ok) {
+            for (size_t c = 0; c < b->C; c++)          // channel c of every stream: one 2-D device-to-device copy
+                FVAD_CUDA_TRY(cudaMemcpy2DAsync(dst + c * b->work_cap, b->C * b->work_cap * sizeof(float),
+                                                d_pcm + c * channel_stride + off, stream_stride * sizeof(float), m * sizeof(float),
+                                                b->S, cudaMemcpyDeviceToDevice, b->sH));
+        } else {
+            FVAD_TRY(gather_rows_launch(b->d_work_buf[b->work_par], b->work_cap, b->fill_len, d_pcm, stream_stride, channel_stride,
+                                        off, b->S, (int)b->C, m, b->sH));
+        }
+        b->h2d_dirty = true;
+        b->fill_len += m;
         off += m;
+        if (b->fill_len == tile_samples(b)) FVAD_TRY(launch_tile(b));
     }
-    FVAD_TRY(join_machines(b));
     b->total_write_count += n;
     return FVAD_OK;
 }
 
 static int collect(fvad_batch *b) {
+    FVAD_TRY(launch_tile(b));                                  // whatever complete frames the filling buffer holds
     FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
     if (!b->dirty) return FVAD_OK;
     unsigned ns = 0, ne = 0;
@@ -595,8 +653,9 @@ extern "C" int fvad_batch_reset(fvad_batch *b) {
         FVAD_CUDA_TRY(cudaMemsetAsync(b->d_ratio480, 0, sizeof(float) * b->S * b->stride480, b->stream));
         FVAD_CUDA_TRY(cudaMemsetAsync(b->d_vad480, 0, sizeof(float) * b->S * b->stride480, b->stream));
     }
-    b->carry_len = 0; b->den_carry = 0; b->base480 = 0; b->tile_no = 0; b->stft_tile_no = 0; b->e_pending = -1;
-    b->work_par = 0; b->d_work = b->d_work_next = b->d_work_buf[0];
+    b->fill_len = 0; b->fill_waited = false; b->h2d_dirty = false;
+    b->den_carry = 0; b->base480 = 0; b->tile_no = 0; b->stft_tile_no = 0; b->e_pending = -1;
+    b->work_par = 0;
     b->total_write_count = b->read_count = b->stft_done = 0;
     for (auto &v : b->segs) v.clear();
     for (auto &v : b->events) v.clear();
@@ -628,7 +687,10 @@ extern "C" int fvad_batch_events(fvad_batch *b, size_t stream, const fvad_captur
 extern "C" int fvad_batch_counts(fvad_batch *b, uint64_t *total_write_count, uint64_t *pipeline_read_count) {
     if (!b) return set_error(FVAD_EINVALID_ARGUMENT, "null batch");
     if (total_write_count) *total_write_count = b->total_write_count;
-    if (pipeline_read_count) *pipeline_read_count = b->read_count;
+    // VAD.run consumes every whole frame before pushSamples returns (VAD.zig:214-251); here the frames of the filling
+    // buffer are consumed at the next tile launch, which does not change the count the reference reports
+    if (pipeline_read_count)
+        *pipeline_read_count = b->cfg.skip_processing ? 0 : (b->total_write_count / b->frame_len) * (uint64_t)b->frame_len;
     return FVAD_OK;
 }
 
