@@ -79,9 +79,18 @@ struct fvad_batch {
     VadmState *d_states = nullptr;
     double *d_rings = nullptr;
     std::vector<VadmParams> h_params;
-    std::vector<VadmState> h_states0;
-    std::vector<double> h_rings0;
     size_t rings_per_stream = 0;
+    // result arenas: appended on the device, drained at a sync -- or earlier, when the counters (mirrored into pinned host
+    // memory after every tile, read without waiting) say an arena is half full
+    unsigned *h_arena_cnt = nullptr;       // pinned [2]: segments, events (a value the device has reached: a lower bound)
+    // FVAD_KEEP_FEATURES: the per-STFT-frame features of the whole run stay in HBM for fvad_batch_sweep
+    float *d_feat_min = nullptr, *d_feat_ratio = nullptr, *d_feat_vad = nullptr;   // [bands][S][feat_cap], [S][feat_cap] x 2
+    size_t feat_cap = 0;
+    // sweep scratch, kept between calls
+    VadmParams *d_sw_params = nullptr; size_t sw_params_cap = 0;
+    double *d_sw_rings = nullptr; size_t sw_rings_cap = 0;
+    fvad_segment *d_sw_segs = nullptr; size_t sw_segs_cap = 0;
+    uint32_t *d_sw_counts = nullptr; size_t sw_counts_cap = 0;
     SegRecord *d_segs = nullptr; unsigned *d_seg_count = nullptr; unsigned seg_cap = 0;
     EventRecord *d_events = nullptr; unsigned *d_event_count = nullptr; unsigned event_cap = 0;
     fvad_stft_record *d_trace = nullptr;   // [S][max_stft]
@@ -130,13 +139,11 @@ int freq_to_bin(size_t sample_rate, size_t n_fft, float freq, int *bin) {   // F
     return FVAD_OK;
 }
 
-int upload_machine_state(fvad_batch *b) {
-    FVAD_CUDA_TRY(cudaMemcpyAsync(b->d_states, b->h_states0.data(), sizeof(VadmState) * b->h_states0.size(),
-                                  cudaMemcpyHostToDevice, b->stream));
-    FVAD_CUDA_TRY(cudaMemcpyAsync(b->d_rings, b->h_rings0.data(), sizeof(double) * b->h_rings0.size(),
-                                  cudaMemcpyHostToDevice, b->stream));
+int upload_machine_state(fvad_batch *b) {       // VADMachine.init for every (stream, machine), on the device
+    FVAD_TRY(vadm_init_launch(b->d_params, b->d_states, b->d_rings, b->S, b->n_machines, b->stream));
     FVAD_CUDA_TRY(cudaMemsetAsync(b->d_seg_count, 0, sizeof(unsigned), b->stream));
     FVAD_CUDA_TRY(cudaMemsetAsync(b->d_event_count, 0, sizeof(unsigned), b->stream));
+    if (b->h_arena_cnt) b->h_arena_cnt[0] = b->h_arena_cnt[1] = 0;
     return FVAD_OK;
 }
 
@@ -160,6 +167,9 @@ extern "C" void fvad_batch_destroy(fvad_batch *b) {
         cudaFree(b->d_vad_stft); cudaFree(b->d_spectra); cudaFree(b->d_params); cudaFree(b->d_states);
         cudaFree(b->d_rings); cudaFree(b->d_segs); cudaFree(b->d_seg_count); cudaFree(b->d_events);
         cudaFree(b->d_event_count); cudaFree(b->d_trace);
+        cudaFree(b->d_feat_min); cudaFree(b->d_feat_ratio); cudaFree(b->d_feat_vad);
+        cudaFree(b->d_sw_params); cudaFree(b->d_sw_rings); cudaFree(b->d_sw_segs); cudaFree(b->d_sw_counts);
+        if (b->h_arena_cnt) cudaFreeHost(b->h_arena_cnt);
         for (cudaStream_t st : {b->sA, b->sB, b->sB2, b->sC, b->sE}) if (st && st != b->stream) cudaStreamDestroy(st);
         if (b->stream) cudaStreamDestroy(b->stream);
     }
@@ -207,20 +217,20 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
         // (measured: ~5 ms per tile, 6 % of the step); then C, then B, then D in chain-length order.
         // Throughput regime (SMs saturated): what matters is that the SMALL kernels between the big ones (history copies,
         // scans, carries: a few CTAs each) do not wait for a 30 000-CTA grid to be dispatched -- measured with
-        // FVAD_TIMELINE: a 10 us copy took 3 ms -- and that older tiles drain first, so later stages outrank earlier ones.
-        // FVAD_PRIO="a,b1,b2,c,d,e" overrides the ranks.
+        // knob timeline: a 10 us copy took 3 ms -- and that older tiles drain first, so later stages outrank earlier ones.
+        // knob prio="a,b1,b2,c,d,e" overrides the ranks.
         int lo = 0, hi = 0;
         if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess) lo = hi = 0;      // hi = numerically lowest = most urgent
         int rank[6] = {0, 2, 2, 1, 99, 2};                                               // A, B1, B2, C, D, E
         if (!latency_regime(n_streams, b->device)) { const int thr[6] = {0, 5, 4, 3, 2, 1}; for (int i = 0; i < 6; i++) rank[i] = thr[i]; }
-        if (const char *e = getenv("FVAD_PRIO")) {
+        if (const char *e = debug_knob("prio")) {
             int v[6];
             if (sscanf(e, "%d,%d,%d,%d,%d,%d", &v[0], &v[1], &v[2], &v[3], &v[4], &v[5]) == 6) for (int i = 0; i < 6; i++) rank[i] = v[i];
         }
         auto prio = [&](int r) { const int p = hi + (r < 0 ? 0 : r); return p > lo ? lo : p; };
         if (cudaStreamCreateWithPriority(&b->stream, cudaStreamNonBlocking, prio(rank[4])) != cudaSuccess)
             return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
-        if (getenv("FVAD_SERIAL_STAGES")) {
+        if (debug_knob("serial_stages")) {
             // measurement aid: all stages on one stream, so the per-kernel event times are free of overlap
             b->sA = b->sB = b->sB2 = b->sC = b->sE = b->stream;
         } else if (cudaStreamCreateWithPriority(&b->sA, cudaStreamNonBlocking, prio(rank[0])) != cudaSuccess ||
@@ -231,7 +241,7 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
             return fail(set_error(FVAD_ECUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError())));
     }
     {
-        const char *es = getenv("FVAD_SLOTS");
+        const char *es = debug_knob("slots");
         int ns = es ? atoi(es) : 3;
         b->n_slots = ns < 1 ? 1 : ns > fvad_batch::kMaxSlots ? fvad_batch::kMaxSlots : ns;
         for (int i = 0; i < b->n_slots; i++)
@@ -265,14 +275,9 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
         ring_off += nd;
     }
     b->rings_per_stream = ring_off;
-    b->h_states0.resize(b->S * b->n_machines);
-    b->h_rings0.resize(b->S * ring_off);
-    for (size_t s = 0; s < b->S; s++)
-        for (int k = 0; k < b->n_machines; k++)
-            vadm_init_host(b->h_params[k], &b->h_states0[s * b->n_machines + k], &b->h_rings0[s * ring_off + b->h_params[k].ring_off]);
 
     // tile geometry
-    const char *env = getenv("FVAD_TILE_FRAMES");
+    const char *env = debug_knob("tile_frames");
     size_t tf;
     if (b->use_denoiser) {
         tf = 131072 / b->rows;
@@ -312,9 +317,19 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
     if ((rc = dmalloc(&b->d_ratio_stft, 2 * b->S * b->max_stft)) != FVAD_OK) return fail(rc);
     if ((rc = dmalloc(&b->d_vad_stft, 2 * b->S * b->max_stft)) != FVAD_OK) return fail(rc);
     if ((rc = dmalloc(&b->d_params, (size_t)b->n_machines)) != FVAD_OK) return fail(rc);
-    if ((rc = dmalloc(&b->d_states, b->h_states0.size())) != FVAD_OK) return fail(rc);
-    if ((rc = dmalloc(&b->d_rings, b->h_rings0.size())) != FVAD_OK) return fail(rc);
-    b->seg_cap = 1u << 20; b->event_cap = 1u << 21;
+    if ((rc = dmalloc(&b->d_states, b->S * (size_t)b->n_machines)) != FVAD_OK) return fail(rc);
+    if ((rc = dmalloc(&b->d_rings, b->S * b->rings_per_stream)) != FVAD_OK) return fail(rc);
+    {
+        // A machine completes at most one segment (and reports at most two state changes) per three STFT frames; up to
+        // n_slots + 2 tiles are in flight behind the mirrored counters.  Four times that, within [2^20, 2^24] records.
+        const size_t per_tile = b->S * (size_t)b->n_machines * (b->max_stft / 3 + 1);
+        const size_t want = 4 * (size_t)(b->n_slots + 2) * per_tile;
+        b->seg_cap = (unsigned)std::min<size_t>(std::max<size_t>(want, (size_t)1 << 20), (size_t)1 << 24);
+        b->event_cap = (unsigned)std::min<size_t>(std::max<size_t>(2 * want / (size_t)b->n_machines, (size_t)1 << 20), (size_t)1 << 24);
+    }
+    if (cudaHostAlloc((void **)&b->h_arena_cnt, 2 * sizeof(unsigned), cudaHostAllocDefault) != cudaSuccess)
+        return fail(set_error(FVAD_EOUT_OF_MEMORY, "cudaHostAlloc failed: %s", cudaGetErrorString(cudaGetLastError())));
+    b->h_arena_cnt[0] = b->h_arena_cnt[1] = 0;
     if ((rc = dmalloc(&b->d_segs, (size_t)b->seg_cap)) != FVAD_OK) return fail(rc);
     if ((rc = dmalloc(&b->d_events, (size_t)b->event_cap)) != FVAD_OK) return fail(rc);
     if ((rc = dmalloc(&b->d_seg_count, (size_t)1)) != FVAD_OK) return fail(rc);
@@ -339,6 +354,7 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
 
 // ------------------------------------------------------------------------------------------
 // ------------------------------------------------------------------------------------------
+constexpr unsigned kHostTraces = FVAD_TRACE_RECORDS | FVAD_TRACE_DENOISED | FVAD_TRACE_RNN_VAD | FVAD_TRACE_SPECTRA;
 static int trace_tile(fvad_batch *b, size_t F, size_t J, size_t den_before) {
     FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
     if (b->sE) FVAD_CUDA_TRY(cudaStreamSynchronize(b->sE));   // the records trace is written by the machines
@@ -379,6 +395,28 @@ static float *band_buf(fvad_batch *b, int par) { return b->d_band + (size_t)par 
 static float *ratio_buf(fvad_batch *b, int par) { return b->d_ratio_stft + (size_t)par * b->S * b->max_stft; }
 static float *vad_buf(fvad_batch *b, int par) { return b->d_vad_stft + (size_t)par * b->S * b->max_stft; }
 
+// The kept features grow with the run: capacity doubles (a rare stop-the-world copy; every stream of the batch waits).
+static int ensure_feature_capacity(fvad_batch *b, size_t need) {
+    if (need <= b->feat_cap) return FVAD_OK;
+    size_t cap = b->feat_cap ? b->feat_cap : 4096;
+    while (cap < need) cap *= 2;
+    for (cudaStream_t st : {b->sH, b->sA, b->sB, b->sB2, b->sC, b->sE, b->stream}) if (st) FVAD_CUDA_TRY(cudaStreamSynchronize(st));
+    float *nm = nullptr, *nr = nullptr, *nv = nullptr;
+    const size_t rows_min = (size_t)b->bands.n_bands * b->S;
+    FVAD_TRY(dmalloc(&nm, rows_min * cap));
+    FVAD_TRY(dmalloc(&nr, b->S * cap));
+    FVAD_TRY(dmalloc(&nv, b->S * cap));
+    if (b->feat_cap && b->stft_done) {
+        const size_t w = b->stft_done * sizeof(float);
+        FVAD_CUDA_TRY(cudaMemcpy2D(nm, cap * sizeof(float), b->d_feat_min, b->feat_cap * sizeof(float), w, rows_min, cudaMemcpyDeviceToDevice));
+        FVAD_CUDA_TRY(cudaMemcpy2D(nr, cap * sizeof(float), b->d_feat_ratio, b->feat_cap * sizeof(float), w, b->S, cudaMemcpyDeviceToDevice));
+        FVAD_CUDA_TRY(cudaMemcpy2D(nv, cap * sizeof(float), b->d_feat_vad, b->feat_cap * sizeof(float), w, b->S, cudaMemcpyDeviceToDevice));
+    }
+    cudaFree(b->d_feat_min); cudaFree(b->d_feat_ratio); cudaFree(b->d_feat_vad);
+    b->d_feat_min = nm; b->d_feat_ratio = nr; b->d_feat_vad = nv; b->feat_cap = cap;
+    return FVAD_OK;
+}
+
 static int run_machines(fvad_batch *b, int par, bool with_vad, unsigned long long first_index, size_t J, cudaStream_t st) {
     VadmIo io{};
     io.band = band_buf(b, par); io.band_rows = b->rows; io.band_frame_stride = b->max_stft;
@@ -389,7 +427,17 @@ static int run_machines(fvad_batch *b, int par, bool with_vad, unsigned long lon
     io.events = b->d_events; io.event_count = b->d_event_count; io.event_cap = b->event_cap;
     io.trace = (b->trace_flags & FVAD_TRACE_RECORDS) ? b->d_trace : nullptr;
     io.trace_stride = b->max_stft; io.trace_offset = 0;
-    return vadm_launch(b->d_params, b->d_states, b->d_rings, b->S, b->n_machines, io, st);
+    if (b->trace_flags & FVAD_KEEP_FEATURES) {
+        FVAD_TRY(ensure_feature_capacity(b, b->stft_done + J));
+        io.feat_min = b->d_feat_min; io.feat_ratio = b->d_feat_ratio; io.feat_vad = b->d_feat_vad;
+        io.feat_stride = b->feat_cap; io.feat_offset = b->stft_done; io.feat_band_stride = b->S * b->feat_cap;
+        io.feat_bands = b->bands.n_bands;
+    }
+    FVAD_TRY(vadm_launch(b->d_params, b->d_states, b->d_rings, b->S, b->n_machines, io, st));
+    // the arena counters as of this tile, for the host to look at without waiting (launch_tile)
+    FVAD_CUDA_TRY(cudaMemcpyAsync(&b->h_arena_cnt[0], b->d_seg_count, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    FVAD_CUDA_TRY(cudaMemcpyAsync(&b->h_arena_cnt[1], b->d_event_count, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    return FVAD_OK;
 }
 
 // One tile: rows of `avail` valid samples at in[row * in_stride] (a work buffer, or the caller's device rows).  Whole
@@ -451,7 +499,7 @@ static int process_tile(fvad_batch *b, const float *in, size_t in_stride, size_t
                 FVAD_CUDA_TRY(cudaEventRecord(b->evE[par], b->sE));
                 b->e_pending = par;
             }
-            if (b->trace_flags) FVAD_TRY(trace_tile(b, F, J, den_before));
+            if (b->trace_flags & kHostTraces) FVAD_TRY(trace_tile(b, F, J, den_before));
             const size_t tail = den_avail - J * b->fft_size;
             if (J > 0 && tail > 0) {
                 FVAD_TRY(copy_rows_launch(b->d_den_carry, b->fft_size, 0, b->d_den, b->den_cap, J * b->fft_size, b->rows, tail, sD));
@@ -463,7 +511,7 @@ static int process_tile(fvad_batch *b, const float *in, size_t in_stride, size_t
             b->base480 += (long long)F;
             FVAD_CUDA_TRY(cudaEventRecord(b->evD[slot], sD));
         }
-        if (!b->use_denoiser && b->trace_flags) FVAD_TRY(trace_tile(b, F, J, 0));
+        if (!b->use_denoiser && (b->trace_flags & kHostTraces)) FVAD_TRY(trace_tile(b, F, J, 0));
         b->stft_done += J;
         b->dirty = true;
     }
@@ -493,6 +541,14 @@ static int ensure_trace_buffers(fvad_batch *b) {
     return FVAD_OK;
 }
 
+static int drain_results(fvad_batch *b);
+
+// An arena half full (as of the last tile the device has finished): drain it to the host lists before adding more.
+static int arena_check(fvad_batch *b) {
+    if (b->h_arena_cnt[0] > b->seg_cap / 2 || b->h_arena_cnt[1] > b->event_cap / 2) return drain_results(b);
+    return FVAD_OK;
+}
+
 // Samples per row a work buffer takes before its tile is launched.
 static size_t tile_samples(const fvad_batch *b) { return b->tile_frames * (size_t)b->frame_len; }
 
@@ -502,6 +558,7 @@ static int launch_tile(fvad_batch *b) {
     const int cur = b->work_par;
     if (!b->cfg.skip_processing && b->fill_len / b->frame_len == 0) return FVAD_OK;     // no complete frame yet
     cudaStream_t sIn = b->use_denoiser ? b->sA : b->stream;
+    FVAD_TRY(arena_check(b));
     if (b->h2d_dirty) {
         FVAD_CUDA_TRY(cudaEventRecord(b->evH[cur], b->sH));
         FVAD_CUDA_TRY(cudaStreamWaitEvent(sIn, b->evH[cur], 0));
@@ -577,6 +634,7 @@ extern "C" int fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t 
     for (size_t off = 0; off < n;) {
         if (b->fill_len == 0 && uniform && n - off >= tile_samples(b)) {
             size_t tail = 0;
+            FVAD_TRY(arena_check(b));
             FVAD_TRY(process_tile(b, d_pcm + off, row_stride, tile_samples(b), nullptr, &tail));
             FVAD_TRY(join_machines(b));
             off += tile_samples(b);
@@ -605,13 +663,19 @@ extern "C" int fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t 
 
 static int collect(fvad_batch *b) {
     FVAD_TRY(launch_tile(b));                                  // whatever complete frames the filling buffer holds
+    return drain_results(b);
+}
+
+static int drain_results(fvad_batch *b) {
+    FVAD_TRY(join_machines(b));
     FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
     if (!b->dirty) return FVAD_OK;
     unsigned ns = 0, ne = 0;
     FVAD_CUDA_TRY(cudaMemcpy(&ns, b->d_seg_count, sizeof ns, cudaMemcpyDeviceToHost));
     FVAD_CUDA_TRY(cudaMemcpy(&ne, b->d_event_count, sizeof ne, cudaMemcpyDeviceToHost));
     if (ns > b->seg_cap || ne > b->event_cap)
-        return set_error(FVAD_EOUT_OF_MEMORY, "segment/event buffer overflow (%u/%u segments, %u/%u events): sync more often", ns, b->seg_cap, ne, b->event_cap);
+        return set_error(FVAD_EOUT_OF_MEMORY, "segment/event arena overflow (%u/%u segments, %u/%u events) although it is drained "
+                         "when half full: more than one result per three STFT frames per machine?", ns, b->seg_cap, ne, b->event_cap);
     if (ns) {
         std::vector<SegRecord> tmp(ns);
         FVAD_CUDA_TRY(cudaMemcpy(tmp.data(), b->d_segs, sizeof(SegRecord) * ns, cudaMemcpyDeviceToHost));
@@ -633,6 +697,7 @@ static int collect(fvad_batch *b) {
         for (auto &r : tmp) b->events[r.stream].push_back(r.ev);
         FVAD_CUDA_TRY(cudaMemset(b->d_event_count, 0, sizeof(unsigned)));
     }
+    b->h_arena_cnt[0] = b->h_arena_cnt[1] = 0;
     b->dirty = false;
     return FVAD_OK;
 }
@@ -691,6 +756,100 @@ extern "C" int fvad_batch_counts(fvad_batch *b, uint64_t *total_write_count, uin
     // buffer are consumed at the next tile launch, which does not change the count the reference reports
     if (pipeline_read_count)
         *pipeline_read_count = b->cfg.skip_processing ? 0 : (b->total_write_count / b->frame_len) * (uint64_t)b->frame_len;
+    return FVAD_OK;
+}
+
+// ---- alt machines after the fact, on the device (BASELINE configs[4]) ------------------------------------------------
+template <class T> static int grow(T **p, size_t *cap, size_t need) {
+    if (need <= *cap) return FVAD_OK;
+    cudaFree(*p); *p = nullptr; *cap = 0;
+    FVAD_TRY(dmalloc(p, need));
+    *cap = need;
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_sweep(fvad_batch *b, const fvad_vad_machine_config *configs, size_t n_configs, size_t max_segs,
+                                fvad_segment *segs, uint32_t *counts, int outputs_on_device) {
+    if (!b || !configs || !n_configs || !max_segs || !segs || !counts)
+        return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_sweep: null/zero argument");
+    if (!(b->trace_flags & FVAD_KEEP_FEATURES))
+        return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_sweep: the batch does not keep its features (fvad_batch_set_trace with "
+                         "FVAD_KEEP_FEATURES before the first push)");
+    DeviceGuard g(b->device);
+    if (!g.ok) return set_error(FVAD_ECUDA, "cannot select device %d", b->device);
+    FVAD_TRY(collect(b));                                       // everything pushed so far has reached the feature planes
+    std::vector<VadmParams> params(n_configs);
+    for (size_t k = 0; k < n_configs; k++) {
+        size_t nd = 0;
+        FVAD_TRY(vadm_params_from_config(configs[k], b->cfg.sample_rate, (size_t)b->fft_size, &params[k], &nd));
+        int lo = 0, hi = 0;
+        FVAD_TRY(freq_to_bin(b->cfg.sample_rate, (size_t)b->fft_size, configs[k].speech_min_freq, &lo));
+        FVAD_TRY(freq_to_bin(b->cfg.sample_rate, (size_t)b->fft_size, configs[k].speech_max_freq, &hi));
+        int band = -1;
+        for (int i = 0; i < b->bands.n_bands; i++) if (b->bands.lo[i] == lo && b->bands.hi[i] == hi) band = i;
+        if (band < 0)
+            return set_error(FVAD_EUNSUPPORTED, "fvad_batch_sweep: config %zu reads bins %d..%d, a band this batch keeps no sums of "
+                             "(create it with a machine config of that band)", k, lo, hi);
+        params[k].band = band;
+    }
+    const size_t n_scans = b->S * n_configs, n_rec = (size_t)b->stft_done;
+    int max_long = 0, max_short = 0, max_ratio = 0;
+    vadm_sweep_rows(params.data(), n_configs, &max_long, &max_short, &max_ratio);
+    FVAD_TRY(grow(&b->d_sw_params, &b->sw_params_cap, n_configs));
+    FVAD_TRY(grow(&b->d_sw_rings, &b->sw_rings_cap, (size_t)(max_long + max_short + max_ratio) * n_scans));
+    fvad_segment *d_segs = segs; uint32_t *d_counts = counts;
+    if (!outputs_on_device) {
+        FVAD_TRY(grow(&b->d_sw_segs, &b->sw_segs_cap, n_scans * max_segs));
+        FVAD_TRY(grow(&b->d_sw_counts, &b->sw_counts_cap, n_scans));
+        d_segs = b->d_sw_segs; d_counts = b->d_sw_counts;
+    }
+    if (!n_rec) {
+        if (outputs_on_device) FVAD_CUDA_TRY(cudaMemsetAsync(counts, 0, sizeof(uint32_t) * n_scans, b->stream));
+        else memset(counts, 0, sizeof(uint32_t) * n_scans);
+        return FVAD_OK;
+    }
+    FVAD_CUDA_TRY(cudaMemcpyAsync(b->d_sw_params, params.data(), sizeof(VadmParams) * n_configs, cudaMemcpyHostToDevice, b->stream));
+    VadmSweepIo io{};
+    io.min_volume = b->d_feat_min; io.band_stride = b->S * b->feat_cap; io.vol_ratio = b->d_feat_ratio;
+    io.vad = b->use_denoiser ? b->d_feat_vad : nullptr;        // fft_input.vad is null without the denoiser (VAD.zig:306-312)
+    io.rec_stride = b->feat_cap; io.n_records = n_rec;
+    io.first_index = 0; io.index_step = (unsigned long long)b->fft_size;
+    io.segs = d_segs; io.max_segs = max_segs; io.counts = d_counts; io.fallbacks = nullptr;
+    FVAD_TRY(vadm_sweep_launch(b->d_sw_params, b->d_sw_rings, max_long, max_short, b->S, (int)n_configs, io, b->stream));
+    if (!outputs_on_device) {
+        FVAD_CUDA_TRY(cudaMemcpyAsync(counts, d_counts, sizeof(uint32_t) * n_scans, cudaMemcpyDeviceToHost, b->stream));
+        FVAD_CUDA_TRY(cudaMemcpyAsync(segs, d_segs, sizeof(fvad_segment) * n_scans * max_segs, cudaMemcpyDeviceToHost, b->stream));
+    }
+    FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));            // `params` is pageable: it must outlive the copy
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_features(fvad_batch *b, size_t stream, fvad_stft_record *out, size_t cap, size_t *n) {
+    if (!b || stream >= b->S) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_features: bad argument");
+    if (!(b->trace_flags & FVAD_KEEP_FEATURES))
+        return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_features: the batch does not keep its features (FVAD_KEEP_FEATURES)");
+    DeviceGuard g(b->device);
+    if (!g.ok) return set_error(FVAD_ECUDA, "cannot select device %d", b->device);
+    FVAD_TRY(collect(b));
+    const size_t have = (size_t)b->stft_done, m = std::min(cap, have);
+    if (n) *n = have;
+    if (!out || !m) return FVAD_OK;
+    const int band0 = b->h_params[0].band;                      // the MAIN machine's band, as in the records trace
+    std::vector<float> mv(m), rt(m), vd(m);
+    FVAD_CUDA_TRY(cudaMemcpy(mv.data(), b->d_feat_min + ((size_t)band0 * b->S + stream) * b->feat_cap, sizeof(float) * m, cudaMemcpyDeviceToHost));
+    FVAD_CUDA_TRY(cudaMemcpy(rt.data(), b->d_feat_ratio + stream * b->feat_cap, sizeof(float) * m, cudaMemcpyDeviceToHost));
+    FVAD_CUDA_TRY(cudaMemcpy(vd.data(), b->d_feat_vad + stream * b->feat_cap, sizeof(float) * m, cudaMemcpyDeviceToHost));
+    for (size_t f = 0; f < m; f++) {
+        out[f].index = (uint64_t)f * (uint64_t)b->fft_size;
+        out[f].min_volume = mv[f]; out[f].vol_ratio = rt[f]; out[f].rnn_vad = vd[f];
+        out[f].has_vad = b->use_denoiser ? 1.0f : 0.0f;
+    }
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_feature_count(fvad_batch *b, size_t *n_records) {
+    if (!b || !n_records) return set_error(FVAD_EINVALID_ARGUMENT, "null argument");
+    *n_records = (size_t)b->stft_done + 0;
     return FVAD_OK;
 }
 

@@ -40,8 +40,21 @@ void profile_end(cudaStream_t stream) {
     if (!g_prof.empty()) cudaEventRecord(g_prof.back().b, stream);
 }
 
+namespace {
+std::mutex g_knob_mu;
+std::map<std::string, std::string> g_knobs;
+}
+const char *debug_knob(const char *key) {
+    static thread_local std::string copy;
+    std::lock_guard<std::mutex> lk(g_knob_mu);
+    auto it = g_knobs.find(key);
+    if (it == g_knobs.end()) return nullptr;
+    copy = it->second;
+    return copy.c_str();
+}
+
 bool latency_regime(size_t n_chains, int device) {
-    if (const char *e = getenv("FVAD_LATENCY_MODE")) return atoi(e) != 0;
+    if (const char *e = debug_knob("latency_mode")) return atoi(e) != 0;
     // measured on B200 (148 SMs), x real-time latency / throughput rule: 40 chains 28.0k / 22.0k, 80: 47.5k / 37.7k,
     // 110: 48.9k / 47.7k, 148: 49.8k / 54.5k -- the crossover sits near three quarters of the SM count
     return 4 * n_chains <= 3 * (size_t)device_sm_count(device);
@@ -85,7 +98,15 @@ const char *fvad_status_name(int s) {
     }
 }
 
-const char *fvad_version(void) { return "fvad-b200 0.1 (sm_100a)"; }
+int fvad_debug_set(const char *key, const char *value) {
+    std::lock_guard<std::mutex> lk(fvad::g_knob_mu);
+    if (!key) { fvad::g_knobs.clear(); return FVAD_OK; }
+    if (!value) fvad::g_knobs.erase(key);
+    else fvad::g_knobs[key] = value;
+    return FVAD_OK;
+}
+
+const char *fvad_version(void) { return "fvad-b200 0.2 (sm_100a)"; }
 
 int fvad_device_count(void) {
     int n = 0;
@@ -105,9 +126,9 @@ int fvad_profile_report(char *buf, size_t cap) {
     std::map<std::string, std::pair<long, double>> agg;
     {
         std::lock_guard<std::mutex> lk(g_prof_mu);
-        // measurement aid: FVAD_TIMELINE=<file> writes every launch's start / end (ms since the first recorded launch),
+        // measurement aid: knob timeline=<file> writes every launch's start / end (ms since the first recorded launch),
         // which shows how the stages of the wavefront overlap
-        if (const char *tl = getenv("FVAD_TIMELINE")) {
+        if (const char *tl = debug_knob("timeline")) {
             if (FILE *f = (buf && cap && !g_prof.empty()) ? fopen(tl, "w") : nullptr) {
                 fprintf(f, "kernel,start_ms,end_ms\n");
                 for (auto &r : g_prof) {

@@ -62,10 +62,15 @@ constexpr int kRnFrame = 480;      // RNNoise frame (Denoiser.zig:68-70)
 
 inline size_t ceil_div(size_t a, size_t b) { return (a + b - 1) / b; }
 
+// Measurement / test knobs (kernel shapes, tile length, stream priorities ...): set ONLY through fvad_debug_set(); the
+// library never reads the process environment, so a host's environment cannot change kernel selection.  Returns the
+// value set for `key` (a copy valid until the calling thread's next query) or nullptr.
+const char *debug_knob(const char *key);
+
 // Device properties cached per device.
 int device_sm_count(int device);
 // Latency regime = few enough sequential chains that each can own an SM (biquad SM reservation, stage-stream priorities);
-// otherwise throughput regime.  FVAD_LATENCY_MODE=0/1 overrides the default rule (n_chains <= latency_chain_limit).
+// otherwise throughput regime.  knob latency_mode=0/1 overrides the default rule (n_chains <= latency_chain_limit).
 bool latency_regime(size_t n_chains, int device);
 
 }  // namespace fvad

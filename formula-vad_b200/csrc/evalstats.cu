@@ -92,36 +92,53 @@ template <class T> int to_device(T **d, const T *h, size_t n) {
 
 using namespace fvad;
 
-extern "C" int fvad_eval_stats_batch(const fvad_segment *segs, size_t n_sets, size_t max_segs, const uint32_t *counts,
-                                     const uint32_t *set_ref, const float *ref_from, const float *ref_to,
-                                     const uint32_t *ref_offsets, size_t n_refs, size_t sample_rate,
-                                     const fvad_stat_config *config, int device, fvad_single_stats *out) {
+static int eval_stats_run(const fvad_segment *segs, bool on_device, size_t n_sets, size_t max_segs, const uint32_t *counts,
+                          const uint32_t *set_ref, const float *ref_from, const float *ref_to, const uint32_t *ref_offsets,
+                          size_t n_refs, size_t sample_rate, const fvad_stat_config *config, fvad_single_stats *out) {
     if (!segs || !counts || !set_ref || !ref_offsets || !config || !out || !n_sets || !n_refs || !max_segs)
         return set_error(FVAD_EINVALID_ARGUMENT, "fvad_eval_stats_batch: null/zero argument");
     for (size_t i = 0; i < n_sets; i++)
         if (set_ref[i] >= n_refs) return set_error(FVAD_EOUT_OF_RANGE, "set %zu names reference list %u of %zu", i, set_ref[i], n_refs);
     const size_t n_lab = ref_offsets[n_refs];
     if (n_lab && (!ref_from || !ref_to)) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_eval_stats_batch: null reference labels");
-    if (device < 0) FVAD_CUDA_TRY(cudaGetDevice(&device));
-    int prev = 0;
-    FVAD_CUDA_TRY(cudaGetDevice(&prev));
-    FVAD_CUDA_TRY(cudaSetDevice(device));
     fvad_segment *d_segs = nullptr; uint32_t *d_counts = nullptr, *d_set_ref = nullptr, *d_off = nullptr;
     float *d_from = nullptr, *d_to = nullptr; fvad_single_stats *d_out = nullptr;
-    int rc = to_device(&d_segs, segs, n_sets * max_segs);
-    if (rc == FVAD_OK) rc = to_device(&d_counts, counts, n_sets);
+    int rc = FVAD_OK;
+    if (!on_device) {
+        rc = to_device(&d_segs, segs, n_sets * max_segs);
+        if (rc == FVAD_OK) rc = to_device(&d_counts, counts, n_sets);
+    }
     if (rc == FVAD_OK) rc = to_device(&d_set_ref, set_ref, n_sets);
     if (rc == FVAD_OK) rc = to_device(&d_off, ref_offsets, n_refs + 1);
     if (rc == FVAD_OK) rc = to_device(&d_from, ref_from, n_lab);
     if (rc == FVAD_OK) rc = to_device(&d_to, ref_to, n_lab);
     if (rc == FVAD_OK) rc = to_device<fvad_single_stats>(&d_out, nullptr, n_sets);
     if (rc == FVAD_OK) {
-        FVAD_LAUNCH(k_eval_stats, (unsigned)ceil_div(n_sets, 128), 128, 0, 0, d_segs, n_sets, max_segs, d_counts, d_set_ref, d_from,
-                    d_to, d_off, (float)sample_rate, *config, d_out);
+        FVAD_LAUNCH(k_eval_stats, (unsigned)ceil_div(n_sets, 128), 128, 0, 0, on_device ? segs : d_segs, n_sets, max_segs,
+                    on_device ? counts : d_counts, d_set_ref, d_from, d_to, d_off, (float)sample_rate, *config, d_out);
         if (cudaMemcpy(out, d_out, sizeof(fvad_single_stats) * n_sets, cudaMemcpyDeviceToHost) != cudaSuccess)
             rc = set_error(FVAD_ECUDA, "k_eval_stats: %s", cudaGetErrorString(cudaGetLastError()));
     }
     cudaFree(d_segs); cudaFree(d_counts); cudaFree(d_set_ref); cudaFree(d_off); cudaFree(d_from); cudaFree(d_to); cudaFree(d_out);
+    return rc;
+}
+
+extern "C" int fvad_eval_stats_batch(const fvad_segment *segs, size_t n_sets, size_t max_segs, const uint32_t *counts,
+                                     const uint32_t *set_ref, const float *ref_from, const float *ref_to,
+                                     const uint32_t *ref_offsets, size_t n_refs, size_t sample_rate,
+                                     const fvad_stat_config *config, int device, fvad_single_stats *out) {
+    if (device < 0) FVAD_CUDA_TRY(cudaGetDevice(&device));
+    int prev = 0;
+    FVAD_CUDA_TRY(cudaGetDevice(&prev));
+    FVAD_CUDA_TRY(cudaSetDevice(device));
+    const int rc = eval_stats_run(segs, false, n_sets, max_segs, counts, set_ref, ref_from, ref_to, ref_offsets, n_refs, sample_rate, config, out);
     cudaSetDevice(prev);
     return rc;
+}
+
+extern "C" int fvad_eval_stats_batch_device(const fvad_segment *d_segs, size_t n_sets, size_t max_segs, const uint32_t *d_counts,
+                                            const uint32_t *set_ref, const float *ref_from, const float *ref_to,
+                                            const uint32_t *ref_offsets, size_t n_refs, size_t sample_rate,
+                                            const fvad_stat_config *config, fvad_single_stats *out) {
+    return eval_stats_run(d_segs, true, n_sets, max_segs, d_counts, set_ref, ref_from, ref_to, ref_offsets, n_refs, sample_rate, config, out);
 }

@@ -11,6 +11,32 @@
 
 using namespace fvad;
 
+namespace {
+struct SweepBuffers {
+    void *p[8] = {};
+    int n = 0;
+    template <class T> int get(T **out, size_t count) {
+        *out = nullptr;
+        cudaError_t e = cudaMalloc((void **)out, sizeof(T) * (count ? count : 1));
+        if (e != cudaSuccess)
+            return set_error(e == cudaErrorMemoryAllocation ? FVAD_EOUT_OF_MEMORY : FVAD_ECUDA, "cudaMalloc(%zu bytes): %s",
+                             sizeof(T) * count, cudaGetErrorString(e));
+        p[n++] = *out;
+        return FVAD_OK;
+    }
+    ~SweepBuffers() { for (int i = 0; i < n; i++) cudaFree(p[i]); }
+};
+struct LeafDeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit LeafDeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~LeafDeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+}  // namespace
+
 struct fvad_fft {
     size_t n_fft, sample_rate;
     int device;
@@ -76,15 +102,13 @@ extern "C" int fvad_fft_run(fvad_fft *f, const float *first, size_t n_first, con
     if (n_second) memcpy(f->h_in.data() + n_first, second, sizeof(float) * n_second);
     // window norm factor is recomputed per call as the reference does (FFT.zig:94); in-order f32 sum
     const float norm = host_window_norm_factor(window, n_window) / (float)(f->n_fft / 2);
-    int prev = 0;
-    FVAD_CUDA_TRY(cudaGetDevice(&prev));
-    FVAD_CUDA_TRY(cudaSetDevice(f->device));
+    LeafDeviceGuard g(f->device);
+    if (!g.ok) return set_error(FVAD_ECUDA, "cannot select CUDA device %d (no CPU fallback exists)", f->device);
     FVAD_CUDA_TRY(cudaMemcpyAsync(f->d_in, f->h_in.data(), sizeof(float) * f->n_fft, cudaMemcpyHostToDevice, 0));
     FVAD_CUDA_TRY(cudaMemcpyAsync(f->d_window, window, sizeof(float) * f->n_fft, cudaMemcpyHostToDevice, 0));
     StftBands b{}; b.n_bands = 0;
     FVAD_TRY(stft_launch(*f->tabs, f->d_in, 1, f->n_fft, 1, f->n_fft, b, f->d_band, 1, 0, f->d_out, f->d_window, norm, f->device, 0));
     FVAD_CUDA_TRY(cudaMemcpy(result, f->d_out, sizeof(float) * n_result, cudaMemcpyDeviceToHost));
-    FVAD_CUDA_TRY(cudaSetDevice(prev));
     return FVAD_OK;
 }
 
@@ -158,93 +182,65 @@ extern "C" int fvad_spectrogram_compute(const float *samples, size_t n_samples, 
 
 // ---- VADMachine sweep (BASELINE config 5) --------------------------------------------------
 // One scan per (stream, config) over the same records: VAD.stateMachineStep's alt machines
-// (VAD.zig:375-380) run on "shared features".  Machines are laid out as n_configs machines per stream.
+// (VAD.zig:375-380) run on "shared features".  Host records in, host lists out; the scans are vadm_sweep.cu's.
+// A record's vad is `fft_input.vad orelse 0` (VADMachine.zig:240,245): has_vad == 0 contributes 0.  The index of record f
+// is taken as records[s][0].index + f * fft_size; records that say otherwise are rejected.
+
 extern "C" int fvad_vadm_sweep(const fvad_stft_record *records, size_t n_streams, size_t n_records,
                                const fvad_vad_machine_config *configs, size_t n_configs, size_t sample_rate,
                                size_t fft_size, int device, fvad_segment *segs, size_t max_segs, uint32_t *counts) {
-    if (!records || !configs || !segs || !counts || !n_streams || !n_configs)
+    if (!records || !configs || !segs || !counts || !n_streams || !n_configs || !max_segs)
         return set_error(FVAD_EINVALID_ARGUMENT, "fvad_vadm_sweep: null/zero argument");
-    if (device < 0) FVAD_CUDA_TRY(cudaGetDevice(&device));
-    int prev = 0;
-    FVAD_CUDA_TRY(cudaGetDevice(&prev));
-    FVAD_CUDA_TRY(cudaSetDevice(device));
+    if (device < 0) {
+        cudaError_t e = cudaGetDevice(&device);
+        if (e != cudaSuccess) return set_error(FVAD_ECUDA, "cudaGetDevice: %s (no CPU fallback exists)", cudaGetErrorString(e));
+    }
+    LeafDeviceGuard g(device);
+    if (!g.ok) return set_error(FVAD_ECUDA, "cannot select CUDA device %d (no CPU fallback exists)", device);
     std::vector<VadmParams> params(n_configs);
-    size_t ring_off = 0;
     for (size_t k = 0; k < n_configs; k++) {
         size_t nd = 0;
         FVAD_TRY(vadm_params_from_config(configs[k], sample_rate, fft_size, &params[k], &nd));
-        params[k].band = 0;
-        params[k].ring_off = ring_off;
-        ring_off += nd;
+        params[k].band = 0;                                   // the records carry ONE min_volume: the band they were made with
     }
-    std::vector<VadmState> states(n_streams * n_configs);
-    std::vector<double> rings(n_streams * ring_off);
-    for (size_t s = 0; s < n_streams; s++)
-        for (size_t k = 0; k < n_configs; k++)
-            vadm_init_host(params[k], &states[s * n_configs + k], &rings[s * ring_off + params[k].ring_off]);
-    // split records into the planes the scan kernel reads
-    std::vector<float> minv(n_streams * n_records), ratio(n_streams * n_records), vad(n_streams * n_records);
-    bool any_vad = false;
-    for (size_t i = 0; i < n_streams * n_records; i++) {
-        minv[i] = records[i].min_volume; ratio[i] = records[i].vol_ratio; vad[i] = records[i].rnn_vad;
-        any_vad |= records[i].has_vad != 0.0f;
+    int max_long = 0, max_short = 0, max_ratio = 0;
+    vadm_sweep_rows(params.data(), n_configs, &max_long, &max_short, &max_ratio);
+    const size_t n_scans = n_streams * n_configs, total = n_streams * n_records;
+    memset(counts, 0, sizeof(uint32_t) * n_scans);
+    if (!n_records) return FVAD_OK;
+    // split the records into the planes the scans read
+    std::vector<float> minv(total), ratio(total), vad(total);
+    for (size_t s = 0; s < n_streams; s++) {
+        const fvad_stft_record *r = records + s * n_records;
+        if (r[0].index != records[0].index)
+            return set_error(FVAD_EINVALID_ARGUMENT, "fvad_vadm_sweep: stream %zu starts at index %llu, stream 0 at %llu", s,
+                             (unsigned long long)r[0].index, (unsigned long long)records[0].index);
+        for (size_t f = 0; f < n_records; f++) {
+            if (r[f].index != r[0].index + f * fft_size)
+                return set_error(FVAD_EINVALID_ARGUMENT, "fvad_vadm_sweep: record %zu of stream %zu has index %llu, expected %llu "
+                                 "(records must be consecutive STFT frames)", f, s, (unsigned long long)r[f].index,
+                                 (unsigned long long)(r[0].index + f * fft_size));
+            minv[s * n_records + f] = r[f].min_volume; ratio[s * n_records + f] = r[f].vol_ratio;
+            vad[s * n_records + f] = r[f].has_vad != 0.0f ? r[f].rnn_vad : 0.0f;
+        }
     }
-    int rc = FVAD_OK;
-    VadmParams *d_params = nullptr; VadmState *d_states = nullptr; double *d_rings = nullptr;
-    float *d_minv = nullptr, *d_ratio = nullptr, *d_vad = nullptr;
-    SegRecord *d_segs = nullptr; EventRecord *d_events = nullptr; unsigned *d_counts = nullptr;
-    const unsigned seg_cap = (unsigned)std::min<size_t>(n_streams * n_configs * max_segs + 16, (size_t)1 << 26);
-    auto cleanup = [&]() {
-        cudaFree(d_params); cudaFree(d_states); cudaFree(d_rings); cudaFree(d_minv); cudaFree(d_ratio); cudaFree(d_vad);
-        cudaFree(d_segs); cudaFree(d_events); cudaFree(d_counts);
-        cudaSetDevice(prev);
-    };
-#define SWEEP_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { rc = set_error(FVAD_ECUDA, "%s: %s", #x, cudaGetErrorString(e_)); cleanup(); return rc; } } while (0)
-    SWEEP_TRY(cudaMalloc(&d_params, sizeof(VadmParams) * n_configs));
-    SWEEP_TRY(cudaMalloc(&d_states, sizeof(VadmState) * states.size()));
-    SWEEP_TRY(cudaMalloc(&d_rings, sizeof(double) * rings.size()));
-    SWEEP_TRY(cudaMalloc(&d_minv, sizeof(float) * minv.size()));
-    SWEEP_TRY(cudaMalloc(&d_ratio, sizeof(float) * minv.size()));
-    SWEEP_TRY(cudaMalloc(&d_vad, sizeof(float) * minv.size()));
-    SWEEP_TRY(cudaMalloc(&d_segs, sizeof(SegRecord) * seg_cap));
-    SWEEP_TRY(cudaMalloc(&d_events, sizeof(EventRecord) * 16));
-    SWEEP_TRY(cudaMalloc(&d_counts, sizeof(unsigned) * 2));
-    SWEEP_TRY(cudaMemcpy(d_params, params.data(), sizeof(VadmParams) * n_configs, cudaMemcpyHostToDevice));
-    SWEEP_TRY(cudaMemcpy(d_states, states.data(), sizeof(VadmState) * states.size(), cudaMemcpyHostToDevice));
-    SWEEP_TRY(cudaMemcpy(d_rings, rings.data(), sizeof(double) * rings.size(), cudaMemcpyHostToDevice));
-    SWEEP_TRY(cudaMemcpy(d_minv, minv.data(), sizeof(float) * minv.size(), cudaMemcpyHostToDevice));
-    SWEEP_TRY(cudaMemcpy(d_ratio, ratio.data(), sizeof(float) * minv.size(), cudaMemcpyHostToDevice));
-    SWEEP_TRY(cudaMemcpy(d_vad, vad.data(), sizeof(float) * minv.size(), cudaMemcpyHostToDevice));
-    SWEEP_TRY(cudaMemset(d_counts, 0, sizeof(unsigned) * 2));
-    VadmIo io{};
-    io.band = d_minv; io.band_rows = n_streams; io.band_frame_stride = n_records;
-    io.vol_ratio = d_ratio; io.vad = any_vad ? d_vad : nullptr; io.ratio_stride = n_records;
-    io.n_channels = 1;
-    io.first_index = n_records ? records[0].index : 0;
-    io.index_step = fft_size; io.n_frames = n_records;
-    io.segs = d_segs; io.seg_count = d_counts; io.seg_cap = seg_cap;
-    io.events = d_events; io.event_count = d_counts + 1; io.event_cap = 0;
-    io.trace = nullptr;
-    rc = vadm_launch(d_params, d_states, d_rings, n_streams, (int)n_configs, io, 0);
-    if (rc != FVAD_OK) { cleanup(); return rc; }
-    SWEEP_TRY(cudaDeviceSynchronize());
-    unsigned ns = 0;
-    SWEEP_TRY(cudaMemcpy(&ns, d_counts, sizeof ns, cudaMemcpyDeviceToHost));
-    if (ns > seg_cap) { cleanup(); return set_error(FVAD_EOUT_OF_MEMORY, "sweep produced %u segments, buffer holds %u", ns, seg_cap); }
-    std::vector<SegRecord> tmp(ns);
-    if (ns) SWEEP_TRY(cudaMemcpy(tmp.data(), d_segs, sizeof(SegRecord) * ns, cudaMemcpyDeviceToHost));
-    std::stable_sort(tmp.begin(), tmp.end(), [](const SegRecord &a, const SegRecord &c) {
-        if (a.stream != c.stream) return a.stream < c.stream;
-        if (a.machine != c.machine) return a.machine < c.machine;
-        return a.seg.sample_to < c.seg.sample_to;
-    });
-    memset(counts, 0, sizeof(uint32_t) * n_streams * n_configs);
-    for (auto &r : tmp) {
-        const size_t id = (size_t)r.stream * n_configs + r.machine;
-        if (counts[id] < max_segs) segs[id * max_segs + counts[id]] = r.seg;
-        counts[id]++;
-    }
-    cleanup();
-#undef SWEEP_TRY
+    SweepBuffers buf;
+    VadmParams *d_params; double *d_rings; float *d_minv, *d_ratio, *d_vad; fvad_segment *d_segs; uint32_t *d_counts;
+    FVAD_TRY(buf.get(&d_params, n_configs));
+    FVAD_TRY(buf.get(&d_rings, (size_t)(max_long + max_short + max_ratio) * n_scans));
+    FVAD_TRY(buf.get(&d_minv, total)); FVAD_TRY(buf.get(&d_ratio, total)); FVAD_TRY(buf.get(&d_vad, total));
+    FVAD_TRY(buf.get(&d_segs, n_scans * max_segs)); FVAD_TRY(buf.get(&d_counts, n_scans));
+    FVAD_CUDA_TRY(cudaMemcpy(d_params, params.data(), sizeof(VadmParams) * n_configs, cudaMemcpyHostToDevice));
+    FVAD_CUDA_TRY(cudaMemcpy(d_minv, minv.data(), sizeof(float) * total, cudaMemcpyHostToDevice));
+    FVAD_CUDA_TRY(cudaMemcpy(d_ratio, ratio.data(), sizeof(float) * total, cudaMemcpyHostToDevice));
+    FVAD_CUDA_TRY(cudaMemcpy(d_vad, vad.data(), sizeof(float) * total, cudaMemcpyHostToDevice));
+    VadmSweepIo io{};
+    io.min_volume = d_minv; io.band_stride = 0; io.vol_ratio = d_ratio; io.vad = d_vad;
+    io.rec_stride = n_records; io.n_records = n_records;
+    io.first_index = records[0].index; io.index_step = fft_size;
+    io.segs = d_segs; io.max_segs = max_segs; io.counts = d_counts; io.fallbacks = nullptr;
+    FVAD_TRY(vadm_sweep_launch(d_params, d_rings, max_long, max_short, n_streams, (int)n_configs, io, 0));
+    FVAD_CUDA_TRY(cudaMemcpy(counts, d_counts, sizeof(uint32_t) * n_scans, cudaMemcpyDeviceToHost));
+    FVAD_CUDA_TRY(cudaMemcpy(segs, d_segs, sizeof(fvad_segment) * n_scans * max_segs, cudaMemcpyDeviceToHost));
     return FVAD_OK;
 }

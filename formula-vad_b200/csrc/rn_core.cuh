@@ -1188,9 +1188,9 @@ RN_HD void rnn_frame_cta(const unsigned *W2, const float *bias, const float *tan
 }
 
 // biquad (denoise.c:410-420) with the Denoiser's x32767 input scaling (Denoiser.zig:72-82)
-RN_HD float biquad_step(float in_norm, float &m0, float &m1) {
+// xi = the sample already scaled by 32767 (Denoiser.zig:45-66 normalizedPcmToRnnoise)
+RN_HD float biquad_step_x(float xi, float &m0, float &m1) {
     const float a0 = -1.99599f, a1 = 0.99600f, b0 = -2.f, b1 = 1.f;     // denoise.c:470-471
-    const float xi = in_norm * 32767.0f;
     const float yi = xi + m0;
     // a0*yi and a1*yi are products of two floats: exact in double, so DMUL+DADD == one DFMA bit for bit
     // (b0*xi = -2*xi and b1*xi = xi are exact as well).  Shortens the dependent chain by one DADD.
@@ -1200,6 +1200,7 @@ RN_HD float biquad_step(float in_norm, float &m0, float &m1) {
     m1 = (float)fma(-(double)a1, yd, xd);
     return yi;
 }
+RN_HD float biquad_step(float in_norm, float &m0, float &m1) { return biquad_step_x(in_norm * 32767.0f, m0, m1); }
 
 // ------------------------------------------------------------------------------------------
 // The same biquad step WITHOUT double precision: error-free transformations in f32 (TwoSum, FMA
@@ -1249,9 +1250,8 @@ RN_HD bool round_hazard(float r, float v, float big) {
     if ((ur & 0x7fffffu) == 0u) half *= 0.5f;                  // below a power of two the grid is twice as fine
     return (av >= half * 0.99993896484375f) || (big >= ar * 4096.0f);
 }
-RN_HD float biquad_step_eft(float in_norm, float &m0, float &m1, bool &hazard) {
+RN_HD float biquad_step_eft_x(float x, float &m0, float &m1, bool &hazard) {     // x already scaled by 32767
     const float A0 = 1.99599f, A1 = 0.99600f;
-    const float x = in_norm * 32767.0f;
     const float c = -2.0f * x;                                 // exact
     float dh, dl;
     two_sum(m1, c, dh, dl);                                    // m1 - 2x = dh + dl          (off the chain)
@@ -1283,6 +1283,30 @@ RN_HD float biquad_step_eft(float in_norm, float &m0, float &m1, bool &hazard) {
     m0 = r;
     m1 = n1;
     return y;
+}
+RN_HD float biquad_step_eft(float in_norm, float &m0, float &m1, bool &hazard) {
+    return biquad_step_eft_x(in_norm * 32767.0f, m0, m1, hazard);
+}
+
+// The chain lane's step, second form (k_rn_biquad_v2): the sample arrives scaled, nothing but the state is produced
+// (the verifying threads form y = x + m0 themselves, it is the reference's own float add), and -2x is never
+// materialised: RN(m1 - 2x) and RN(-2x - bb) are single fused operations on the exact product, bit-identical to the
+// add / subtract of the exact float -2x.  20 instructions per sample instead of 23, the same 7 on the dependent chain.
+RN_HD void biquad_chain_step(float x, float &m0, float &m1) {
+    const float A0 = 1.99599f, A1 = 0.99600f;
+    const float dh = fma_rn(-2.0f, x, m1);                     // TwoSum(m1, -2x): dh + dl = m1 - 2x
+    const float bb = dh - m1;
+    const float dl = (m1 - (dh - bb)) + fma_rn(-2.0f, x, -bb);
+    const float y = x + m0;
+    const float p = A0 * y, pl = fma_rn(A0, y, -p);
+    const float w = p + dh;
+    const bool pbig = fabsf(y) >= fabsf(dh) * (1.0f / 1.99599f);       // ordering decided beside p and w (see biquad_step_fast)
+    const float hi = pbig ? p : dh, lo = pbig ? dh : p;
+    const float f = (hi - w) + lo;
+    const float th = pl + dl;
+    const float uh = th + f;
+    m1 = fma_rn(-A1, y, x);
+    m0 = w + uh;
 }
 
 // The chain-only version of biquad_step_eft (same operations for y, m0', m1'; no hazard analysis): what the

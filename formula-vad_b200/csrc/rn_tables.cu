@@ -10,7 +10,7 @@ namespace fvad {
 namespace rn {
 
 std::string default_blob_path() {
-    const char *env = getenv("FVAD_MODEL_BLOB");
+    const char *env = debug_knob("model_blob");
     if (env && *env) return env;
     Dl_info info;
     if (dladdr((void *)&default_blob_path, &info) && info.dli_fname) {

@@ -115,7 +115,7 @@ static int rn_tables_get(int device, RnDevTables *out) {
 // L1.5 instruction cache a kernel with a small grid is throttled (B300_MICROARCH.md, I-cache), and the other stages'
 // kernels compete for the shared instruction cache levels.  Rolled form (16 samples per iteration, ~6 KB body, lives in
 // the lowest instruction cache levels): BQ = 48: 71.0, 96: 66.2, 120: 67.8, 160: 66.7 ms alone and 96 stays at 69 ms inside the
-// wavefront -- the default.  FVAD_BQ_BLOCK / FVAD_BQ_ROLL override.
+// wavefront -- the default.  knob bq_block / knob bq_roll override.
 __host__ __device__ constexpr int bq_threads(int BQ) { return 32 + ((BQ + 31) / 32) * 32; }
 #define FVAD_BQ_VARIANTS(X) X(32, false) X(48, false) X(60, false) X(48, true) X(96, true) X(160, true)
 #ifndef FVAD_BQ_SUB
@@ -278,6 +278,354 @@ __global__ void __launch_bounds__(bq_threads(BQ)) k_rn_biquad(const float *__res
         __syncthreads();                                           // replay results visible before anyone moves on
     }
     if (threadIdx.x == 0) { persist[n].biq[0] = m0; persist[n].biq[1] = m1; }
+}
+
+// Second form of the chain-per-CTA kernel (knob bq_form=2; an experiment of round 2 that did NOT pay: 250 ms per 240 s of 20
+// streams against 244 ms for the first form).  The premise was that the chain lane is issue-bound: 42 cycles per sample
+// against a 28-cycle dependent chain with ~25 instructions per sample on ONE warp.  tools/ubench/chain_mix.cu says otherwise:
+// one warp issues independent FADD / FFMA / FMUL at 1.09 cycles each, the 7-operation chain alone costs 28.4 cycles, the whole
+// step in registers 30.8 (the two FSELs that order the Fast2Sum operands sit on the ALU pipe: +1 cycle each way), with its
+// shared-memory traffic 33-39, inside the block structure with barriers and verifying warps 36.3 -- the kernel's 41.6 is
+// neither instruction count (21 vs 25 per sample changes nothing) nor barriers (0.5 cycles per sample) nor replays (2 %) nor
+// the frame I/O (1.4 cycles); a bare chain with everything else switched off (knob bq_dbg=23) still costs 40.3.  What this
+// form takes off the lane:
+//  * the scaling by 32767 (the staging warp stores x * 32767: every consumer wants the scaled sample) and the product -2x
+//    (folded into two FFMAs, rn_core.cuh biquad_chain_step);
+//  * every y store and the m1 half of the state record: the lane publishes m0 before each sample (one STS.128 per four
+//    samples instead of three) plus m1 at the block's ends.  A verifying thread rebuilds its sample's m1 the way the lane
+//    formed it, fma(-A1, x' + m0', x') of the PREVIOUS sample, re-evaluates the step with the full hazard analysis, compares
+//    the m0 the lane carried on and its own fused m1 against the analysed results, and stores y = x + m0 itself.
+// Protocol, replay and the denormal-tail path are those of k_rn_biquad.
+template <int BQ>
+__global__ void __launch_bounds__(bq_threads(BQ)) k_rn_biquad_v2(const float *__restrict__ in, size_t in_stride, int C, int Q,
+                                                                 RnPersist *persist, float *__restrict__ hp, size_t hp_stride, size_t N,
+                                                                 int dbg) {
+    // dbg (knob bq_dbg, measurement only, results then unverified): 1 = no hazard analysis, 2 = verdicts ignored
+    constexpr int kBPF = kFrame / BQ, kThreads = bq_threads(BQ);
+    constexpr int kSub = BQ % FVAD_BQ_SUB == 0 ? FVAD_BQ_SUB : 8;   // samples per iteration of the chain loop
+    static_assert(kFrame % BQ == 0 && BQ % 8 == 0, "blocks tile the frame");
+    const size_t n = blockIdx.x;
+    if (n >= N) return;
+    __shared__ __align__(16) float sx[2][kFrame];          // input scaled by 32767
+    __shared__ __align__(16) float sy[2][kFrame];
+    __shared__ __align__(16) float PM[2][BQ + 4];          // m0 before every sample of the block; [BQ] = after the block
+    __shared__ float M1[2][2];                             // m1 before / after the block
+    __shared__ int FINAL[2];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float m0 = persist[n].biq[0], m1 = persist[n].biq[1];         // meaningful on thread 0
+    float *dst = hp + n * hp_stride + kPHist;
+    auto src = [&](int q) { return in + (n * C + (q % C)) * in_stride + (size_t)(q / C) * kFrame; };
+    if (threadIdx.x < 2) FINAL[threadIdx.x] = 0;
+    if (Q > 0) for (int i = threadIdx.x; i < kFrame; i += kThreads) sx[0][i] = src(0)[i] * 32767.0f;
+    __syncthreads();
+    const int G = Q * kBPF;
+    float pf[kFrame / 32]; int pf_buf = -1;                        // warp 1: a frame in flight from global memory
+    for (int g = 0; g <= G + 1; g++) {
+        bool hz = false;
+        if (warp == 0) {
+            if (lane == 0 && g < G) {                              // ---- the chain: block g
+                const int q = g / kBPF, b0 = (g - q * kBPF) * BQ, par = g & 1;
+                const float *xin = &sx[q & 1][b0];
+                const float a0 = fabsf(m0), a1 = fabsf(m1);
+                if ((a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f)) {
+                    float *yout = &sy[q & 1][b0];
+                    for (int i = 0; i < BQ; i++) yout[i] = biquad_step_x(xin[i], m0, m1);     // denormal tail of a silence
+                    FINAL[par] = 1;
+                } else {
+                    M1[par][0] = m1;
+                    float4 xc[kSub / 4], xn[kSub / 4];
+#pragma unroll
+                    for (int k = 0; k < kSub / 4; k++) xc[k] = *reinterpret_cast<const float4 *>(xin + 4 * k);
+#pragma unroll 1
+                    for (int i = 0; i < BQ; i += kSub) {
+                        const int inx = i + kSub < BQ ? i + kSub : i;     // last iteration: a harmless re-fetch instead of a branch
+#pragma unroll
+                        for (int k = 0; k < kSub / 4; k++) xn[k] = *reinterpret_cast<const float4 *>(xin + inx + 4 * k);
+#pragma unroll
+                        for (int k = 0; k < kSub / 4; k++) {
+                            float4 pm;
+                            pm.x = m0; biquad_chain_step(xc[k].x, m0, m1);
+                            pm.y = m0; biquad_chain_step(xc[k].y, m0, m1);
+                            pm.z = m0; biquad_chain_step(xc[k].z, m0, m1);
+                            pm.w = m0; biquad_chain_step(xc[k].w, m0, m1);
+                            *reinterpret_cast<float4 *>(&PM[par][i + 4 * k]) = pm;
+                        }
+#pragma unroll
+                        for (int k = 0; k < kSub / 4; k++) xc[k] = xn[k];
+                    }
+                    PM[par][BQ] = m0;
+                    M1[par][1] = m1;
+                    FINAL[par] = 0;
+                }
+            }
+        } else {
+            const int v = (int)threadIdx.x - 32;                   // verification: one sample of the block per thread of warps >= 1
+            if (warp == 1 && pf_buf >= 0) {                        // ---- the frame fetched one iteration ago lands in shared memory
+#pragma unroll
+                for (int k = 0; k < kFrame / 32; k++) sx[pf_buf][lane + 32 * k] = pf[k] * 32767.0f;
+                pf_buf = -1;
+            }
+            if (g >= 1 && g - 1 < G && v < BQ && !(dbg & 16)) {    // ---- verification of block g-1
+                const int gv = g - 1, q = gv / kBPF, b0 = (gv - q * kBPF) * BQ, par = gv & 1;
+                if (!FINAL[par]) {
+                    const float *xb = &sx[q & 1][b0];
+                    float a = PM[par][v], b;
+                    if (v == 0) b = M1[par][0];
+                    else { const float xp = xb[v - 1]; b = __fmaf_rn(-0.99600f, xp + PM[par][v - 1], xp); }
+                    const float xv = xb[v];
+                    float yv;
+                    if (dbg & 1) yv = xv + a;
+                    else {
+                        yv = biquad_step_eft_x(xv, a, b, hz);
+                        hz |= (__float_as_uint(a) != __float_as_uint(PM[par][v + 1])) |
+                              (__float_as_uint(b) != __float_as_uint(__fmaf_rn(-0.99600f, yv, xv)));
+                    }
+                    if (!(dbg & 8)) sy[q & 1][b0 + v] = yv;        // the reference's own float add: nothing to verify
+                }
+            }
+            if (warp == 1 && g >= 2) {                             // ---- block g-2 is final: frame I/O at frame edges
+                const int gf = g - 2, q = gf / kBPF;
+                if (gf - q * kBPF == kBPF - 1 && !(dbg & 4)) {
+                    for (int i = lane; i < kFrame; i += 32) dst[(size_t)q * kFrame + i] = sy[q & 1][i];
+                    if (q + 2 < Q) {
+                        const float *s2 = src(q + 2);
+#pragma unroll
+                        for (int k = 0; k < kFrame / 32; k++) pf[k] = s2[lane + 32 * k];
+                        pf_buf = q & 1;
+                    }
+                }
+            }
+            if (warp == 1 && g == 0 && Q > 1) {
+                const float *s1 = src(1);
+#pragma unroll
+                for (int k = 0; k < kFrame / 32; k++) pf[k] = s1[lane + 32 * k];
+                pf_buf = 1;
+            }
+        }
+        const int verdict = __syncthreads_or(hz ? 1 : 0);          // the verdict on block g-1 travels with the barrier
+        if (threadIdx.x == 0 && verdict && !(dbg & 2)) {           // ---- replay of a hazardous block g-1
+            const int gv = g - 1, q = gv / kBPF, b0 = (gv - q * kBPF) * BQ, par = gv & 1;
+            float r0 = PM[par][0], r1 = M1[par][0];
+            for (int i = 0; i < BQ; i++) sy[q & 1][b0 + i] = biquad_step_x(sx[q & 1][b0 + i], r0, r1);
+            if (__float_as_uint(r0) != __float_as_uint(PM[par][BQ]) || __float_as_uint(r1) != __float_as_uint(M1[par][1])) {
+                // the fast step was wrong: block g (computed from its end state) is void, redo it from the true state
+                m0 = r0; m1 = r1;
+                if (g < G) {
+                    const int q2 = g / kBPF, c0 = (g - q2 * kBPF) * BQ;
+                    for (int i = 0; i < BQ; i++) sy[q2 & 1][c0 + i] = biquad_step_x(sx[q2 & 1][c0 + i], m0, m1);
+                    FINAL[g & 1] = 1;
+                }
+            }
+        }
+        __syncthreads();                                           // replay results visible before anyone moves on
+    }
+    if (threadIdx.x == 0) { persist[n].biq[0] = m0; persist[n].biq[1] = m1; }
+}
+
+// Third form (knob bq_form=3; also an experiment that did not pay: 270 ms against 244 ms): the chain warp and the verifying
+// warps no longer meet at two CTA-wide barriers per block.
+// ncu on the second form (profiles/r02a: source page, per-instruction samples of the chain warp) put the chain loop at
+// 35.4 cycles per sample and the per-block hand-over at ~640 cycles -- 6.7 cycles per sample at 96 samples per block: two
+// __syncthreads round trips, the reconvergence of the divergent warp, instruction-cache misses on the jumps between the
+// warps' code regions, the division of the block index, the exposed LDS latency of the block's first inputs.  Here
+//  * warp 0 runs its own loop: block g, then a NON-blocking bar.arrive on FULL[g & 1]; the verifying warps run theirs:
+//    bar.sync on FULL[g & 1], verify block g (hazard analysis, y stores, verdict flag), bar.arrive on DONE[g & 1].  The chain
+//    warp reads the verdict on block g-1 after block g -- bar.sync on DONE[(g-1) & 1], which the verifiers reached one block
+//    ago, so it never waits for them;
+//  * the chain lane's inputs travel in three register stages (current iteration, next, next-but-one: 16 samples each),
+//    fetched straight across block boundaries, so no LDS latency meets the chain whichever way ptxas orders the loads.
+// A bad verdict on block g-1 (hazard, or a difference from the fast step): the chain warp first takes DONE[g & 1] as well
+// (the verifiers may be busy with block g, which it has just computed from a state that may be wrong), replays block g-1 with
+// the reference's double arithmetic from the recorded state and, only if the end state differs from what it carried on,
+// recomputes block g the same way and voids the verifiers' verdict on it.  Frames leave for global memory two blocks behind
+// the verifiers, when every block of the frame is final.  Blocks per frame >= 3 (BQ <= 160) keeps the frame buffers apart.
+__device__ __forceinline__ void nb_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void nb_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+template <int BQ>
+__global__ void __launch_bounds__(bq_threads(BQ)) k_rn_biquad_v3(const float *__restrict__ in, size_t in_stride, int C, int Q,
+                                                                 RnPersist *persist, float *__restrict__ hp, size_t hp_stride, size_t N,
+                                                                 int dbg) {
+    // dbg (knob bq_dbg, measurement only, results then unverified): 1 = no hazard analysis, 2 = verdicts ignored
+    constexpr int kBPF = kFrame / BQ, kThreads = bq_threads(BQ), kSub = 16, kIPB = BQ / kSub;
+    static_assert(kFrame % BQ == 0 && BQ % kSub == 0 && kBPF >= 3, "blocks tile the frame, at least three per frame");
+    constexpr int kFull = 1, kDone = 3;                    // named barriers: FULL[par] = 1 + par, DONE[par] = 3 + par
+    const size_t n = blockIdx.x;
+    if (n >= N) return;
+    __shared__ __align__(16) float sx[3][kFrame];          // input scaled by 32767: frame q in sx[q % 3]
+    __shared__ __align__(16) float sy[2][kFrame];
+    __shared__ __align__(16) float PM[2][BQ + 4];          // m0 before every sample of the block; [BQ] = after the block
+    __shared__ float M1[2][2];                             // m1 before / after the block
+    __shared__ int FINAL[2], VERDICT[2];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float *dst = hp + n * hp_stride + kPHist;
+    auto src = [&](int q) { return in + (n * C + (q % C)) * in_stride + (size_t)(q / C) * kFrame; };
+    if (threadIdx.x < 2) { FINAL[threadIdx.x] = 0; VERDICT[threadIdx.x] = 0; }
+    if (Q > 0) for (int i = threadIdx.x; i < kFrame; i += kThreads) sx[0][i] = src(0)[i] * 32767.0f;
+    if (Q > 1) for (int i = threadIdx.x; i < kFrame; i += kThreads) sx[1][i] = src(1)[i] * 32767.0f;
+    if (Q > 2) for (int i = threadIdx.x; i < kFrame; i += kThreads) sx[2][i] = src(2)[i] * 32767.0f;
+    __syncthreads();
+    const int G = Q * kBPF;
+
+    if (warp == 0) {
+        // ================================ the chain warp ================================
+        float m0 = persist[n].biq[0], m1 = persist[n].biq[1];     // meaningful on lane 0
+        float4 xa[kSub / 4], xb[kSub / 4], xc[kSub / 4];          // inputs of this iteration, the next, the one after
+        bool primed = false;
+        bool done_taken = false;                                  // DONE of the block about to be judged was taken early
+        int q = 0, qb = 0, b0 = 0;                                // block g = frame q (buffer qb = q % 3), samples b0 .. b0 + BQ
+        // Whole warp: the verdict on block gv (its verifiers have arrived on DONE[gv & 1], or are about to).
+        auto judge = [&](int gv, int qv, int bv) {
+            const int pv = gv & 1;
+            if (!done_taken) nb_sync(kDone + pv, kThreads);
+            done_taken = false;
+            int bad = 0;
+            if (lane == 0) bad = VERDICT[pv] && !(dbg & 2);
+            bad = __shfl_sync(0xffffffffu, bad, 0);
+            if (!bad) return;
+            const bool has_next = gv + 1 < G;
+            if (has_next) { nb_sync(kDone + (pv ^ 1), kThreads); done_taken = true; }   // nobody touches block gv+1 any more
+            if (lane == 0) {
+                VERDICT[pv] = 0;
+                float r0 = PM[pv][0], r1 = M1[pv][0];
+                for (int i = 0; i < BQ; i++) sy[qv & 1][bv + i] = biquad_step_x(sx[qv % 3][bv + i], r0, r1);
+                if (__float_as_uint(r0) != __float_as_uint(PM[pv][BQ]) || __float_as_uint(r1) != __float_as_uint(M1[pv][1])) {
+                    // the fast step was wrong: block gv+1 (computed from its end state) is void, redo it from the true state
+                    m0 = r0; m1 = r1;
+                    if (has_next) {
+                        int q2 = qv, c0 = bv + BQ;
+                        if (c0 == kFrame) { c0 = 0; q2++; }
+                        for (int i = 0; i < BQ; i++) sy[q2 & 1][c0 + i] = biquad_step_x(sx[q2 % 3][c0 + i], m0, m1);
+                        VERDICT[pv ^ 1] = 0;                      // whatever the verifiers found on the void data
+                    }
+                }
+            }
+            __syncwarp();
+        };
+        for (int g = 0; g < G; g++) {
+            const int par = g & 1;
+            if (lane == 0) {
+                const float *xin = &sx[qb][b0];
+                const float a0 = fabsf(m0), a1 = fabsf(m1);
+                if ((a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f)) {
+                    float *yout = &sy[q & 1][b0];
+                    for (int i = 0; i < BQ; i++) yout[i] = biquad_step_x(xin[i], m0, m1);     // denormal tail of a silence
+                    FINAL[par] = 1;
+                    primed = false;
+                } else {
+                    M1[par][0] = m1;
+                    // position of the iteration after next, for the prefetch (runs on across block and frame boundaries)
+                    int fq = q, fb = qb, fo = b0 + 2 * kSub;
+                    if (fo >= kFrame) { fo -= kFrame; fq++; fb = fb == 2 ? 0 : fb + 1; }
+                    if (!primed) {
+#pragma unroll
+                        for (int k = 0; k < kSub / 4; k++) xa[k] = *reinterpret_cast<const float4 *>(xin + 4 * k);
+                        int nq = q, nb = qb, no = b0 + kSub;
+                        if (no >= kFrame) { no -= kFrame; nq++; nb = nb == 2 ? 0 : nb + 1; }
+                        if (nq >= Q) { nb = qb; no = b0; }
+#pragma unroll
+                        for (int k = 0; k < kSub / 4; k++) xb[k] = *reinterpret_cast<const float4 *>(&sx[nb][no + 4 * k]);
+                        primed = true;
+                    }
+#pragma unroll 1
+                    for (int it = 0; it < kIPB; it++) {
+                        const float *xf = (fq < Q) ? &sx[fb][fo] : xin;         // past the end: a harmless re-fetch
+#pragma unroll
+                        for (int k = 0; k < kSub / 4; k++) xc[k] = *reinterpret_cast<const float4 *>(xf + 4 * k);
+                        fo += kSub;
+                        if (fo >= kFrame) { fo -= kFrame; fq++; fb = fb == 2 ? 0 : fb + 1; }
+#pragma unroll
+                        for (int k = 0; k < kSub / 4; k++) {
+                            float4 pm;
+                            pm.x = m0; biquad_chain_step(xa[k].x, m0, m1);
+                            pm.y = m0; biquad_chain_step(xa[k].y, m0, m1);
+                            pm.z = m0; biquad_chain_step(xa[k].z, m0, m1);
+                            pm.w = m0; biquad_chain_step(xa[k].w, m0, m1);
+                            *reinterpret_cast<float4 *>(&PM[par][it * kSub + 4 * k]) = pm;
+                        }
+#pragma unroll
+                        for (int k = 0; k < kSub / 4; k++) { xa[k] = xb[k]; xb[k] = xc[k]; }
+                    }
+                    PM[par][BQ] = m0;
+                    M1[par][1] = m1;
+                    FINAL[par] = 0;
+                }
+            }
+            __syncwarp();
+            __threadfence_block();
+            nb_arrive(kFull + par, kThreads);                      // block g is published; nobody is waited for
+            if (g >= 1) {
+                int qv = q, bv = b0 - BQ;
+                if (bv < 0) { bv += kFrame; qv--; }
+                judge(g - 1, qv, bv);      // (a replay leaves the register stages valid: they hold INPUTS of block g+1 onwards)
+            }
+            b0 += BQ;
+            if (b0 == kFrame) { b0 = 0; q++; qb = qb == 2 ? 0 : qb + 1; }
+        }
+        if (G >= 1) {
+            int qv = q, bv = b0 - BQ;
+            if (bv < 0) { bv += kFrame; qv--; }
+            judge(G - 1, qv, bv);
+        }
+        if (lane == 0) { persist[n].biq[0] = m0; persist[n].biq[1] = m1; }
+    } else {
+        // ================================ verifying warps (warp 1 also moves the frames) ================================
+        const int v = (int)threadIdx.x - 32;                       // one sample of the block per thread
+        float pf[kFrame / 32]; int pf_buf = -1;                    // warp 1: a frame in flight from global memory
+        int q = 0, qb = 0, b0 = 0;
+        for (int g = 0; g < G; g++) {
+            const int par = g & 1;
+            if (warp == 1 && pf_buf >= 0) {                        // the frame fetched one block ago lands in shared memory
+#pragma unroll
+                for (int k = 0; k < kFrame / 32; k++) sx[pf_buf][lane + 32 * k] = pf[k] * 32767.0f;
+                pf_buf = -1;
+            }
+            nb_sync(kFull + par, kThreads);                        // block g is there
+            bool hz = false;
+            if (v < BQ && !FINAL[par]) {
+                const float *xb = &sx[qb][b0];
+                float a = PM[par][v], b;
+                if (v == 0) b = M1[par][0];
+                else { const float xp = xb[v - 1]; b = __fmaf_rn(-0.99600f, xp + PM[par][v - 1], xp); }
+                const float xv = xb[v];
+                float yv;
+                if (dbg & 1) yv = xv + a;
+                else {
+                    yv = biquad_step_eft_x(xv, a, b, hz);
+                    hz |= (__float_as_uint(a) != __float_as_uint(PM[par][v + 1])) |
+                          (__float_as_uint(b) != __float_as_uint(__fmaf_rn(-0.99600f, yv, xv)));
+                }
+                sy[q & 1][b0 + v] = yv;                            // the reference's own float add: nothing to verify
+            }
+            if (__any_sync(0xffffffffu, hz) && lane == 0) VERDICT[par] = 1;
+            if (warp == 1 && g >= 2) {                             // block g-2 is final: frame I/O at frame edges
+                int bf = b0 - 2 * BQ, qf = q;
+                if (bf < 0) { bf += kFrame; qf--; }
+                if (bf == kFrame - BQ) {                           // it was the last block of frame qf
+                    for (int i = lane; i < kFrame; i += 32) dst[(size_t)qf * kFrame + i] = sy[qf & 1][i];
+                    // sx[qf % 3] is free: fetch frame qf + 3 (into registers now, into shared memory next block: the load
+                    // latency never meets a barrier).  The chain reaches that frame more than a frame later, behind several
+                    // DONE barriers that follow the write.
+                    if (qf + 3 < Q) {
+                        const float *s2 = src(qf + 3);
+#pragma unroll
+                        for (int k = 0; k < kFrame / 32; k++) pf[k] = s2[lane + 32 * k];
+                        pf_buf = qf % 3;
+                    }
+                }
+            }
+            __threadfence_block();
+            nb_arrive(kDone + par, kThreads);                      // done with block g (verdict, y, frame I/O)
+            b0 += BQ;
+            if (b0 == kFrame) { b0 = 0; q++; qb = qb == 2 ? 0 : qb + 1; }
+        }
+    }
+    __syncthreads();                                               // every verdict is in, every replay written
+    if (warp == 1) {                                               // the frames whose last block became final after the loops
+        for (int qf = 0; qf < Q; qf++)
+            if (qf * kBPF + kBPF - 1 + 2 >= G)
+                for (int i = lane; i < kFrame; i += 32) dst[(size_t)qf * kFrame + i] = sy[qf & 1][i];
+    }
 }
 
 // Throughput regime (many states): the same protocol with a state per LANE.  Warp 0 walks the chains of 32 states in
@@ -706,6 +1054,9 @@ static size_t biquad_smem_hog(size_t static_bytes) {
     return per_block_max > static_bytes ? per_block_max - static_bytes : 0;
 }
 static size_t g_bq_static[512];                              // static shared memory per BQ variant (cudaFuncGetAttributes)
+static size_t g_bq2_static[512], g_bq3_static[512];
+#define FVAD_BQ2_VARIANTS(X) X(48) X(96) X(160) X(240)
+#define FVAD_BQ3_VARIANTS(X) X(48) X(96) X(160)
 constexpr size_t kSmemAna = (size_t)kWarpsPerCta * kScrAna * sizeof(float);
 constexpr size_t smem_pitch(int F) { return (size_t)F * kScrPitch * sizeof(float); }
 #define FVAD_PITCH_VARIANTS(X) X(4) X(6) X(8)
@@ -788,6 +1139,26 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
         }
         FVAD_BQ_VARIANTS(FVAD_BQ_ATTR)
 #undef FVAD_BQ_ATTR
+#define FVAD_BQ2_ATTR(BB)                                                                                                \
+        if (e == cudaSuccess) {                                                                                          \
+            cudaFuncAttributes fa{};                                                                                     \
+            e = cudaFuncGetAttributes(&fa, k_rn_biquad_v2<BB>);                                                          \
+            g_bq2_static[BB] = fa.sharedSizeBytes;                                                                       \
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_v2<BB>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                                           (int)biquad_smem_hog(fa.sharedSizeBytes));                  \
+        }
+        FVAD_BQ2_VARIANTS(FVAD_BQ2_ATTR)
+#undef FVAD_BQ2_ATTR
+#define FVAD_BQ3_ATTR(BB)                                                                                                \
+        if (e == cudaSuccess) {                                                                                          \
+            cudaFuncAttributes fa{};                                                                                     \
+            e = cudaFuncGetAttributes(&fa, k_rn_biquad_v3<BB>);                                                          \
+            g_bq3_static[BB] = fa.sharedSizeBytes;                                                                       \
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_v3<BB>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                                           (int)biquad_smem_hog(fa.sharedSizeBytes));                  \
+        }
+        FVAD_BQ3_VARIANTS(FVAD_BQ3_ATTR)
+#undef FVAD_BQ3_ATTR
         if (e != cudaSuccess) rc = set_error(FVAD_ECUDA, "cudaFuncSetAttribute: %s (is this an sm_100 device?)", cudaGetErrorString(e));
     }
     if (rc == FVAD_OK) rc = rnnoise_batch_reset(r, 0);
@@ -827,17 +1198,39 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
     // x real time, lanes / chain-per-CTA: 296 streams 70.1k / 103.2k, 592: 104.4k / 116.5k, 1184: 130.4k / 113.0k,
     // 2368: 134.2k / 113.8k.
     bool lanes = !lat && N >= 1000;
-    if (const char *e = getenv("FVAD_BIQUAD_LANES")) lanes = atoi(e) != 0;
+    if (const char *e = debug_knob("biquad_lanes")) lanes = atoi(e) != 0;
     if (lanes) {
         FVAD_LAUNCH_NAMED("k_rn_biquad", k_rn_biquad_lanes, (unsigned)ceil_div(N, (size_t)kBqlStates), 32 * kBqlWarps, 0, st, d_in,
                           in_stride, C, (int)Qs, r->persist, s.hp, r->hp_stride(), N);
     } else {
         const size_t hog_on = lat ? 1 : 0;
         int BQ = 96;
-        if (const char *e = getenv("FVAD_BQ_BLOCK")) BQ = atoi(e);
+        if (const char *e = debug_knob("bq_block")) BQ = atoi(e);
         bool roll = BQ > 60;
-        if (const char *e = getenv("FVAD_BQ_ROLL")) roll = atoi(e) != 0;
+        if (const char *e = debug_knob("bq_roll")) roll = atoi(e) != 0;
         bool launched = false;
+        int dbg = 0;
+        if (const char *e = debug_knob("bq_dbg")) dbg = atoi(e);
+        int form = 1;                                         // knob bq_form: 1 = first form (default: still the fastest, see below), 2 = light chain lane, 3 = named-barrier hand-over
+        if (const char *e = debug_knob("bq_form")) form = atoi(e);
+        const bool v2 = form == 2;
+#define FVAD_BQ3_GO(BB)                                                                                                  \
+        if (form == 3 && !launched && BQ == BB) {                                                                        \
+            launched = true;                                                                                             \
+            FVAD_LAUNCH_NAMED("k_rn_biquad", (k_rn_biquad_v3<BB>), (unsigned)N, bq_threads(BB), hog_on * biquad_smem_hog(g_bq3_static[BB]), st, d_in, in_stride, C, (int)Qs,   \
+                              r->persist, s.hp, r->hp_stride(), N, dbg);                                                 \
+        }
+        FVAD_BQ3_VARIANTS(FVAD_BQ3_GO)
+#undef FVAD_BQ3_GO
+        if (form == 3 && !launched) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_block=%d: no such variant of the third form", BQ);
+#define FVAD_BQ2_GO(BB)                                                                                                  \
+        if (v2 && !launched && BQ == BB) {                                                                               \
+            launched = true;                                                                                             \
+            FVAD_LAUNCH_NAMED("k_rn_biquad", (k_rn_biquad_v2<BB>), (unsigned)N, bq_threads(BB), hog_on * biquad_smem_hog(g_bq2_static[BB]), st, d_in, in_stride, C, (int)Qs,   \
+                              r->persist, s.hp, r->hp_stride(), N, dbg);                                                    \
+        }
+        FVAD_BQ2_VARIANTS(FVAD_BQ2_GO)
+#undef FVAD_BQ2_GO
 #define FVAD_BQ_GO(BB, RL)                                                                                               \
         if (!launched && BQ == BB && roll == RL) {                                                                       \
             launched = true;                                                                                             \
@@ -846,7 +1239,7 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
         }
         FVAD_BQ_VARIANTS(FVAD_BQ_GO)
 #undef FVAD_BQ_GO
-        if (!launched) return set_error(FVAD_EINVALID_ARGUMENT, "FVAD_BQ_BLOCK=%d: no such biquad variant", BQ);
+        if (!launched) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_block=%d: no such biquad variant", BQ);
     }
     FVAD_LAUNCH(k_rn_hp_save, (unsigned)N, 256, 0, st, s.hp, r->hp_stride(), r->hp_hist, (int)Qs);
     FVAD_CUDA_TRY(cudaGetLastError());
@@ -854,7 +1247,7 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
 }
 
 // Frames per pitch CTA.  Measured at 592 streams: F = 4 95.2k, 6 93.9k, 8 92.4k x real time -- the fuller pooled warps of
-// a larger F do not pay for the longer barrier waits and the coarser shared-memory granularity (FVAD_PITCH_F overrides).
+// a larger F do not pay for the longer barrier waits and the coarser shared-memory granularity (knob pitch_f overrides).
 static int pitch_frames_per_cta(size_t, int) { return 4; }
 
 // Stage B1: frame-parallel analysis and pitch correlations (no carry between tiles).
@@ -869,7 +1262,7 @@ int rnnoise_stage_b1(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     FVAD_LAUNCH(k_rn_analysis, warp_grid, 32 * kWarpsPerCta, kSmemAna, st, t, s.hp, r->hp_stride(), N, Q, Qcap, s.X, s.Ex, s.ceps, s.sil);
     {
         int F = pitch_frames_per_cta(NQ, r->device);
-        if (const char *e = getenv("FVAD_PITCH_F")) { const int v = atoi(e); if (v == 4 || v == 6 || v == 8) F = v; }
+        if (const char *e = debug_knob("pitch_f")) { const int v = atoi(e); if (v == 4 || v == 6 || v == 8) F = v; }
         bool launched = false;
 #define FVAD_PITCH_GO(FF)                                                                                                \
         if (!launched && F == FF) {                                                                                      \
@@ -919,7 +1312,7 @@ int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     // group's weight fetches, G groups fill each other's narrow layers, and packing six states into a CTA (R, G = 2, 3)
     // leaves the other SMs wholly to the frame-parallel kernels (an RNN CTA's 174 KB of weights keep almost everything
     // else off its SM) -- measured, x real time: 148 streams (1,1) 81.3k, (1,3) 82.7k, (2,3) 87.8k; 296 streams (1,2)
-    // 102.2k, (2,1) 100.2k, (2,3) 103.9k.  FVAD_RNN_R / FVAD_RNN_G override (tests exercise every variant).
+    // 102.2k, (2,1) 100.2k, (2,3) 103.9k.  knob rnn_r / knob rnn_g override (tests exercise every variant).
     const size_t sms = (size_t)device_sm_count(r->device);
     const size_t per_sm = ceil_div(r->N, sms);
     int R = 1, G = 1;
@@ -928,8 +1321,8 @@ int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
         else if (per_sm <= 8) { R = 4; G = 2; }
         else { R = 4; G = 3; }
     }
-    if (const char *e = getenv("FVAD_RNN_R")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) R = v; }
-    if (const char *e = getenv("FVAD_RNN_G")) { const int v = atoi(e); if (v >= 1 && v <= 3) G = v; }
+    if (const char *e = debug_knob("rnn_r")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) R = v; }
+    if (const char *e = debug_knob("rnn_g")) { const int v = atoi(e); if (v >= 1 && v <= 3) G = v; }
     const unsigned grid = (unsigned)ceil_div(r->N, (size_t)R * G);
     bool launched = false;
 #define FVAD_RNN_GO(RR, GG)                                                                                              \

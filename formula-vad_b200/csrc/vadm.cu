@@ -3,12 +3,12 @@
 // The reference recomputes every rolling mean by re-summing its whole ring in index
 // order in f64 on every push (RollingAverage.zig:45-56): 4218 dependent adds per STFT
 // frame for the long-term ring.  Its value feeds exactly one thing, the comparison
-// `short_term > last_avg * factor` (VADMachine.zig:158-160).  We keep a running value of
-// the same sum whose error is bounded far below 1e-9 relative, decide with it when the
-// comparison is not within 1e-9 of a tie, and otherwise redo the reference's exact
-// in-order sum.  The decision -- hence the segment list -- is therefore always the
-// reference's.  The two short rings (4 and 11 entries by default) are summed exactly.
-#include "vadm.cuh"
+// `short_term > last_avg * factor` (VADMachine.zig:158-160).  We keep a running sum with a
+// running ABSOLUTE error bound, decide with it when the comparison is further from a tie than
+// that bound allows, and otherwise redo the reference's exact in-order sum (vadm_step.cuh).
+// The decision -- hence the segment list -- is therefore always the reference's.  The two
+// short rings (4 and 11 entries by default) are summed exactly.
+#include "vadm_step.cuh"
 #include <cmath>
 #include <cstring>
 
@@ -43,42 +43,29 @@ int vadm_params_from_config(const fvad_vad_machine_config &c, size_t sample_rate
     return FVAD_OK;
 }
 
-void vadm_init_host(const VadmParams &p, VadmState *st, double *rings) {
-    memset(st, 0, sizeof *st);
-    const size_t n = (size_t)p.long_len + p.short_len + p.ratio_len;
-    for (size_t i = 0; i < n; i++) rings[i] = 0.0;
-    if (p.has_initial) {                                                              // RollingAverage.zig:19-25
-        for (int i = 0; i < p.long_len; i++) rings[i] = p.initial;
-        st->long_cnt = p.long_len;
-        double a = 0.0, scalar = 1.0 / (double)p.long_len;
-        for (int i = 0; i < p.long_len; i++) a += rings[i] * scalar;
-        st->long_last = a; st->approx = a; st->long_has_last = 1; st->long_exact = 1;
-    }
+// One thread per (stream, machine): the state VADMachine.init leaves behind.
+__global__ void k_vadm_init(const VadmParams *__restrict__ params, VadmState *__restrict__ states, double *__restrict__ rings,
+                            size_t n_streams, int n_machines) {
+    const size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= n_streams * (size_t)n_machines) return;
+    const size_t s = id / n_machines;
+    const VadmParams P = params[id - s * n_machines];
+    const VadmParams last = params[n_machines - 1];
+    const size_t per_stream = last.ring_off + (size_t)last.long_len + last.short_len + last.ratio_len;
+    double *base = rings + s * per_stream + P.ring_off;
+    const RingFlat rl{base}, rs{base + P.long_len}, rr{base + P.long_len + P.short_len};
+    VadmState S;
+    vadm_regs_init(P, rl, rs, rr, S);
+    states[id] = S;
 }
 
-__device__ __forceinline__ double ring_avg_exact(const double *ring, int cnt) {      // RollingAverage.zig:45-56
-    double a = 0.0;
-    const double scalar = 1.0 / (double)cnt;
-    for (int i = 0; i < cnt; i++) a += ring[i] * scalar;
-    return a;
-}
-
-__device__ __forceinline__ double ring_sum_blocked(const double *ring, int cnt) {    // refresh of the running value
-    const double scalar = 1.0 / (double)cnt;
-    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-    int i = 0;
-    for (; i + 3 < cnt; i += 4) {
-        a0 += ring[i] * scalar; a1 += ring[i + 1] * scalar; a2 += ring[i + 2] * scalar; a3 += ring[i + 3] * scalar;
-    }
-    for (; i < cnt; i++) a0 += ring[i] * scalar;
-    return (a0 + a1) + (a2 + a3);
-}
-
-__device__ __forceinline__ double ring_push_exact(double *ring, int len, int &w, int &cnt, float sample) {
-    ring[w] = (double)sample;                                                         // RollingAverage.zig:34-43
-    w = (w + 1) % len;
-    if (cnt < len) cnt++;
-    return ring_avg_exact(ring, cnt);
+int vadm_init_launch(const VadmParams *d_params, VadmState *d_states, double *d_rings, size_t n_streams, int n_machines,
+                     cudaStream_t stream) {
+    const size_t n = n_streams * (size_t)n_machines;
+    if (!n) return FVAD_OK;
+    FVAD_LAUNCH(k_vadm_init, (unsigned)ceil_div(n, 32), 32, 0, stream, d_params, d_states, d_rings, n_streams, n_machines);
+    FVAD_CUDA_TRY(cudaGetLastError());
+    return FVAD_OK;
 }
 
 __global__ void k_vadm(const VadmParams *__restrict__ params, VadmState *__restrict__ states, double *__restrict__ rings,
@@ -90,15 +77,11 @@ __global__ void k_vadm(const VadmParams *__restrict__ params, VadmState *__restr
     const VadmParams P = params[k];
     VadmState S = states[id];
     // ring pool: per stream a block holding every machine's rings
-    size_t per_stream = 0;
-    {
-        const VadmParams last = params[n_machines - 1];
-        per_stream = last.ring_off + (size_t)last.long_len + last.short_len + last.ratio_len;
-    }
-    double *ring_long = rings + s * per_stream + P.ring_off;
-    double *ring_short = ring_long + P.long_len;
-    double *ring_ratio = ring_short + P.short_len;
-    const double kTie = 1e-9;
+    const VadmParams last = params[n_machines - 1];
+    const size_t per_stream = last.ring_off + (size_t)last.long_len + last.short_len + last.ratio_len;
+    double *base = rings + s * per_stream + P.ring_off;
+    const RingFlat rl{base}, rs{base + P.long_len}, rr{base + P.long_len + P.short_len};
+    const double k_rel = vadm_k_rel(P.long_len);
     const int C = io.n_channels;
 
     for (size_t f = 0; f < io.n_frames; f++) {
@@ -111,110 +94,21 @@ __global__ void k_vadm(const VadmParams *__restrict__ params, VadmState *__restr
         const float volume_ratio = io.vol_ratio[s * io.ratio_stride + f];
         const float vad = io.vad ? io.vad[s * io.ratio_stride + f] : 0.0f;
         const unsigned long long index = io.first_index + f * io.index_step;
-
-        const double short_term = ring_push_exact(ring_short, P.short_len, S.short_w, S.short_cnt, min_volume);
-        const double cvr = ring_push_exact(ring_ratio, P.ratio_len, S.ratio_w, S.ratio_cnt, volume_ratio);
-
-        bool primary;
-        if (!S.long_has_last) {
-            const double base = P.has_initial ? P.initial : short_term;               // VADMachine.zig:158
-            primary = short_term > base * P.factor;
-        } else {
-            bool decided = false;
-            if (!S.long_exact) {
-                const double thr = S.approx * P.factor;
-                if (thr > 0.0 && thr < 1e300) {
-                    if (short_term > thr * (1.0 + kTie)) { primary = true; decided = true; }
-                    else if (short_term < thr * (1.0 - kTie)) { primary = false; decided = true; }
-                }
-                if (!decided) {                                                       // near a tie: the reference's own sum
-                    S.long_last = ring_avg_exact(ring_long, S.long_cnt);
-                    S.long_exact = 1;
-                    S.exact_fallbacks++;
-                }
-            }
-            if (!decided) primary = short_term > S.long_last * P.factor;
-        }
-        const bool met = primary && (cvr > P.ratio_threshold);
-
-        if (!met) {                                                                   // VADMachine.zig:165-167
-            const double nv = (double)min_volume;
-            if (S.long_cnt < P.long_len) {
-                // ring still filling (only without initial_long_term_avg): scalar changes each push
-                S.long_last = ring_push_exact(ring_long, P.long_len, S.long_w, S.long_cnt, min_volume);
-                S.approx = S.long_last; S.long_exact = 1; S.long_has_last = 1; S.since_refresh = 0;
-            } else {
-                const double scalar = 1.0 / (double)P.long_len;
-                const double old = ring_long[S.long_w];
-                ring_long[S.long_w] = nv;
-                S.long_w = (S.long_w + 1) % P.long_len;
-                S.approx += (nv * scalar - old * scalar);
-                S.long_exact = 0; S.long_has_last = 1;
-                if (++S.since_refresh >= 512 || !(S.approx >= 0.0)) {
-                    S.approx = ring_sum_blocked(ring_long, P.long_len);
-                    S.since_refresh = 0;
-                }
-            }
-        }
-
-        int rec = FVAD_REC_NONE;
-        unsigned long long sample_number = 0;
-        const int from_state = S.state;
-        bool emit = false;
-        fvad_segment seg;
-        switch (S.state) {                                                            // VADMachine.zig:176-221
-        case 0:   // closed
-            if (met) { S.state = 1; S.start_idx = index; }
-            break;
-        case 1: { // opening
-            const unsigned long long since = index - S.start_idx;
-            if (met && since >= P.min_consecutive) {
-                S.state = 2; rec = FVAD_REC_STARTED;
-                sample_number = P.start_buffer > S.start_idx ? 0 : S.start_idx - P.start_buffer;
-            } else if (!met) S.state = 0;
-            break; }
-        case 2:   // open
-            if (!met) { S.state = 3; S.end_idx = index; }
-            break;
-        case 3: { // closing
-            const unsigned long long since = index - S.end_idx;
-            if (met) S.state = 2;
-            else if (since >= P.max_gap) {
-                S.state = 0;
-                // onSpeechEnd (VADMachine.zig:252-294)
-                const unsigned long long from = S.start_idx, to = S.end_idx;
-                const float length_realtime = (float)(to - from) / P.sample_rate_f;
-                const bool dur_met = length_realtime >= P.min_dur;
-                if (dur_met) {
-                    seg.sample_from = P.start_buffer > from ? 0 : from - P.start_buffer;
-                    seg.sample_to = to + P.end_buffer;
-                    seg.debug_rnn_vad = S.sp_vad / (float)S.sp_vad_cnt;
-                    seg.debug_avg_speech_vol_ratio = S.sp_ratio / (float)S.sp_ratio_cnt;
-                    emit = true;
-                    rec = FVAD_REC_COMPLETED; sample_number = to + P.end_buffer;
-                } else { rec = FVAD_REC_ABORTED; sample_number = 0; }
-            }
-            break; }
-        }
-        // trackSpeechStats (VADMachine.zig:232-250)
-        if (from_state == 0 && S.state == 1) {
-            S.sp_vad = vad; S.sp_vad_cnt = 1; S.sp_ratio = volume_ratio; S.sp_ratio_cnt = 1;
-        } else if (from_state == 1 || from_state == 2) {
-            S.sp_vad += vad; S.sp_vad_cnt += 1; S.sp_ratio += volume_ratio; S.sp_ratio_cnt += 1;
-        }
-        if (emit) {
+        VadmStepOut o;
+        vadm_step(P, k_rel, rl, rs, rr, S, min_volume, volume_ratio, vad, index, o);
+        if (o.emit) {
             unsigned slot = atomicAdd(io.seg_count, 1u);
             if (slot < io.seg_cap) {
-                SegRecord r; r.stream = (unsigned)s; r.machine = (unsigned)k; r.seg = seg;
+                SegRecord r; r.stream = (unsigned)s; r.machine = (unsigned)k; r.seg = o.seg;
                 io.segs[slot] = r;
             }
         }
         if (k == 0) {
-            if (rec != FVAD_REC_NONE) {
+            if (o.rec != FVAD_REC_NONE) {
                 unsigned slot = atomicAdd(io.event_count, 1u);
                 if (slot < io.event_cap) {
                     EventRecord e; e.stream = (unsigned)s; e._pad = 0;
-                    e.ev.at_index = index; e.ev.recording_state = rec; e.ev._pad = 0; e.ev.sample_number = sample_number;
+                    e.ev.at_index = index; e.ev.recording_state = o.rec; e.ev._pad = 0; e.ev.sample_number = o.sample_number;
                     io.events[slot] = e;
                 }
             }
@@ -223,6 +117,19 @@ __global__ void k_vadm(const VadmParams *__restrict__ params, VadmState *__restr
                 tr.index = index; tr.min_volume = min_volume; tr.vol_ratio = volume_ratio; tr.rnn_vad = vad;
                 tr.has_vad = io.vad ? 1.0f : 0.0f;
                 io.trace[s * io.trace_stride + io.trace_offset + f] = tr;
+            }
+            if (io.feat_min) {                                    // the run's features kept on the device (fvad_batch_sweep)
+                const size_t at = s * io.feat_stride + io.feat_offset + f;
+                io.feat_ratio[at] = volume_ratio;
+                io.feat_vad[at] = vad;
+                for (int bnd = 0; bnd < io.feat_bands; bnd++) {
+                    float mv = 999.0f;
+                    for (int c = 0; c < C; c++) {
+                        const float v = io.band[((size_t)bnd * io.band_rows + s * C + c) * io.band_frame_stride + f];
+                        if (v < mv) mv = v;
+                    }
+                    io.feat_min[(size_t)bnd * io.feat_band_stride + at] = mv;
+                }
             }
         }
     }

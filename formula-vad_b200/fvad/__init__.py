@@ -14,6 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "libfvad_cuda.so")
 
 TRACE_RECORDS, TRACE_DENOISED, TRACE_RNN_VAD, TRACE_SPECTRA = 1, 2, 4, 8
+KEEP_FEATURES = 16        # FVAD_KEEP_FEATURES: per-STFT-frame features stay in HBM for PipelineBatch.sweep
 
 
 class VadMachineConfig(C.Structure):
@@ -74,6 +75,7 @@ def lib():
     sig = {
         "fvad_last_error": (C.c_char_p, []), "fvad_status_name": (C.c_char_p, [C.c_int]),
         "fvad_version": (C.c_char_p, []), "fvad_device_count": (C.c_int, []), "fvad_launch_count": (C.c_uint64, []),
+        "fvad_debug_set": (C.c_int, [C.c_char_p, C.c_char_p]),
         "fvad_profile_enable": (None, [C.c_int]), "fvad_profile_report": (C.c_int, [C.c_char_p, sz]),
         "fvad_default_vad_machine_config": (None, [C.POINTER(VadMachineConfig)]),
         "fvad_default_config": (None, [C.POINTER(Config), sz, sz]),
@@ -86,6 +88,9 @@ def lib():
         "fvad_batch_events": (C.c_int, [vp, sz, C.POINTER(vp), szp]),
         "fvad_batch_counts": (C.c_int, [vp, u64p, u64p]),
         "fvad_batch_cuda_stream": (vp, [vp]),
+        "fvad_batch_sweep": (C.c_int, [vp, C.POINTER(VadMachineConfig), sz, sz, vp, vp, C.c_int]),
+        "fvad_batch_feature_count": (C.c_int, [vp, szp]),
+        "fvad_batch_features": (C.c_int, [vp, sz, vp, sz, szp]),
         "fvad_batch_set_trace": (C.c_int, [vp, C.c_uint]),
         "fvad_batch_trace_records": (C.c_int, [vp, sz, vp, sz, szp]),
         "fvad_batch_trace_denoised": (C.c_int, [vp, sz, sz, _fp, sz, szp]),
@@ -114,6 +119,7 @@ def lib():
         "fvad_vadm_sweep": (C.c_int, [vp, sz, sz, C.POINTER(VadMachineConfig), sz, sz, sz, C.c_int, vp, sz, vp]),
         "fvad_vadm_sweep_static": (C.c_int, [vp, vp, vp, sz, sz, C.c_uint64, C.POINTER(VadMachineConfig), sz, sz, sz, vp, sz, vp, vp]),
         "fvad_eval_stats_batch": (C.c_int, [vp, sz, sz, vp, vp, vp, vp, vp, sz, sz, vp, C.c_int, vp]),
+        "fvad_eval_stats_batch_device": (C.c_int, [vp, sz, sz, vp, vp, vp, vp, vp, sz, sz, vp, vp]),
         "fvad_synth_fill_host": (C.c_int, [_fp, C.c_uint64, C.c_uint64, C.c_uint64, sz]),
         "fvad_synth_fill_device": (C.c_int, [vp, sz, C.c_uint64, C.c_uint64, sz, C.c_uint64, sz, vp]),
     }
@@ -145,6 +151,12 @@ def default_machine_config(**kw):
         else:
             setattr(c, k, v)
     return c
+
+
+def debug_set(key=None, value=None):
+    """fvad_debug_set: measurement / test knobs (kernel shapes, tile length, ...).  value None clears the key, key None
+    clears all.  The library reads no environment variables."""
+    _check(lib().fvad_debug_set(None if key is None else str(key).encode(), None if value is None else str(value).encode()))
 
 
 def launch_count():
@@ -244,6 +256,36 @@ class PipelineBatch:
 
     def reset(self):
         _check(lib().fvad_batch_reset(self._h))
+
+    def feature_count(self):
+        n = C.c_size_t()
+        _check(lib().fvad_batch_feature_count(self._h, C.byref(n)))
+        return n.value
+
+    def features(self, stream):
+        """The kept features of one stream as REC_DTYPE records (trace=KEEP_FEATURES)."""
+        n = C.c_size_t()
+        _check(lib().fvad_batch_features(self._h, stream, None, 0, C.byref(n)))
+        out = np.zeros(n.value, REC_DTYPE)
+        _check(lib().fvad_batch_features(self._h, stream, out.ctypes.data, n.value, C.byref(n)))
+        return out
+
+    def sweep(self, configs, max_segs=512, d_segs=0, d_counts=0):
+        """fvad_batch_sweep: further VADMachine configs over the features the batch kept (trace=KEEP_FEATURES), on the
+        device.  Host form (default): returns [stream][config] -> SEG_DTYPE arrays (re-run with a larger max_segs if a
+        list was truncated).  Device form: d_segs / d_counts are device addresses of [S*K*max_segs] fvad_segment and
+        [S*K] u32; returns None, the lists stay on the device (fvad.evaluator.stats_batch_device consumes them)."""
+        K = len(configs)
+        cfgs = (VadMachineConfig * K)(*configs)
+        if d_segs:
+            _check(lib().fvad_batch_sweep(self._h, cfgs, K, max_segs, C.c_void_p(d_segs), C.c_void_p(d_counts), 1))
+            return None
+        segs = np.zeros((self.n_streams * K, max_segs), SEG_DTYPE)
+        counts = np.zeros(self.n_streams * K, np.uint32)
+        _check(lib().fvad_batch_sweep(self._h, cfgs, K, max_segs, segs.ctypes.data, counts.ctypes.data, 0))
+        if counts.max(initial=0) > max_segs:
+            return self.sweep(configs, int(counts.max()))
+        return [[segs[s * K + k, :counts[s * K + k]].copy() for k in range(K)] for s in range(self.n_streams)]
 
     def counts(self):
         a, b = C.c_uint64(), C.c_uint64()

@@ -123,6 +123,22 @@ def stats_batch(segs, counts, set_ref, refs, sample_rate, config, device=-1):
     return out
 
 
+def stats_batch_device(d_segs, n_sets, max_segs, d_counts, set_ref, refs, sample_rate, config):
+    """The same with the result sets already on the device (PipelineBatch.sweep's device form, fvad_vadm_sweep_static):
+    d_segs / d_counts are device addresses; runs on the current device."""
+    set_ref = np.ascontiguousarray(set_ref, np.uint32)
+    offs = np.zeros(len(refs) + 1, np.uint32)
+    offs[1:] = np.cumsum([len(r) for r in refs])
+    allr = np.concatenate([np.asarray(r, dtype=REF_DTYPE) for r in refs]) if len(refs) else np.zeros(0, REF_DTYPE)
+    rf = np.ascontiguousarray(allr["from_sec"]) if len(allr) else np.zeros(1, np.float32)
+    rt = np.ascontiguousarray(allr["to_sec"]) if len(allr) else np.zeros(1, np.float32)
+    out = np.empty(n_sets, STATS_DTYPE)
+    _check(lib().fvad_eval_stats_batch_device(C.c_void_p(d_segs), n_sets, max_segs, C.c_void_p(d_counts), set_ref.ctypes.data,
+                                              rf.ctypes.data, rt.ctypes.data, offs.ctypes.data, len(refs), sample_rate,
+                                              C.addressof(config), out.ctypes.data))
+    return out
+
+
 def stack_segments(per_set):
     """Lists of SEG_DTYPE arrays -> ([n_sets, max_segs] array, counts)."""
     m = max([len(s) for s in per_set] + [1])

@@ -61,6 +61,12 @@ uint64_t fvad_launch_count(void);
 void fvad_profile_enable(int on);
 int  fvad_profile_report(char *buf, size_t cap);
 
+/* Measurement / test knobs -- kernel shapes ("bq_block", "bq_form", "biquad_lanes", "rnn_r", "rnn_g", "pitch_f"), tiling
+ * ("tile_frames", "slots"), scheduling ("prio", "latency_mode", "serial_stages"), "timeline", "model_blob".  They
+ * take effect for handles created afterwards.  value NULL clears the key; key NULL clears all.  This setter is the ONLY
+ * way to change them: the library does not read the process environment.  No counterpart in the reference. */
+int  fvad_debug_set(const char *key, const char *value);
+
 /* ---- configuration PODs ---------------------------------------------------------- */
 /* VADMachine.Config, src/AudioPipeline/VADMachine.zig:18-39 (same fields, same defaults
  * via fvad_default_config). */
@@ -167,13 +173,31 @@ void *fvad_batch_cuda_stream(fvad_batch *b);
 /* Optional traces for parity tests and for the config-5 sweep ("shared features").
  * Bits: 1 = per-STFT-frame records, 2 = denoised PCM, 4 = per-480-frame RNNoise VAD,
  * 8 = full STFT magnitude spectra.  Set before the first push. */
-enum { FVAD_TRACE_RECORDS = 1, FVAD_TRACE_DENOISED = 2, FVAD_TRACE_RNN_VAD = 4, FVAD_TRACE_SPECTRA = 8 };
+enum { FVAD_TRACE_RECORDS = 1, FVAD_TRACE_DENOISED = 2, FVAD_TRACE_RNN_VAD = 4, FVAD_TRACE_SPECTRA = 8,
+       /* not a trace (no host copies, no synchronisation): the per-STFT-frame features of everything pushed stay in HBM
+        * (12 B per frame per stream and 4 B per extra speech band) for fvad_batch_sweep */
+       FVAD_KEEP_FEATURES = 16 };
 int  fvad_batch_set_trace(fvad_batch *b, unsigned flags);
 /* Copy out (host): returns the number of items available via *n; copies min(cap, *n). */
 int  fvad_batch_trace_records(fvad_batch *b, size_t stream, fvad_stft_record *out, size_t cap, size_t *n);
 int  fvad_batch_trace_denoised(fvad_batch *b, size_t stream, size_t channel, float *out, size_t cap, size_t *n);
 int  fvad_batch_trace_rnn_vad(fvad_batch *b, size_t stream, float *out, size_t cap, size_t *n);
 int  fvad_batch_trace_spectra(fvad_batch *b, size_t stream, size_t channel, float *out, size_t cap_floats, size_t *n_floats);
+
+/* VAD.stateMachineStep's alt machines (src/AudioPipeline/VAD.zig:171-183,375-381) AFTER the fact and on the device:
+ * n_configs further VADMachine configurations scanned over the features the batch kept of everything pushed so far
+ * (FVAD_KEEP_FEATURES), one scan per (stream, config), no host round trip of the features (BASELINE configs[4]).  A
+ * config's speech band must be one the batch was created with (main or alt config).  Output layout = fvad_vadm_sweep's:
+ * segs[(stream*n_configs + k)*max_segs ...] in emission order, counts[stream*n_configs + k] (a count may exceed
+ * max_segs: the list is truncated); host arrays, or device arrays when outputs_on_device != 0 (feed them to
+ * fvad_eval_stats_batch_device).  Implies fvad_batch_sync; returns when the lists are complete. */
+int  fvad_batch_sweep(fvad_batch *b, const fvad_vad_machine_config *configs, size_t n_configs, size_t max_segs,
+                      fvad_segment *segs, uint32_t *counts, int outputs_on_device);
+/* The kept features of one stream as records (host copy; the main machine's band): what FVAD_TRACE_RECORDS gives, without
+ * its per-tile synchronisation.  Returns the number available via *n; copies min(cap, *n). */
+int  fvad_batch_features(fvad_batch *b, size_t stream, fvad_stft_record *out, size_t cap, size_t *n);
+/* STFT frames (feature records per stream) the machines have seen so far. */
+int  fvad_batch_feature_count(fvad_batch *b, size_t *n_records);
 
 /* ---- single pipeline = batch of 1 --------------------------------------------------- */
 typedef struct fvad_batch fvad_pipeline;
@@ -300,6 +324,12 @@ int    fvad_eval_stats_batch(const fvad_segment *segs, size_t n_sets, size_t max
                              const uint32_t *set_ref, const float *ref_from, const float *ref_to,
                              const uint32_t *ref_offsets, size_t n_refs, size_t sample_rate,
                              const fvad_stat_config *config, int device, fvad_single_stats *out);
+/* The same with the result sets already on the device (d_segs, d_counts: what fvad_batch_sweep / fvad_vadm_sweep_static
+ * leave there); everything else is host memory as above.  Runs on the current device. */
+int    fvad_eval_stats_batch_device(const fvad_segment *d_segs, size_t n_sets, size_t max_segs, const uint32_t *d_counts,
+                                    const uint32_t *set_ref, const float *ref_from, const float *ref_to,
+                                    const uint32_t *ref_offsets, size_t n_refs, size_t sample_rate,
+                                    const fvad_stat_config *config, fvad_single_stats *out);
 
 /* ---- seeded synthetic 48 kHz input ------------------------------ */
 /* Bit-identical on host and device.  Sample i of stream `stream_id` (absolute index

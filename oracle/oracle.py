@@ -9,6 +9,8 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 PORT_SO = os.path.join(HERE, "liboracle_port.so")
 REF_SO = os.path.join(HERE, "_ref", "liboracle_ref.so")
+REF_FAST_SO = os.path.join(HERE, "_ref", "liboracle_ref_fast.so")      # timing stand-in for zig ReleaseFast (Makefile: ref_fast)
+SYNTH_SO = os.path.join(HERE, "libsynth_host.so")
 
 
 class VadmConfig(C.Structure):
@@ -57,15 +59,17 @@ def build(kind="port"):
 
 
 class Oracle:
-    """One loaded oracle build ('port' or 'reference')."""
+    """One loaded oracle build: 'port', 'reference', or 'reference_fast' (the reference's sources at -O3 with AVX2/FMA
+    and contraction allowed: for TIMING only, never a parity checker)."""
 
     def __init__(self, kind="port"):
-        path = PORT_SO if kind == "port" else REF_SO
+        path = {"port": PORT_SO, "reference": REF_SO, "reference_fast": REF_FAST_SO}[kind]
         if not os.path.exists(path):
-            build(kind)
+            build("port" if kind == "port" else "reference")
         if not os.path.exists(path):
             raise FileNotFoundError(path)
         self.kind = kind
+        kind = "reference" if kind == "reference_fast" else kind
         L = self.lib = C.CDLL(path)
         L.orc_build_kind.restype = C.c_char_p
         L.orc_fft_create.restype = C.c_void_p
@@ -254,3 +258,30 @@ class Oracle:
 
 def have_reference():
     return os.path.exists(REF_SO)
+
+
+def have_reference_fast():
+    """The -O3 -march=x86-64-v3 build exists AND this host can run it (AVX2 + FMA)."""
+    if not os.path.exists(REF_FAST_SO):
+        return False
+    try:
+        flags = next(l for l in open("/proc/cpuinfo") if l.startswith("flags")).split()
+    except (OSError, StopIteration):
+        return False
+    return all(f in flags for f in ("avx2", "fma", "bmi2"))
+
+
+_synth = None
+
+
+def synth(seed, stream_id, first_sample, n):
+    """The seeded input generator (include/fvad_synth_core.h) on the host, without libfvad_cuda.so."""
+    global _synth
+    if _synth is None:
+        if not os.path.exists(SYNTH_SO):
+            build("port")
+        _synth = C.CDLL(SYNTH_SO)
+        _synth.orc_synth_fill.argtypes = [_fp, C.c_uint64, C.c_uint64, C.c_uint64, C.c_size_t]
+    out = np.empty(n, np.float32)
+    _synth.orc_synth_fill(_f(out), seed, stream_id, first_sample, n)
+    return out

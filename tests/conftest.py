@@ -70,3 +70,13 @@ def assert_segments_equal(got, want):
     assert len(got) == len(want), (len(got), len(want), got, want)
     assert np.array_equal(got["sample_from"], want["sample_from"])
     assert np.array_equal(got["sample_to"], want["sample_to"])
+
+
+@pytest.fixture
+def knobs(fv):
+    """Set library knobs (fvad_debug_set) for one test; cleared afterwards."""
+    def set_(**kw):
+        for k, v in kw.items():
+            fv.debug_set(k, v)
+    yield set_
+    fv.debug_set()

@@ -11,13 +11,13 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("rnn_rg", [None, (2, 1), (4, 1), (1, 2), (1, 3), (2, 2), (2, 3), (4, 2), (4, 3)])
-def test_denoiser_batch_bit_exact(fv, checker, rnn_rg, monkeypatch):
+def test_denoiser_batch_bit_exact(fv, checker, rnn_rg, knobs):
     """rnn_rg forces the RNN kernel shape: G independent thread groups per CTA, each walking R states in lock-step
     (chosen by itself only beyond 148 states); 5 states leave the last group / CTA partly filled or empty and the
     streams' silent frames make the states' frame counts differ, so idle states and idle groups are exercised."""
     if rnn_rg:
-        monkeypatch.setenv("FVAD_RNN_R", str(rnn_rg[0]))
-        monkeypatch.setenv("FVAD_RNN_G", str(rnn_rg[1]))
+        knobs(rnn_r=str(rnn_rg[0]))
+        knobs(rnn_g=str(rnn_rg[1]))
     S, secs = 5, 8
     pcm = np.stack([synth(fv, 20 + s, secs) for s in range(S)])
     d = fv.DenoiserBatch(S)
@@ -35,12 +35,14 @@ def test_denoiser_batch_bit_exact(fv, checker, rnn_rg, monkeypatch):
     assert silent > 0 and voiced > 0, "input must exercise silent and voiced frames"
 
 
-@pytest.mark.parametrize("bq,roll", [(32, 0), (48, 0), (60, 0), (48, 1), (160, 1)])
-def test_denoiser_biquad_block_sizes(fv, checker, bq, roll, monkeypatch):
-    """The biquad kernel's block length (samples between two verdicts of the verifying warps; 96 by default) and the form
-    of the chain lane's loop (unrolled / rolled) change how the chain is cut into verified pieces, never the result."""
-    monkeypatch.setenv("FVAD_BQ_BLOCK", str(bq))
-    monkeypatch.setenv("FVAD_BQ_ROLL", str(roll))
+@pytest.mark.parametrize("bq,roll,form", [(32, 0, 1), (48, 0, 1), (60, 0, 1), (48, 1, 1), (96, 1, 1), (160, 1, 1), (48, 1, 2), (96, 1, 2),
+                                          (240, 1, 2), (48, 1, 3), (160, 1, 3)])
+def test_denoiser_biquad_block_sizes(fv, checker, bq, roll, form, knobs):
+    """The biquad kernel's block length (samples between two verdicts of the verifying warps; 96 by default), the form
+    of the chain lane's loop (unrolled / rolled) and the kernel's form (3, the default: chain warp and verifying warps
+    hand blocks over through named barriers without waiting for each other; 2: lock-step, the lane publishes only m0;
+    1: the first form) change how the chain is cut into verified pieces and who stores what, never the result."""
+    knobs(bq_block=str(bq), bq_roll=str(roll), bq_form=str(form))
     S, secs = 3, 6
     pcm = np.stack([synth(fv, 40 + s, secs) for s in range(S)])
     d = fv.DenoiserBatch(S)
@@ -51,11 +53,11 @@ def test_denoiser_biquad_block_sizes(fv, checker, bq, roll, monkeypatch):
         assert np.array_equal(out[s], wo), (s, np.abs(out[s] - wo).max())
 
 
-def test_denoiser_biquad_state_per_lane(fv, checker, monkeypatch):
+def test_denoiser_biquad_state_per_lane(fv, checker, knobs):
     """The many-stream biquad (a state per lane, 32 states per CTA; chosen by itself only from 1000 states on)
     forced on 37 states: the second CTA has 5 live lanes, the streams' digital silences exercise the denormal path and the
     hazard replays are lane-divergent.  A second call continues from the carried filter state."""
-    monkeypatch.setenv("FVAD_BIQUAD_LANES", "1")
+    knobs(biquad_lanes="1")
     S, secs = 37, 6
     pcm = np.stack([synth(fv, 60 + s, secs) for s in range(S)])
     d = fv.DenoiserBatch(S)
@@ -90,9 +92,9 @@ def test_denoiser_single_frame_api(fv, checker):
 
 
 @pytest.mark.parametrize("n_channels,tile", [(1, None), (1, 37), (2, 53)])
-def test_full_pipeline_bit_exact(fv, checker, n_channels, tile, monkeypatch):
+def test_full_pipeline_bit_exact(fv, checker, n_channels, tile, knobs):
     if tile:
-        monkeypatch.setenv("FVAD_TILE_FRAMES", str(tile))
+        knobs(tile_frames=str(tile))
     S, secs = 3, 50
     pcm = np.stack([np.stack([synth(fv, 200 + 5 * s + c, secs) * np.float32(1.0 if c == 0 else 0.7)
                               for c in range(n_channels)]) for s in range(S)])

@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 SEED = 0xF1AD5EED00000000
 
 
-def _run(fv, torch, ids, secs, tile=None, monkeypatch=None):
+def _run(fv, torch, ids, secs, tile=None, knobs=None):
     n = secs * 48000
     x = torch.empty(len(ids), n, dtype=torch.float32, device="cuda")
     for r, sid in enumerate(ids):                                    # one fill per row so that rows can be permuted
@@ -22,7 +22,7 @@ def _run(fv, torch, ids, secs, tile=None, monkeypatch=None):
             fv.synth_device(x.data_ptr() + 4 * (r * n + off), n, SEED, sid, 1, off, m)
     torch.cuda.synchronize()
     if tile:
-        monkeypatch.setenv("FVAD_TILE_FRAMES", str(tile))
+        knobs(tile_frames=str(tile))
     with fv.PipelineBatch(len(ids)) as b:
         b.push_device(x.data_ptr(), n, n, n)
         b.sync()
@@ -32,7 +32,7 @@ def _run(fv, torch, ids, secs, tile=None, monkeypatch=None):
     return out
 
 
-def test_configs1_full_size_properties(fv, checker, monkeypatch):
+def test_configs1_full_size_properties(fv, checker, knobs):
     torch = pytest.importorskip("torch")
     free, _ = torch.cuda.mem_get_info()
     if free < 60e9:
@@ -40,7 +40,7 @@ def test_configs1_full_size_properties(fv, checker, monkeypatch):
     S, secs = 20, 7200
     ids = list(range(S))
     a = _run(fv, torch, ids, secs)
-    b = _run(fv, torch, ids[::-1], secs, tile=4111, monkeypatch=monkeypatch)
+    b = _run(fv, torch, ids[::-1], secs, tile=4111, knobs=knobs)
     total = 0
     for sid in ids:
         (sa, ea), (sb, eb) = a[sid], b[sid]

@@ -15,10 +15,10 @@ def _result(b, S):
 
 
 @pytest.mark.parametrize("n_channels,tile", [(1, 61), (2, 47), (1, None)])
-def test_push_cut_invariance(fv, checker, n_channels, tile, monkeypatch):
+def test_push_cut_invariance(fv, checker, n_channels, tile, knobs):
     import torch
     if tile:
-        monkeypatch.setenv("FVAD_TILE_FRAMES", str(tile))
+        knobs(tile_frames=str(tile))
     S, secs = 3, 45
     n = secs * 48000
     pcm = np.stack([np.stack([synth(fv, 620 + 3 * s, secs) * np.float32(1.0 if c == 0 else 0.6)

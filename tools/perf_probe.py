@@ -10,9 +10,17 @@ reps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
 use_dn = int(sys.argv[4]) if len(sys.argv) > 4 else 1
 prof = int(sys.argv[5]) if len(sys.argv) > 5 else 0
 host = int(sys.argv[6]) if len(sys.argv) > 6 else 0
+for k, v in os.environ.items():          # FVADK_<knob>=<value> -> fvad_debug_set (the library itself reads no environment)
+    if k.startswith("FVADK_"):
+        fvad.debug_set(k[6:].lower(), v)
 n = secs * 48000
 x = torch.empty(S, n, dtype=torch.float32, device="cuda")
 fvad.synth_device(x.data_ptr(), n, 0xF1AD5EED00000000, 0, S, 0, n)
+if os.environ.get("PROBE_INPUT") == "noise":      # white noise of constant level instead of the synthetic streams
+    x.uniform_(-0.06, 0.06)
+elif os.environ.get("PROBE_INPUT") == "tone":
+    t = torch.arange(n, device="cuda", dtype=torch.float32)
+    x.copy_((0.1 * torch.sin(t * (2 * 3.141592653589793 * 220.0 / 48000.0))).expand(S, n))
 torch.cuda.synchronize()
 b = fvad.PipelineBatch(S, use_denoiser=bool(use_dn))
 if host:
