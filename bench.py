@@ -259,7 +259,9 @@ def b200_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        # a leg that one rank skips and another does not would otherwise hang for NCCL's default ten minutes
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=240))
     S, secs = args.streams, args.seconds
     n = secs * SR
     first_stream = rank * S                      # weak scaling: every rank owns its own S streams
@@ -273,6 +275,13 @@ def b200_arm(args):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    def host_mem_per_rank():
+        """MemAvailable split over the ranks of this box, agreed on by all of them (every rank must take the same branch)."""
+        a = torch.tensor([mem_available()], dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_reduce(a, op=dist.ReduceOp.MIN)
+        return int(a[0]) // world
 
     def timed(fn, k, ext):
         """k calls of fn between two CUDA events on the batch's own stream, a barrier + synchronize on both sides;
@@ -384,10 +393,10 @@ def b200_arm(args):
     e2e = e2e_sim = None
     if not args.no_e2e:
         need = S * n * 4
-        avail = mem_available()
+        avail = host_mem_per_rank()
         win = n
-        if avail and need * world * 2 > avail:                    # keep well inside host RAM: bounded window, pushed repeatedly
-            win = max(600 * SR, int(avail / (world * 8) / (S * 4)) // (600 * SR) * (600 * SR))
+        if avail and need * 2 > avail:                            # keep well inside host RAM: bounded window, pushed repeatedly
+            win = max(600 * SR, int(avail / 8 / (S * 4)) // (600 * SR) * (600 * SR))
             win = min(win, n)
         h = torch.empty(S, win, dtype=torch.float32, pin_memory=True)
         for off in range(0, win, CH):
@@ -493,7 +502,7 @@ def b200_arm(args):
     batched = None
     if not args.no_batched:
         try:
-            batched = batched_leg(args, fvad, shard, torch, dist, dev, local, rank, world, timed, fill_device, host_rows, barrier)
+            batched = batched_leg(args, fvad, shard, torch, dist, dev, local, rank, world, timed, fill_device, host_rows, host_mem_per_rank)
         except Exception as e:
             errors["batched"] = repr(e)
             barrier()
@@ -586,7 +595,7 @@ def stft_leg(fvad, torch, dev, peak):
     return stft
 
 
-def batched_leg(args, fvad, shard, torch, dist, dev, local, rank, world, timed, fill_device, host_rows, barrier):
+def batched_leg(args, fvad, shard, torch, dist, dev, local, rank, world, timed, fill_device, host_rows, host_mem_per_rank):
     sizes = [int(v) for v in str(args.batched_streams).split(",") if v]
     Sb, sb = sizes[0], args.batched_seconds
     nb = sb * SR
@@ -616,9 +625,9 @@ def batched_leg(args, fvad, shard, torch, dist, dev, local, rank, world, timed, 
            "input": "device-resident"}
     # host-fed: the same step through fvad_batch_push, from pinned rows and (N = 1) from pageable rows
     need = Sb * nb * 4
-    avail = mem_available()
-    if avail and need * world * 1.5 > avail:
-        out["e2e"] = {"skipped": f"{need * world / 1e9:.0f} GB of host rows do not fit beside MemAvailable {avail / 1e9:.0f} GB"}
+    avail = host_mem_per_rank()
+    if avail and need * 1.5 > avail:
+        out["e2e"] = {"skipped": f"{need / 1e9:.0f} GB of host rows per rank do not fit beside {avail / 1e9:.0f} GB of free host memory per rank"}
     else:
         hb = torch.empty(Sb, nb, dtype=torch.float32, pin_memory=True)
         hb.copy_(xb)

@@ -86,6 +86,24 @@ struct fvad_batch {
     // FVAD_KEEP_FEATURES: the per-STFT-frame features of the whole run stay in HBM for fvad_batch_sweep
     float *d_feat_min = nullptr, *d_feat_ratio = nullptr, *d_feat_vad = nullptr;   // [bands][S][feat_cap], [S][feat_cap] x 2
     size_t feat_cap = 0;
+    // Recorder (fvad_batch_set_recording): history of the original PCM + the host-side capture state per stream
+    bool rec_on = false;
+    bool hist_fixed = false;               // a ring of hist_cap samples (else: everything pushed, growing)
+    float *d_hist = nullptr;               // [rows][hist_cap]: absolute sample i of a row at [i % hist_cap]
+    size_t hist_cap = 0;
+    uint64_t hist_len = 0;                 // samples per row copied into the history so far
+    fvad_on_recording_fn on_recording = nullptr;
+    void *on_recording_ctx = nullptr;
+    struct RecState { bool active = false; uint64_t start = 0; size_t next_event = 0; };
+    struct PendingClip { size_t stream; uint64_t start, end; };
+    struct StoredClip { fvad_clip meta; std::vector<float> pcm; };
+    std::vector<RecState> rec_state;       // [stream]
+    std::vector<PendingClip> rec_pending;  // completed by the machine, waiting for the stream to reach their end
+    std::vector<std::vector<StoredClip>> rec_clips;     // [stream] delivered since the last fvad_batch_clips
+    std::vector<std::vector<fvad_clip>> rec_view;       // [stream] what the last fvad_batch_clips returned
+    std::vector<std::vector<StoredClip>> rec_held;      // [stream] storage behind rec_view
+    ClipPiece *d_clip_pieces = nullptr; size_t clip_pieces_cap = 0;
+    float *d_clip_stage = nullptr; size_t clip_stage_cap = 0;
     // sweep scratch, kept between calls
     VadmParams *d_sw_params = nullptr; size_t sw_params_cap = 0;
     double *d_sw_rings = nullptr; size_t sw_rings_cap = 0;
@@ -168,6 +186,7 @@ extern "C" void fvad_batch_destroy(fvad_batch *b) {
         cudaFree(b->d_rings); cudaFree(b->d_segs); cudaFree(b->d_seg_count); cudaFree(b->d_events);
         cudaFree(b->d_event_count); cudaFree(b->d_trace);
         cudaFree(b->d_feat_min); cudaFree(b->d_feat_ratio); cudaFree(b->d_feat_vad);
+        cudaFree(b->d_hist); cudaFree(b->d_clip_pieces); cudaFree(b->d_clip_stage);
         cudaFree(b->d_sw_params); cudaFree(b->d_sw_rings); cudaFree(b->d_sw_segs); cudaFree(b->d_sw_counts);
         if (b->h_arena_cnt) cudaFreeHost(b->h_arena_cnt);
         for (cudaStream_t st : {b->sA, b->sB, b->sB2, b->sC, b->sE}) if (st && st != b->stream) cudaStreamDestroy(st);
@@ -542,6 +561,7 @@ static int ensure_trace_buffers(fvad_batch *b) {
 }
 
 static int drain_results(fvad_batch *b);
+static int extract_clips(fvad_batch *b);
 
 // An arena half full (as of the last tile the device has finished): drain it to the host lists before adding more.
 static int arena_check(fvad_batch *b) {
@@ -571,6 +591,34 @@ static int launch_tile(fvad_batch *b) {
     b->fill_len = tail;
     b->fill_waited = false;
     return join_machines(b);
+}
+
+// Recorder: the m samples per row just appended (device rows at src, row r at src + r * src_stride) also go into the PCM
+// history, on the copy stream behind the copy that brought them.
+static int history_append(fvad_batch *b, const float *src, size_t src_stride, size_t m) {
+    if (!b->rec_on || !m) return FVAD_OK;
+    if (!b->hist_fixed && b->hist_len + m > b->hist_cap) {       // everything is kept: the buffer doubles (stop-the-world)
+        size_t cap = b->hist_cap ? b->hist_cap : (size_t)1 << 20;
+        while (cap < b->hist_len + m) cap *= 2;
+        for (cudaStream_t st : {b->sH, b->sA, b->sB, b->sB2, b->sC, b->sE, b->stream}) if (st) FVAD_CUDA_TRY(cudaStreamSynchronize(st));
+        float *nh = nullptr;
+        FVAD_TRY(dmalloc(&nh, b->rows * cap));
+        if (b->hist_len)
+            FVAD_CUDA_TRY(cudaMemcpy2D(nh, cap * sizeof(float), b->d_hist, b->hist_cap * sizeof(float), (size_t)b->hist_len * sizeof(float),
+                                       b->rows, cudaMemcpyDeviceToDevice));
+        cudaFree(b->d_hist);
+        b->d_hist = nh; b->hist_cap = cap;
+    }
+    size_t done = 0;
+    while (done < m) {                                           // at most two pieces when the ring wraps
+        const size_t pos = (size_t)((b->hist_len + done) % b->hist_cap);
+        const size_t n = std::min(m - done, b->hist_cap - pos);
+        FVAD_CUDA_TRY(cudaMemcpy2DAsync(b->d_hist + pos, b->hist_cap * sizeof(float), src + done, src_stride * sizeof(float),
+                                        n * sizeof(float), b->rows, cudaMemcpyDeviceToDevice, b->sH));
+        done += n;
+    }
+    b->hist_len += m;
+    return FVAD_OK;
 }
 
 // Before the first copy into the filling buffer since it changed hands: its previous tile must have been read.
@@ -608,6 +656,7 @@ extern "C" int fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n,
             for (size_t r = 0; r < b->rows; r++)
                 FVAD_CUDA_TRY(cudaMemcpyAsync(dst + r * b->work_cap, pcm[r] + off, sizeof(float) * m, cudaMemcpyHostToDevice, b->sH));
         }
+        FVAD_TRY(history_append(b, dst, b->work_cap, m));
         b->h2d_dirty = true;
         b->fill_len += m;
         off += m;
@@ -635,6 +684,7 @@ extern "C" int fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t 
         if (b->fill_len == 0 && uniform && n - off >= tile_samples(b)) {
             size_t tail = 0;
             FVAD_TRY(arena_check(b));
+            FVAD_TRY(history_append(b, d_pcm + off, row_stride, tile_samples(b)));
             FVAD_TRY(process_tile(b, d_pcm + off, row_stride, tile_samples(b), nullptr, &tail));
             FVAD_TRY(join_machines(b));
             off += tile_samples(b);
@@ -652,6 +702,7 @@ extern "C" int fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t 
             FVAD_TRY(gather_rows_launch(b->d_work_buf[b->work_par], b->work_cap, b->fill_len, d_pcm, stream_stride, channel_stride,
                                         off, b->S, (int)b->C, m, b->sH));
         }
+        FVAD_TRY(history_append(b, dst, b->work_cap, m));
         b->h2d_dirty = true;
         b->fill_len += m;
         off += m;
@@ -663,7 +714,111 @@ extern "C" int fvad_batch_push_device(fvad_batch *b, const float *d_pcm, size_t 
 
 static int collect(fvad_batch *b) {
     FVAD_TRY(launch_tile(b));                                  // whatever complete frames the filling buffer holds
-    return drain_results(b);
+    FVAD_TRY(drain_results(b));
+    return b->rec_on ? extract_clips(b) : FVAD_OK;             // (drain_results returns early when nothing new was decided)
+}
+
+// audio_utils.rmsVolume (src/audio_utils.zig:14-24): f32 sum of squares in order, mean, sqrt
+static float rms_volume_host(const float *x, size_t n) {
+    float sum = 0.0f;
+    for (size_t i = 0; i < n; i++) sum += x[i] * x[i];
+    return sqrtf(sum / (float)n);
+}
+
+// Recorder: walk the main machine's new events (beginCapture / endCapture, VAD.zig:362-373), then cut every clip whose end
+// the stream has reached out of the PCM history (Recorder.finalize -> segmentToAudioBuffer, Recorder.zig:87-146).
+static int extract_clips(fvad_batch *b) {
+    if (!b->rec_on) return FVAD_OK;
+    for (size_t s = 0; s < b->S; s++) {
+        fvad_batch::RecState &rs = b->rec_state[s];
+        const auto &ev = b->events[s];
+        for (; rs.next_event < ev.size(); rs.next_event++) {
+            const fvad_capture_event &e = ev[rs.next_event];
+            if (e.recording_state == FVAD_REC_STARTED) { rs.active = true; rs.start = e.sample_number; }        // Recorder.start
+            else if (e.recording_state == FVAD_REC_ABORTED) rs.active = false;                                   // finalize(0, false)
+            else if (e.recording_state == FVAD_REC_COMPLETED && rs.active) {
+                rs.active = false;
+                if (e.sample_number > rs.start) b->rec_pending.push_back({s, rs.start, e.sample_number});
+            }
+        }
+    }
+    // ready = the stream has been pushed up to the clip's end (AudioPipeline.maybeRecordBuffer); keep the others waiting
+    std::vector<fvad_batch::PendingClip> ready, wait;
+    for (auto &c : b->rec_pending) (c.end <= b->total_write_count ? ready : wait).push_back(c);
+    b->rec_pending.swap(wait);
+    if (ready.empty()) return FVAD_OK;
+    std::stable_sort(ready.begin(), ready.end(), [](const fvad_batch::PendingClip &a, const fvad_batch::PendingClip &c) {
+        return a.stream != c.stream ? a.stream < c.stream : a.end < c.end; });
+    FVAD_CUDA_TRY(cudaStreamSynchronize(b->sH));                 // the history holds everything pushed
+    const size_t C = b->C;
+    const size_t stage_max = (size_t)1 << 26;                    // floats per gather round (256 MB)
+    size_t i0 = 0;
+    while (i0 < ready.size()) {
+        // a round: as many clips as fit the staging buffer (a single clip larger than that gets a round of its own)
+        std::vector<ClipPiece> pieces;
+        size_t i1 = i0, total = 0, max_len = 0;
+        while (i1 < ready.size()) {
+            const auto &c = ready[i1];
+            const size_t len = (size_t)(c.end - c.start);
+            const bool lost = b->hist_fixed && c.start + b->hist_cap < b->hist_len;
+            const size_t need = lost ? 0 : len * C;
+            if (i1 > i0 && total + need > stage_max) break;
+            if (!lost) {
+                for (size_t ch = 0; ch < C; ch++) pieces.push_back({c.stream * C + ch, c.start, len, total + ch * len});
+                max_len = std::max(max_len, len);
+            }
+            total += need;
+            i1++;
+        }
+        std::vector<float> host(total);
+        if (total) {
+            if (pieces.size() > b->clip_pieces_cap) {
+                cudaFree(b->d_clip_pieces); b->d_clip_pieces = nullptr; b->clip_pieces_cap = 0;
+                FVAD_TRY(dmalloc(&b->d_clip_pieces, pieces.size() * 2));
+                b->clip_pieces_cap = pieces.size() * 2;
+            }
+            if (total > b->clip_stage_cap) {
+                cudaFree(b->d_clip_stage); b->d_clip_stage = nullptr; b->clip_stage_cap = 0;
+                FVAD_TRY(dmalloc(&b->d_clip_stage, total));
+                b->clip_stage_cap = total;
+            }
+            FVAD_CUDA_TRY(cudaMemcpyAsync(b->d_clip_pieces, pieces.data(), sizeof(ClipPiece) * pieces.size(), cudaMemcpyHostToDevice, b->stream));
+            FVAD_TRY(gather_clips_launch(b->d_clip_pieces, pieces.size(), max_len, b->d_hist, b->hist_cap, b->d_clip_stage, b->stream));
+            FVAD_CUDA_TRY(cudaMemcpyAsync(host.data(), b->d_clip_stage, sizeof(float) * total, cudaMemcpyDeviceToHost, b->stream));
+            FVAD_CUDA_TRY(cudaStreamSynchronize(b->stream));
+        }
+        size_t off = 0;
+        for (size_t i = i0; i < i1; i++) {
+            const auto &c = ready[i];
+            const size_t len = (size_t)(c.end - c.start);
+            const bool lost = b->hist_fixed && c.start + b->hist_cap < b->hist_len;
+            fvad_batch::StoredClip sc;
+            sc.meta.global_start_frame_number = c.start;
+            sc.meta.length = len;
+            sc.meta.sample_rate = b->cfg.sample_rate;
+            sc.meta.duration_seconds = (float)len / (float)b->cfg.sample_rate;     // Recorder.zig:139
+            sc.meta.channel = 0; sc.meta.lost = lost ? 1 : 0; sc.meta.pcm = nullptr;
+            if (!lost) {
+                size_t best = 0;
+                float best_vol = 9999.0f;                                           // Recorder.findBestChannel, Recorder.zig:103-119
+                for (size_t ch = 0; ch < C; ch++) {
+                    const float vol = rms_volume_host(host.data() + off + ch * len, len);
+                    if (vol < best_vol) { best = ch; best_vol = vol; }
+                }
+                sc.meta.channel = best;
+                sc.pcm.assign(host.begin() + off + best * len, host.begin() + off + (best + 1) * len);
+                off += len * C;
+            }
+            if (b->on_recording) {
+                fvad_clip view = sc.meta;
+                view.pcm = lost ? nullptr : sc.pcm.data();
+                b->on_recording(b->on_recording_ctx, c.stream, &view);
+            }
+            b->rec_clips[c.stream].push_back(std::move(sc));
+        }
+        i0 = i1;
+    }
+    return FVAD_OK;
 }
 
 static int drain_results(fvad_batch *b) {
@@ -699,7 +854,7 @@ static int drain_results(fvad_batch *b) {
     }
     b->h_arena_cnt[0] = b->h_arena_cnt[1] = 0;
     b->dirty = false;
-    return FVAD_OK;
+    return extract_clips(b);
 }
 
 extern "C" int fvad_batch_sync(fvad_batch *b) {
@@ -719,6 +874,12 @@ extern "C" int fvad_batch_reset(fvad_batch *b) {
         FVAD_CUDA_TRY(cudaMemsetAsync(b->d_vad480, 0, sizeof(float) * b->S * b->stride480, b->stream));
     }
     b->fill_len = 0; b->fill_waited = false; b->h2d_dirty = false;
+    b->hist_len = 0;
+    if (b->rec_on) {
+        b->rec_state.assign(b->S, fvad_batch::RecState());
+        b->rec_pending.clear();
+        for (auto &v : b->rec_clips) v.clear();
+    }
     b->den_carry = 0; b->base480 = 0; b->tile_no = 0; b->stft_tile_no = 0; b->e_pending = -1;
     b->work_par = 0;
     b->total_write_count = b->read_count = b->stft_done = 0;
@@ -850,6 +1011,42 @@ extern "C" int fvad_batch_features(fvad_batch *b, size_t stream, fvad_stft_recor
 extern "C" int fvad_batch_feature_count(fvad_batch *b, size_t *n_records) {
     if (!b || !n_records) return set_error(FVAD_EINVALID_ARGUMENT, "null argument");
     *n_records = (size_t)b->stft_done + 0;
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_set_recording(fvad_batch *b, size_t history_samples, fvad_on_recording_fn on_recording, void *ctx) {
+    if (!b) return set_error(FVAD_EINVALID_ARGUMENT, "null batch");
+    if (b->total_write_count) return set_error(FVAD_EINVALID_ARGUMENT, "enable the recorder before the first push");
+    DeviceGuard g(b->device);
+    if (!g.ok) return set_error(FVAD_ECUDA, "cannot select device %d", b->device);
+    cudaFree(b->d_hist); b->d_hist = nullptr; b->hist_cap = 0; b->hist_len = 0;
+    b->hist_fixed = history_samples != 0;
+    if (b->hist_fixed) {
+        FVAD_TRY(dmalloc(&b->d_hist, b->rows * history_samples));
+        b->hist_cap = history_samples;
+    }
+    b->rec_on = true;
+    b->on_recording = on_recording; b->on_recording_ctx = ctx;
+    b->rec_state.assign(b->S, fvad_batch::RecState());
+    b->rec_pending.clear();
+    b->rec_clips.assign(b->S, {}); b->rec_view.assign(b->S, {}); b->rec_held.assign(b->S, {});
+    return FVAD_OK;
+}
+
+extern "C" int fvad_batch_clips(fvad_batch *b, size_t stream, const fvad_clip **clips, size_t *n) {
+    if (!b || !clips || !n || stream >= b->S) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_clips: bad argument");
+    if (!b->rec_on) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_batch_clips: the recorder is off (fvad_batch_set_recording)");
+    FVAD_TRY(fvad_batch_sync(b));
+    b->rec_held[stream].swap(b->rec_clips[stream]);            // what was handed out before is released now
+    b->rec_clips[stream].clear();
+    auto &view = b->rec_view[stream];
+    view.clear();
+    for (auto &sc : b->rec_held[stream]) {
+        fvad_clip c = sc.meta;
+        c.pcm = sc.meta.lost ? nullptr : sc.pcm.data();
+        view.push_back(c);
+    }
+    *clips = view.data(); *n = view.size();
     return FVAD_OK;
 }
 

@@ -124,6 +124,34 @@ int gather_rows_launch(float *dst, size_t dst_stride, size_t dst_off, const floa
 }  // namespace fvad
 
 namespace fvad {
+// Recorder clips: piece i = `len` samples of history row `row` from absolute sample `start` (ring position start % cap)
+// to dst + dst_off.  One CTA column per piece.
+__global__ void k_gather_clips(const ClipPiece *__restrict__ pieces, const float *__restrict__ hist, size_t cap,
+                               float *__restrict__ dst) {
+    const ClipPiece p = pieces[blockIdx.y];
+    const float *row = hist + p.row * cap;
+    size_t pos = (size_t)((p.start + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) % cap);
+    const size_t step = (size_t)gridDim.x * blockDim.x, wrap = step % cap;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < p.len; i += step) {
+        dst[p.dst_off + i] = row[pos];
+        pos += wrap;
+        if (pos >= cap) pos -= cap;
+    }
+}
+
+int gather_clips_launch(const ClipPiece *d_pieces, size_t n_pieces, size_t max_len, const float *d_hist, size_t cap, float *d_dst,
+                        cudaStream_t stream) {
+    if (!n_pieces || !max_len) return FVAD_OK;
+    unsigned gx = (unsigned)ceil_div(max_len, 256 * 8);
+    if (gx > 256) gx = 256;
+    for (size_t p0 = 0; p0 < n_pieces; p0 += 65535) {
+        const size_t np = n_pieces - p0 < 65535 ? n_pieces - p0 : 65535;
+        FVAD_LAUNCH(k_gather_clips, dim3(gx, (unsigned)np), 256, 0, stream, d_pieces + p0, d_hist, cap, d_dst);
+    }
+    FVAD_CUDA_TRY(cudaGetLastError());
+    return FVAD_OK;
+}
+
 __global__ void k_shift_hist(float *arr, size_t stride, int hist, size_t n_new, size_t n_streams) {
     const size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_streams) return;

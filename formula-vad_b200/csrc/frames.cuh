@@ -29,6 +29,15 @@ int gather_rows_launch(float *dst, size_t dst_stride, size_t dst_off, const floa
 }  // namespace fvad
 
 namespace fvad {
+// Recorder (src/AudioPipeline/Recorder.zig:52-146): the original samples [start, start+len) of one history row, gathered
+// out of the PCM history ring (absolute sample i of row r at d_hist[r*cap + i % cap]) into a packed staging buffer.
+struct ClipPiece {
+    size_t row;                     // history row = stream * n_channels + channel
+    unsigned long long start;       // absolute sample index
+    size_t len, dst_off;            // floats
+};
+int gather_clips_launch(const ClipPiece *d_pieces, size_t n_pieces, size_t max_len, const float *d_hist, size_t cap, float *d_dst,
+                        cudaStream_t stream);
 // arr[s][0..hist) = arr[s][n_new .. n_new+hist) for every stream (keeps the last `hist` entries as history)
 int shift_hist_launch(float *arr, size_t stride, int hist, size_t n_new, size_t n_streams, cudaStream_t stream);
 }

@@ -11,6 +11,7 @@
 // up to the sign of a zero, which no magnitude can observe.
 #include "stft.cuh"
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -20,16 +21,50 @@ namespace fvad {
 // ------------------------------------------------------------------------------------------
 // host tables
 // ------------------------------------------------------------------------------------------
-// hannWindowPeriodic -> cosineSumWindowPeriodic (window_fn.zig:22-28,51-68): K=1, alphas
-// {0.5,0.5}, evaluated in f32; `@cos` on f32 is taken as the correctly rounded cosine.
+// `@cos` on an f32 in Zig is compiler-rt's cosf, a port of musl's (FreeBSD msun s_cosf.c / k_cosf.c / k_sinf.c): range
+// split at odd multiples of pi/4, degree-8 / degree-9 polynomials evaluated in double, one rounding to float.  It is NOT
+// correctly rounded: for the 2048-entry periodic Hann window it differs from (float)cos((double)x) in ONE entry (n = 196)
+// by one ulp of the cosine.  The window is part of every spectrum, so the table is built with the same function the
+// reference calls.  Only |x| <= 9 pi / 4 is needed (the window's arguments lie in [0, 2 pi)).
+namespace {
+float zig_cosdf(double x) {
+    const double C0 = -0x1ffffffd0c5e81.0p-54, C1 = 0x155553e1053a42.0p-57, C2 = -0x16c087e80f1e27.0p-62, C3 = 0x199342e0ee5069.0p-68;
+    const double z = x * x, w = z * z, r = C2 + z * C3;
+    return (float)(((1.0 + z * C0) + w * C1) + (w * z) * r);
+}
+float zig_sindf(double x) {
+    const double S1 = -0x15555554cbac77.0p-55, S2 = 0x111110896efbb2.0p-59, S3 = -0x1a00f9e2cae774.0p-65, S4 = 0x16cd878c3b46a7.0p-71;
+    const double z = x * x, w = z * z, r = S3 + z * S4, s = z * x;
+    return (float)((x + s * (S1 + z * S2)) + s * w * r);
+}
+float zig_cosf(float x) {
+    const double pio2 = 1.57079632679489661923;
+    uint32_t ix;
+    memcpy(&ix, &x, 4);
+    const bool sign = (ix >> 31) != 0;
+    ix &= 0x7fffffffu;
+    if (ix <= 0x3f490fdau) return ix < 0x39800000u ? 1.0f : zig_cosdf(x);                  // |x| <= pi/4
+    if (ix <= 0x407b53d1u) {                                                                // |x| <= 5 pi/4
+        if (ix > 0x4016cbe3u) return -zig_cosdf(sign ? x + 2 * pio2 : x - 2 * pio2);
+        return sign ? zig_sindf(x + pio2) : zig_sindf(pio2 - x);
+    }
+    if (ix <= 0x40e231d5u) {                                                                // |x| <= 9 pi/4
+        if (ix > 0x40afeddfu) return zig_cosdf(sign ? x + 4 * pio2 : x - 4 * pio2);
+        return sign ? zig_sindf(-x - 3 * pio2) : zig_sindf(x - 3 * pio2);
+    }
+    return (float)cos((double)x);                                                           // not reached by the window
+}
+}  // namespace
+
+// hannWindowPeriodic -> cosineSumWindowPeriodic (window_fn.zig:22-28,51-68): K=1, alphas {0.5,0.5}, evaluated in f32.
 void host_hann_window_periodic(float *w, size_t n) {
     const float N = (float)n;
     const float two_pi = (float)(2 * 3.14159265358979323846264338327950288419716939937510);
     for (size_t i = 0; i < n; i++) {
         float nf = (float)i;
         float r = 0;
-        r += (1.0f * 0.5f) * (float)cos((double)(((two_pi * 0.0f) * nf) / N));
-        r += (-1.0f * 0.5f) * (float)cos((double)(((two_pi * 1.0f) * nf) / N));
+        r += (1.0f * 0.5f) * zig_cosf(((two_pi * 0.0f) * nf) / N);
+        r += (-1.0f * 0.5f) * zig_cosf(((two_pi * 1.0f) * nf) / N);
         w[i] = r;
     }
 }
@@ -188,7 +223,13 @@ __device__ __forceinline__ void stage_pair(float *dstA, float *dstB, unsigned lo
     bulk_g2s(dstB, pcm + rB * row_stride + fB * hop, kFft * 4u, bar);
 }
 
-template <bool FULL, bool TMA>
+// LEAN (with FULL): spectra wanted (the bins a band reads are also kept in shared memory for the in-order sums).  The last stage and the kiss_fftr split are fused in registers -- a thread
+// takes butterfly kb AND butterfly 256-kb of the last stage, whose eight outputs are exactly the four split pairs
+// (k, 1024-k) for k = kb, kb+256, 256-kb, 512-kb -- and the magnitudes go straight from registers to global memory (a
+// warp writes 32 consecutive bins per store).  Against the general FULL form that is 16 STS.128 + 18 LDS.128 + 70 4-byte
+// shared-memory accesses less per thread and pair (the kernel is bound by the load/store pipe), and no `mags` array, so
+// the staged (TMA) input fits beside six resident CTAs.  Arithmetic per output bin is unchanged.
+template <bool FULL, bool TMA, bool LEAN = false>
 __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, size_t n_rows, size_t row_stride,
                                                  size_t n_frames, size_t hop, const float *__restrict__ window,
                                                  const float2 *__restrict__ tw4, const float2 *__restrict__ stw4,
@@ -197,7 +238,7 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
                                                  size_t band_frame_stride, size_t band_frame_offset,
                                                  float *__restrict__ d_spectra) {
     __shared__ __align__(16) float4 sm[kSlots];
-    __shared__ float mags[2][FULL ? kBins + 3 : 256];
+    __shared__ float mags[2][LEAN ? 256 : (FULL ? kBins + 3 : 256)];   // LEAN: only the bins some band reads, [bin - lo[0]]
     // TMA staging: the next pair's two frames (2 x 8 KB, each contiguous in HBM) are fetched by cp.async.bulk into
     // shared memory while this pair is transformed, so no warp ever waits on an HBM load (with 12 warps per SM the
     // register file leaves nothing to hide that latency with).
@@ -294,7 +335,55 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
 
         // ---------------- pass C: stage m=256 + kiss_fftr split + |X|*norm -----------------
         const float2 half2 = make_float2(0.5f, 0.5f);
-        if (FULL) {
+        if (LEAN) {
+            float *dstA = d_spectra + (rA * n_frames + fA) * (size_t)kBins;
+            float *dstB = d_spectra + (rB * n_frames + fB) * (size_t)kBins;
+            const int blo = bands.n_bands ? bands.lo[0] : 0, bspan = bands.n_bands ? bands.hi[bands.n_bands - 1] - blo : -1;
+            auto put = [&](int bin, float2 m2) {                     // |X| * norm (FFT.zig:167-176) of frames A and B
+                const float mA = sqrtf(m2.x) * norm_factor, mB = sqrtf(m2.y) * norm_factor;
+                dstA[bin] = mA;
+                if (has_b) dstB[bin] = mB;
+                if ((unsigned)(bin - blo) <= (unsigned)bspan) { mags[0][bin - blo] = mA; mags[1][bin - blo] = mB; }   // for the band sums
+            };
+            auto last_stage = [&](int kb, c2 &f0, c2 &f1, c2 &f2, c2 &f3) {   // tmp[kb + 256 j], j = 0..3 (kiss_fft.c:38-84, m = 256)
+                f0 = lds_c2(sm, kb); f1 = lds_c2(sm, kb + 256); f2 = lds_c2(sm, kb + 512); f3 = lds_c2(sm, kb + 768);
+                bfly4(f0, f1, f2, f3, cmul(f1, __ldg(tw4 + kb), nz), cmul(f2, __ldg(tw4 + 2 * kb), nz), cmul(f3, __ldg(tw4 + 3 * kb), nz));
+            };
+            auto split = [&](int k, const c2 &pk, const c2 &qk, bool low) {   // kiss_fftr.c:90-116: p = tmp[k], q = tmp[1024 - k]
+                const c2 f1k{add2(pk.re, qk.re), sub2(pk.im, qk.im)}, f2k{sub2(pk.re, qk.re), add2(pk.im, qk.im)};
+                const c2 w = cmul(f2k, __ldg(stw4 + (k - 1)), nz);
+                const float2 re2 = mul2(sub2(f1k.re, w.re), half2), im2 = mul2(sub2(w.im, f1k.im), half2);
+                put(1024 - k, add2(prod2(re2, re2, nz), prod2(im2, im2, nz)));
+                if (low) {                                               // k == 512: freqdata[512] is written twice, the second wins
+                    const float2 re = mul2(add2(f1k.re, w.re), half2), im = mul2(add2(f1k.im, w.im), half2);
+                    put(k, add2(prod2(re, re, nz), prod2(im, im, nz)));
+                }
+            };
+#pragma unroll 1
+            for (int it = 0; it < 2; it++) {
+                const int kb = t + 1 + 64 * it;                          // 1..127; thread 63's second turn takes 0 and 128
+                c2 a0, a1, a2, a3, b0, b1, b2, b3;
+                if (kb < 128) {
+                    last_stage(kb, a0, a1, a2, a3);
+                    last_stage(256 - kb, b0, b1, b2, b3);
+                    split(kb, a0, b3, true);                             // partner 1024-kb = (256-kb) + 768
+                    split(kb + 256, a1, b2, true);                       // partner 768-kb
+                    split(256 - kb, b0, a3, true);                       // partner 768+kb
+                    split(512 - kb, b1, a2, true);                       // partner 512+kb
+                } else {
+                    last_stage(0, a0, a1, a2, a3);
+                    last_stage(128, b0, b1, b2, b3);
+                    const float2 r0 = add2(a0.re, a0.im), rn = sub2(a0.re, a0.im);     // DC / Nyquist, kiss_fftr.c:84-88
+                    const float2 z = make_float2(0.0f * 0.0f, 0.0f * 0.0f);
+                    put(0, add2(prod2(r0, r0, nz), z));
+                    put(1024, add2(prod2(rn, rn, nz), z));
+                    split(256, a1, a3, true);
+                    split(512, a2, a2, false);
+                    split(128, b0, b3, true);
+                    split(384, b1, b2, true);
+                }
+            }
+        } else if (FULL) {
 #pragma unroll
             for (int it = 0; it < 4; it++) {
                 const int k = t + 64 * it;
@@ -356,7 +445,15 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
         }
         __syncthreads();
         // averageVolumeInBand (PipelineFFT.zig:99-112): in-order f32 SUM of bins lo..hi, for frame A and frame B
-        if (t < 2 * bands.n_bands) {
+        if (LEAN && t < 2 * bands.n_bands) {
+            const int fr = t >= bands.n_bands, bd = t - fr * bands.n_bands, blo = bands.lo[0];
+            if (!fr || has_b) {
+                float v = 0.0f;
+                for (int i = bands.lo[bd]; i <= bands.hi[bd]; i++) v += mags[fr][i - blo];
+                d_band[((size_t)bd * n_rows + (fr ? rB : rA)) * band_frame_stride + band_frame_offset + (fr ? fB : fA)] = v;
+            }
+        }
+        if (!LEAN && t < 2 * bands.n_bands) {
             const int fr = t >= bands.n_bands, bd = t - fr * bands.n_bands;
             if (!fr || has_b) {
                 float v = 0.0f;
@@ -364,7 +461,7 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
                 d_band[((size_t)bd * n_rows + (fr ? rB : rA)) * band_frame_stride + band_frame_offset + (fr ? fB : fA)] = v;
             }
         }
-        if (FULL && d_spectra != nullptr) {
+        if (FULL && !LEAN && d_spectra != nullptr) {
             float *dstA = d_spectra + (rA * n_frames + fA) * (size_t)kBins;
             for (int k = t; k < kBins; k += 64) dstA[k] = mags[0][k];
             if (has_b) {
@@ -378,14 +475,14 @@ __global__ void __launch_bounds__(64) k_stft2048(const float *__restrict__ pcm, 
 }
 
 namespace {
-struct StftGrid { int occ[2][2] = {{0, 0}, {0, 0}}; int sms = 0; bool ready = false; };
+struct StftGrid { int occ[2][2] = {{0, 0}, {0, 0}}; int occ_lean[2] = {0, 0}; int sms = 0; bool ready = false; };
 StftGrid g_grid[64];
 
-template <bool FULL, bool TMA>
+template <bool FULL, bool TMA, bool LEAN = false>
 int stft_occupancy(int *occ) {
     // the staged variant needs the whole shared-memory carve-out to keep six CTAs (12 warps) per SM
-    FVAD_CUDA_TRY(cudaFuncSetAttribute(k_stft2048<FULL, TMA>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-    FVAD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_stft2048<FULL, TMA>, 64, 0));
+    FVAD_CUDA_TRY(cudaFuncSetAttribute(k_stft2048<FULL, TMA, LEAN>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    FVAD_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, k_stft2048<FULL, TMA, LEAN>, 64, 0));
     if (*occ < 1) *occ = 1;
     return FVAD_OK;
 }
@@ -400,6 +497,7 @@ int stft_launch(const StftTables &tb, const float *d_pcm, size_t n_rows, size_t 
         return set_error(FVAD_EINVALID_ARGUMENT, "stft: pcm must be 8-byte aligned with even strides");
     // cp.async.bulk wants 16-byte aligned sources; anything else takes the plain-load variant
     bool tma = !(reinterpret_cast<uintptr_t>(d_pcm) & 15) && !(row_stride & 3) && !(hop & 3);
+    if (const char *e = debug_knob("stft_tma")) tma = tma && atoi(e) != 0;
     // The pruned variant computes only the bins lo[0]..hi[last]; it needs every band inside 1..255 and the first /
     // last band to carry the extremes (true for the pipeline's single speech band).  Otherwise: all 1025 bins.
     bool full = d_spectra != nullptr || bands.n_bands == 0;
@@ -420,17 +518,29 @@ int stft_launch(const StftTables &tb, const float *d_pcm, size_t n_rows, size_t 
             if ((rc = stft_occupancy<false, false>(&g.occ[0][0])) != FVAD_OK) return rc;
             if ((rc = stft_occupancy<false, true>(&g.occ[0][1])) != FVAD_OK) return rc;
             if ((rc = stft_occupancy<true, false>(&g.occ[1][0])) != FVAD_OK) return rc;
+            if ((rc = stft_occupancy<true, false, true>(&g.occ_lean[0])) != FVAD_OK) return rc;
+            if ((rc = stft_occupancy<true, true, true>(&g.occ_lean[1])) != FVAD_OK) return rc;
             g.ready = true;
         }
     }
-    if (full) tma = false;                    // write-dominated; the staging buffer would cost it a resident CTA
-    size_t grid = (size_t)g.sms * g.occ[full][tma];
+    // spectra wanted (FFT.fft, Spectrogram.compute, fvad_stft_batch(d_spectra)) and the bands, if any, ordered and within 256 bins
+    bool lean = full && d_spectra != nullptr;
+    for (int i = 0; i < bands.n_bands && lean; i++)
+        lean = bands.hi[i] >= bands.lo[i] && bands.lo[i] >= bands.lo[0] && bands.hi[i] <= bands.hi[bands.n_bands - 1] &&
+               bands.hi[bands.n_bands - 1] - bands.lo[0] < 256;
+    if (full && !lean) tma = false;           // the general form's `mags` array plus the staging buffer would cost a resident CTA
+    size_t grid = (size_t)g.sms * (lean ? g.occ_lean[tma] : g.occ[full][tma]);
     if (grid > pairs) grid = pairs;
 #define FVAD_STFT_GO(F, T)                                                                                              \
     FVAD_LAUNCH_NAMED("k_stft2048<" #F ">", (k_stft2048<F, T>), (unsigned)grid, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win, tb.d_tw4, \
                 tb.d_stw4, tb.d_twB4, tb.twA, norm, bands, d_band, band_frame_stride, band_frame_offset, d_spectra)
-    if (full) FVAD_STFT_GO(true, false);
-    else      { if (tma) FVAD_STFT_GO(false, true); else FVAD_STFT_GO(false, false); }
+#define FVAD_STFT_LEAN(T)                                                                                               \
+    FVAD_LAUNCH_NAMED("k_stft2048<true>", (k_stft2048<true, T, true>), (unsigned)grid, 64, 0, stream, d_pcm, n_rows, row_stride, n_frames, hop, win, tb.d_tw4, \
+                tb.d_stw4, tb.d_twB4, tb.twA, norm, bands, d_band, band_frame_stride, band_frame_offset, d_spectra)
+    if (lean)      { if (tma) FVAD_STFT_LEAN(true); else FVAD_STFT_LEAN(false); }
+    else if (full) FVAD_STFT_GO(true, false);
+    else           { if (tma) FVAD_STFT_GO(false, true); else FVAD_STFT_GO(false, false); }
+#undef FVAD_STFT_LEAN
 #undef FVAD_STFT_GO
     FVAD_CUDA_TRY(cudaGetLastError());
     return FVAD_OK;

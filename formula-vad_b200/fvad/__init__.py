@@ -47,6 +47,22 @@ _fp = C.POINTER(C.c_float)
 _lib = None
 
 
+class Clip(C.Structure):
+    """fvad_clip = the AudioBuffer Callbacks.on_recording receives (src/AudioPipeline.zig:15-18, Recorder.zig:121-146)."""
+    _fields_ = [("global_start_frame_number", C.c_uint64), ("length", C.c_size_t), ("sample_rate", C.c_size_t),
+                ("channel", C.c_size_t), ("duration_seconds", C.c_float), ("lost", C.c_int32), ("pcm", C.POINTER(C.c_float))]
+
+
+ON_RECORDING = C.CFUNCTYPE(None, C.c_void_p, C.c_size_t, C.POINTER(Clip))
+
+
+def _clip_dict(c):
+    pcm = None if c.lost or not c.pcm else np.ctypeslib.as_array(c.pcm, shape=(c.length,)).copy()
+    return dict(start=int(c.global_start_frame_number), end=int(c.global_start_frame_number + c.length), length=int(c.length),
+                sample_rate=int(c.sample_rate), channel=int(c.channel), duration_seconds=float(c.duration_seconds),
+                lost=bool(c.lost), pcm=pcm)
+
+
 class SpectrogramInfo(C.Structure):
     _fields_ = [("height", C.c_size_t), ("width", C.c_size_t), ("bin_width", C.c_float), ("nyquist_freq", C.c_float),
                 ("length_sec", C.c_double)]
@@ -88,6 +104,8 @@ def lib():
         "fvad_batch_events": (C.c_int, [vp, sz, C.POINTER(vp), szp]),
         "fvad_batch_counts": (C.c_int, [vp, u64p, u64p]),
         "fvad_batch_cuda_stream": (vp, [vp]),
+        "fvad_batch_set_recording": (C.c_int, [vp, sz, ON_RECORDING, vp]),
+        "fvad_batch_clips": (C.c_int, [vp, sz, C.POINTER(C.POINTER(Clip)), szp]),
         "fvad_batch_sweep": (C.c_int, [vp, C.POINTER(VadMachineConfig), sz, sz, vp, vp, C.c_int]),
         "fvad_batch_feature_count": (C.c_int, [vp, szp]),
         "fvad_batch_features": (C.c_int, [vp, sz, vp, sz, szp]),
@@ -256,6 +274,24 @@ class PipelineBatch:
 
     def reset(self):
         _check(lib().fvad_batch_reset(self._h))
+
+    def set_recording(self, history_samples=0, on_recording=None):
+        """Recorder / Callbacks.on_recording through the C ABI (fvad_batch_set_recording): before the first push.
+        history_samples = 0 keeps every pushed sample in HBM (lossless); else a ring of that many samples per channel.
+        on_recording(stream, clip_dict) is called from inside push / sync, once per clip."""
+        if on_recording is None:
+            self._rec_cb = C.cast(None, ON_RECORDING)
+        else:
+            def tramp(_ctx, stream, clip):
+                on_recording(int(stream), _clip_dict(clip.contents))
+            self._rec_cb = ON_RECORDING(tramp)                  # kept alive with the batch
+        _check(lib().fvad_batch_set_recording(self._h, history_samples, self._rec_cb, None))
+
+    def clips(self, stream):
+        """fvad_batch_clips: the clips completed since the previous call for this stream, as dicts (pcm copied)."""
+        p, n = C.POINTER(Clip)(), C.c_size_t()
+        _check(lib().fvad_batch_clips(self._h, stream, C.byref(p), C.byref(n)))
+        return [_clip_dict(p[i]) for i in range(n.value)]
 
     def feature_count(self):
         n = C.c_size_t()

@@ -163,6 +163,35 @@ int  fvad_batch_reset(fvad_batch *b);
 int  fvad_batch_segments(fvad_batch *b, size_t stream, int machine_idx, const fvad_segment **segs, size_t *n);
 /* Recording-state results of the main machine, in order (drives the Recorder). */
 int  fvad_batch_events(fvad_batch *b, size_t stream, const fvad_capture_event **events, size_t *n);
+/* ---- Recorder: Callbacks.on_recording (src/AudioPipeline.zig:15-18,134-195; src/AudioPipeline/Recorder.zig:52-146) ----
+ * Every started -> completed pair of the main machine yields one clip: the ORIGINAL samples
+ * [start - 2 s (clamped at 0), end + 2 s) of the quietest channel (Recorder.findBestChannel: smallest f32 in-order RMS over
+ * the clip, first channel wins ties), as the AudioBuffer the reference hands to on_recording
+ * (Recorder.segmentToAudioBuffer, Recorder.zig:121-146).  An aborted recording yields nothing.
+ * The reference copies the samples out of its ring while it records; here the decisions lag the input by the depth of
+ * the tile pipeline, so the batch keeps a HISTORY of the original PCM in HBM (every push is copied into it on the copy
+ * stream) and cuts the clips out of it with a gather kernel when the completing event has been seen and the stream has
+ * reached the clip's end sample -- inside fvad_batch_sync (and wherever a push drains results).  history_samples = 0 keeps
+ * everything pushed (the buffer doubles as needed: lossless, costs the input's size in HBM); otherwise a ring of that many
+ * samples per channel: a clip whose start has been overwritten by then is delivered with lost = 1 and pcm = NULL (the
+ * reference fails with IndexOutOfBounds when ITS 10-second ring is too short, MultiRingBuffer.zig:159-169).
+ * Set before the first push.  on_recording (may be NULL) is called on the calling thread from inside push / sync, once per
+ * clip in time order per stream; the clip is borrowed for the duration of the call (as AudioPipeline.zig:182-188 frees the
+ * AudioBuffer right after the callback).  Without a callback, or in addition to it, fvad_batch_clips hands out the clips
+ * completed since its previous call for that stream (owned by the handle until the next call for that stream). */
+typedef struct fvad_clip {
+    uint64_t global_start_frame_number;   /* AudioBuffer.global_start_frame_number = Recorder.startIndex */
+    size_t   length;                      /* samples */
+    size_t   sample_rate;
+    size_t   channel;                     /* the channel findBestChannel chose (the AudioBuffer itself is mono) */
+    float    duration_seconds;            /* (f32)length / (f32)sample_rate */
+    int32_t  lost;                        /* 1: the history ring no longer held the start of the clip */
+    const float *pcm;                     /* length samples of channel `channel`, or NULL when lost */
+} fvad_clip;
+typedef void (*fvad_on_recording_fn)(void *ctx, size_t stream, const fvad_clip *recording);
+int  fvad_batch_set_recording(fvad_batch *b, size_t history_samples, fvad_on_recording_fn on_recording, void *ctx);
+int  fvad_batch_clips(fvad_batch *b, size_t stream, const fvad_clip **clips, size_t *n);
+
 /* Total samples written / consumed by the VAD so far (multi_ring_buffer.total_write_count,
  * VAD.pipeline_read_count). */
 int  fvad_batch_counts(fvad_batch *b, uint64_t *total_write_count, uint64_t *pipeline_read_count);

@@ -26,8 +26,10 @@ void orc_default_vadm_config(orc_vadm_config *c) {   /* VADMachine.zig:18-39 */
 
 /* ---- window_fn.zig -------------------------------------------------------- */
 /* hannWindowPeriodic -> cosineSumWindowPeriodic (window_fn.zig:22-28,51-68), K=1,
- * alphas {0.5,0.5}, all f32.  `@cos` on f32 is Zig's cosf; we use the correctly
- * rounded value (float)cos((double)x), the best available stand-in. */
+ * alphas {0.5,0.5}, all f32.  `@cos` on f32 is Zig's compiler-rt cosf, a port of musl's:
+ * restated in musl_cosf.c (one entry of the 2048-entry table differs from the correctly
+ * rounded cosine; tests/test_oracle.py::test_hann_window_cosf_pin). */
+float orc_musl_cosf(float x);
 void orc_hann_window_periodic(float *w, size_t n) {
     const float N = (float)n;
     const float two_pi = (float)(2 * 3.14159265358979323846264338327950288419716939937510);
@@ -35,9 +37,9 @@ void orc_hann_window_periodic(float *w, size_t n) {
         float nf = (float)i;
         float r = 0;
         /* k = 0: pow(-1,0) * a0 * cos(0) */
-        r += (1.0f * 0.5f) * (float)cos((double)(((two_pi * 0.0f) * nf) / N));
+        r += (1.0f * 0.5f) * orc_musl_cosf(((two_pi * 0.0f) * nf) / N);
         /* k = 1: pow(-1,1) * a1 * cos(2 pi n / N) */
-        r += (-1.0f * 0.5f) * (float)cos((double)(((two_pi * 1.0f) * nf) / N));
+        r += (-1.0f * 0.5f) * orc_musl_cosf(((two_pi * 1.0f) * nf) / N);
         w[i] = r;
     }
 }

@@ -9,7 +9,7 @@ LIB="${1:-$(dirname "$0")/../formula-vad_b200/libfvad_cuda.so}"
 SASS="$(mktemp)"; trap 'rm -f "$SASS"' EXIT
 cuobjdump -sass "$LIB" > "$SASS"
 rc=0
-for v in ILb0ELb0 ILb0ELb1 ILb1ELb0; do
+for v in ILb0ELb0ELb0 ILb0ELb1ELb0 ILb1ELb0ELb0 ILb1ELb0ELb1 ILb1ELb1ELb1; do
     body="$(awk -v v="$v" '$0 ~ "Function : .*k_stft2048" v {p=1; next} p && /Function : / {p=0} p' "$SASS")"
     [ -n "$body" ] || { echo "check_sass: k_stft2048<$v> not found"; rc=1; continue; }
     addends="$(grep FFMA2 <<<"$body" | sed 's/.*FFMA2 [^,]*,[^,]*,[^,]*, *\([A-Z0-9]*\).*/\1/' | sort -u)"
@@ -19,7 +19,9 @@ for v in ILb0ELb0 ILb0ELb1 ILb1ELb0; do
     if [ "$n_vec" -gt 1 ] || [ "$n_uni" -gt 1 ]; then echo "  FAIL: contracted FFMA2 suspected"; rc=1; fi
     if [ "$n_fadd2" -lt 100 ]; then echo "  FAIL: packed f32x2 arithmetic missing"; rc=1; fi
 done
-n_tma="$(awk '$0 ~ "Function : .*k_stft2048ILb0ELb1" {p=1; next} p && /Function : / {p=0} p' "$SASS" | grep -c UBLKCP || true)"
-echo "k_stft2048<ILb0ELb1>: UBLKCP=$n_tma"
-[ "$n_tma" -ge 2 ] || { echo "  FAIL: bulk copies missing"; rc=1; }
+for v in ILb0ELb1ELb0 ILb1ELb1ELb1; do
+    n_tma="$(awk -v v="$v" '$0 ~ "Function : .*k_stft2048" v {p=1; next} p && /Function : / {p=0} p' "$SASS" | grep -c UBLKCP || true)"
+    echo "k_stft2048<$v>: UBLKCP=$n_tma"
+    [ "$n_tma" -ge 2 ] || { echo "  FAIL: bulk copies missing"; rc=1; }
+done
 exit $rc

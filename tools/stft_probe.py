@@ -3,6 +3,9 @@ import sys, os
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "formula-vad_b200"))
 import torch, fvad
+for k, v in os.environ.items():
+    if k.startswith("FVADK_"):
+        fvad.debug_set(k[6:].lower(), v)
 rows = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 frames = int(sys.argv[2]) if len(sys.argv) > 2 else 1406
 xs = torch.empty(rows, frames * 2048, dtype=torch.float32, device="cuda")
