@@ -443,7 +443,9 @@ def b200_arm(args):
     sweep = None
     if not args.no_sweep and rank == 0:
         try:
-            step_device()                                          # the features of one full pass of this rank's streams
+            b.reset()                                              # the features of one full pass of this rank's streams
+            b.push_device(x.data_ptr(), n, n, n)                   # (no collective here: the other ranks are not in this leg)
+            b.sync()
             sweep = sweep_leg(args, fvad, b, S, secs, first_stream, torch, dev, do_cpu=not args.no_cpu and world == 1)
         except Exception as e:                                     # a leg must not cost the line
             errors["sweep"] = repr(e)

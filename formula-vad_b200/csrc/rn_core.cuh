@@ -24,6 +24,16 @@
 namespace fvad {
 namespace rn {
 
+// Ly = log10(1e-2 + Ex) of compute_frame_features (denoise.c:349): a float, widened to double by the double constant, the
+// double log10, rounded to float.  libdevice's log10 and glibc's are both within one ulp of the true value in DOUBLE but
+// neither is correctly rounded, so the two can differ in the last double bit; that changes the float only when the value
+// lies within ~2^-28 of a float rounding boundary.  Parity here is EMPIRICAL: tests/test_gpu_denoiser.py sweeps this very
+// function over 10^8 inputs against the host's log10 (fvad_debug_log10) and every whole-stream test goes through it.
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline float log10_ex(float ex) { return (float)log10(1e-2 + ex); }
+
 constexpr int kFrame = 480, kWin = 960, kFreq = 481, kNB = 22;
 constexpr int kPBuf = 1728, kPHist = kPBuf - kFrame;      // PITCH_BUF_SIZE, denoise.c:52-55
 constexpr int kPMax = 768, kPMin = 60;
@@ -305,7 +315,7 @@ RN_HD void analysis_warp(const Tables &t, const float *hpb, int q, cpx *Xq, floa
         if (lane < kNB) misc[lane] = band_chain_pre(t, be, lane);
     RN_END
     RN_PHASE   // the logarithms are independent per band: 22 lanes, not one (only the follow/logMax scan is sequential)
-        if (lane < kNB) { Exq[lane] = misc[lane]; misc[64 + lane] = (float)log10(1e-2 + misc[lane]); }
+        if (lane < kNB) { Exq[lane] = misc[lane]; misc[64 + lane] = log10_ex(misc[lane]); }
     RN_END
     RN_PHASE
         if (lane == 0) {

@@ -1370,6 +1370,30 @@ int rnnoise_batch_process(RnnoiseBatch *r, const float *d_in, size_t in_stride, 
 }  // namespace fvad
 
 // ------------------------------------------------------------------------------------------
+// test aid: the device's Ly = log10(1e-2 + Ex) (rn_core.cuh log10_ex) on an array
+// ------------------------------------------------------------------------------------------
+namespace fvad {
+__global__ void k_debug_log10(const float *__restrict__ in, float *__restrict__ out, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) out[i] = rn::log10_ex(in[i]);
+}
+}  // namespace fvad
+extern "C" int fvad_debug_log10(const float *ex, float *out, size_t n) {
+    if ((!ex || !out) && n) return fvad::set_error(FVAD_EINVALID_ARGUMENT, "fvad_debug_log10: null argument");
+    if (!n) return FVAD_OK;
+    float *d_in = nullptr, *d_out = nullptr;
+    cudaError_t e = cudaMalloc(&d_in, n * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, n * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpy(d_in, ex, n * sizeof(float), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        FVAD_LAUNCH(fvad::k_debug_log10, 1184, 256, 0, 0, d_in, d_out, n);
+        e = cudaMemcpy(out, d_out, n * sizeof(float), cudaMemcpyDeviceToHost);
+    }
+    cudaFree(d_in); cudaFree(d_out);
+    if (e != cudaSuccess) return fvad::set_error(FVAD_ECUDA, "fvad_debug_log10: %s (no CPU fallback exists)", cudaGetErrorString(e));
+    return FVAD_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // C ABI: Denoiser.zig drop-ins
 // ------------------------------------------------------------------------------------------
 using namespace fvad;

@@ -92,6 +92,7 @@ def lib():
         "fvad_last_error": (C.c_char_p, []), "fvad_status_name": (C.c_char_p, [C.c_int]),
         "fvad_version": (C.c_char_p, []), "fvad_device_count": (C.c_int, []), "fvad_launch_count": (C.c_uint64, []),
         "fvad_debug_set": (C.c_int, [C.c_char_p, C.c_char_p]),
+        "fvad_debug_log10": (C.c_int, [_fp, _fp, sz]),
         "fvad_profile_enable": (None, [C.c_int]), "fvad_profile_report": (C.c_int, [C.c_char_p, sz]),
         "fvad_default_vad_machine_config": (None, [C.POINTER(VadMachineConfig)]),
         "fvad_default_config": (None, [C.POINTER(Config), sz, sz]),
@@ -175,6 +176,14 @@ def debug_set(key=None, value=None):
     """fvad_debug_set: measurement / test knobs (kernel shapes, tile length, ...).  value None clears the key, key None
     clears all.  The library reads no environment variables."""
     _check(lib().fvad_debug_set(None if key is None else str(key).encode(), None if value is None else str(value).encode()))
+
+
+def debug_log10(ex):
+    """The device's (float)log10(1e-2 + ex) of rnnoise's feature extraction, elementwise (fvad_debug_log10)."""
+    ex = np.ascontiguousarray(ex, np.float32)
+    out = np.empty_like(ex)
+    _check(lib().fvad_debug_log10(_f(ex), _f(out), ex.size))
+    return out
 
 
 def launch_count():

@@ -123,13 +123,16 @@ class Instance:
         self.reference = ev.sort_by_start(ev.read_parse_audacity_segments(os.path.normpath(os.path.join(base_path, j["ref_path"]))))
         self.vad_segments = None
         self.events = None
+        self.clips = None
 
     def recordings(self):
         """Recorder / on_recording (src/AudioPipeline/Recorder.zig:52-146, src/AudioPipeline.zig:134-195):
         every started -> completed pair of the main machine yields the ORIGINAL samples [start, end) of the quietest
-        channel (Recorder.findBestChannel: smallest f32 RMS, first wins ties).  A recording is delivered only once the
-        stream has reached its end sample (AudioPipeline.maybeRecordBuffer), so one still waiting at end of stream is
-        dropped, as in the reference.  Yields dicts {start, end, channel, pcm, duration_seconds}."""
+        channel.  The clips are cut ON THE DEVICE out of the PCM history the batch keeps (fvad_batch_set_recording /
+        fvad_batch_clips); this method only drops what a zero-padded tail of a ragged plan produced: a clip is kept iff
+        its completing event was decided inside the real stream and the stream reaches its end sample
+        (AudioPipeline.maybeRecordBuffer), as in the reference.  Yields dicts {start, end, channel, pcm, duration_seconds}."""
+        by_range = {(c["start"], c["end"]): c for c in (self.clips or [])}
         start = None
         for e in self.events:
             st = int(e["recording_state"])
@@ -139,15 +142,9 @@ class Instance:
                 start = None
             elif st == REC_COMPLETED and start is not None:
                 end = int(e["sample_number"])
-                if end <= self.audio.n_frames:
-                    pcm = self.audio.read(start, end - start)
-                    vols = [rms_volume(ch) for ch in pcm]
-                    best, best_vol = 0, np.float32(9999)
-                    for c, v in enumerate(vols):
-                        if v < best_vol:
-                            best, best_vol = c, v
-                    yield dict(start=start, end=end, channel=best, pcm=pcm[best],
-                               duration_seconds=float(np.float32(end - start) / np.float32(self.audio.sample_rate)))
+                c = by_range.get((start, end))
+                if end <= self.audio.n_frames and c is not None and not c["lost"]:
+                    yield dict(start=start, end=end, channel=c["channel"], pcm=c["pcm"], duration_seconds=c["duration_seconds"])
                 start = None
 
 
@@ -183,6 +180,7 @@ class Simulation:
             n_max = max(i.audio.n_frames for i in insts)
             with PipelineBatch(len(insts), sample_rate=rate, n_channels=n_ch, fft_size=self.fft_size, use_denoiser=self.use_denoiser,
                                vad_machine_config=self.machine_config, alt_vad_machine_configs=self.alt_configs, device=device) as b:
+                b.set_recording(0)                  # Callbacks.on_recording: the library keeps the PCM and cuts the clips
                 chunk = int(chunk_seconds * rate)
                 for off in range(0, n_max, chunk):
                     m = min(chunk, n_max - off)
@@ -196,6 +194,7 @@ class Simulation:
                     events = b.events(s)
                     inst.vad_segments = keep_decided_inside(b.segments(s, 0), events, inst.audio.n_frames, self.fft_size)
                     inst.events = events[events["at_index"] < frames_decided(inst.audio.n_frames, self.fft_size) * self.fft_size]
+                    inst.clips = b.clips(s)
 
     # -- statistics, Audacity text, report (simulator.zig:108-139,230-256) ------------------------------------------
     def results(self, device=-1):

@@ -66,6 +66,10 @@ int  fvad_profile_report(char *buf, size_t cap);
  * take effect for handles created afterwards.  value NULL clears the key; key NULL clears all.  This setter is the ONLY
  * way to change them: the library does not read the process environment.  No counterpart in the reference. */
 int  fvad_debug_set(const char *key, const char *value);
+/* Test aid: out[i] = (float)log10(1e-2 + ex[i]) as the DEVICE evaluates it inside rnnoise's feature extraction
+ * (lib/rnnoise/src/denoise.c:349); host arrays.  Lets a test sweep the one libm call of the path whose device and host
+ * implementations are not both correctly rounded. */
+int  fvad_debug_log10(const float *ex, float *out, size_t n);
 
 /* ---- configuration PODs ---------------------------------------------------------- */
 /* VADMachine.Config, src/AudioPipeline/VADMachine.zig:18-39 (same fields, same defaults

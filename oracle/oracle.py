@@ -274,6 +274,16 @@ def have_reference_fast():
 _synth = None
 
 
+def log10_ex(ex):
+    """(float)log10(1e-2 + ex) with the host libm, as lib/rnnoise/src/denoise.c:349 evaluates it."""
+    synth(0, 0, 0, 0)                                   # loads the helper library
+    ex = np.ascontiguousarray(ex, np.float32)
+    out = np.empty_like(ex)
+    _synth.orc_log10_ex.argtypes = [_fp, _fp, C.c_size_t]
+    _synth.orc_log10_ex(_f(ex), _f(out), ex.size)
+    return out
+
+
 def synth(seed, stream_id, first_sample, n):
     """The seeded input generator (include/fvad_synth_core.h) on the host, without libfvad_cuda.so."""
     global _synth

@@ -24,3 +24,9 @@ int orc_synth_fill(float *dst, uint64_t seed, uint64_t stream_id, uint64_t first
     for (size_t i = 0; i < n; i++) dst[i] = fvad_synth_sample(t, seed, stream_id, first_sample + i);
     return 0;
 }
+
+/* Ly = log10(1e-2 + Ex) as the reference's C evaluates it (lib/rnnoise/src/denoise.c:349): the HOST libm's double log10.
+ * Checker for tests/test_gpu_denoiser.py::test_device_log10_equals_host_log10_on_a_sweep. */
+void orc_log10_ex(const float *ex, float *out, size_t n) {
+    for (size_t i = 0; i < n; i++) out[i] = (float)log10(1e-2 + ex[i]);
+}
