@@ -62,7 +62,7 @@ struct fvad_batch {
     float *d_den = nullptr;        // [rows][den_cap]: carried denoised samples + the tile's output
     size_t den_cap = 0, den_carry = 0;
     float *d_den_carry = nullptr;  // [rows][fft_size]
-    static constexpr int kHist480 = 8;
+    static constexpr int kHist480 = 16;         // 480-sample frames of history in front of a tile: an STFT frame reaches fft_size/480 + 2 back
     float *d_ratio480 = nullptr, *d_vad480 = nullptr;   // [S][kHist480 + tile_frames]
     size_t stride480 = 0;
     long long base480 = 0;         // global 480-frame number of slot kHist480
@@ -204,9 +204,14 @@ extern "C" int fvad_batch_create(const fvad_config *cfg, size_t n_streams, int d
     const size_t n_fft = cfg->vad_config.fft_size;
     if (n_fft == 0 || (n_fft % 2) != 0)                                        // FFT.zig:29-31
         return set_error(FVAD_EINVALID_FFT_SIZE, "fft_size %zu must be even and non-zero", n_fft);
-    if (n_fft != (size_t)kFft)
-        return set_error(FVAD_EUNSUPPORTED, "this build's STFT kernel covers fft_size 2048 only (got %zu)", n_fft);
+    if (n_fft != (size_t)kFft) {                                               // any other size: the generic plan (stft_generic.cu)
+        const int rc_fft = stft_generic_supported(n_fft);
+        if (rc_fft != FVAD_OK) return rc_fft;
+    }
     if (cfg->n_channels > 64) return set_error(FVAD_EUNSUPPORTED, "more than 64 channels");
+    if (cfg->vad_config.use_denoiser && n_fft / kRnFrame + 3 > (size_t)fvad_batch::kHist480)
+        return set_error(FVAD_EUNSUPPORTED, "fft_size %zu with the denoiser: the re-framing history covers sizes up to %d", n_fft,
+                         (fvad_batch::kHist480 - 3) * kRnFrame);
     if (device < 0) {
         cudaError_t e = cudaGetDevice(&device);
         if (e != cudaSuccess) return set_error(FVAD_ECUDA, "cudaGetDevice: %s (no CPU fallback exists)", cudaGetErrorString(e));
@@ -385,9 +390,10 @@ static int trace_tile(fvad_batch *b, size_t F, size_t J, size_t den_before) {
         }
     }
     if ((b->trace_flags & FVAD_TRACE_SPECTRA) && J) {
-        std::vector<float> tmp(J * kBins);
+        const size_t bins = (size_t)b->fft_size / 2 + 1;
+        std::vector<float> tmp(J * bins);
         for (size_t r = 0; r < b->rows; r++) {
-            FVAD_CUDA_TRY(cudaMemcpy(tmp.data(), b->d_spectra + r * J * kBins, sizeof(float) * J * kBins, cudaMemcpyDeviceToHost));
+            FVAD_CUDA_TRY(cudaMemcpy(tmp.data(), b->d_spectra + r * J * bins, sizeof(float) * J * bins, cudaMemcpyDeviceToHost));
             b->tr_spectra[r].insert(b->tr_spectra[r].end(), tmp.begin(), tmp.end());
         }
     }
@@ -408,6 +414,15 @@ static int trace_tile(fvad_batch *b, size_t F, size_t J, size_t den_before) {
         }
     }
     return FVAD_OK;
+}
+
+// PipelineFFT.fft for the batch's fft_size: the specialised kernel for 2048, KissFFT's generic plan otherwise
+static int batch_stft(fvad_batch *b, const float *in, size_t in_stride, size_t n_frames, float *d_band, float *spec, cudaStream_t st) {
+    if (b->fft_size == kFft)
+        return stft_launch(*b->tabs, in, b->rows, in_stride, n_frames, b->fft_size, b->bands, d_band, b->max_stft, 0, spec, nullptr, 0.f,
+                           b->device, st);
+    return stft_generic_launch(b->device, (size_t)b->fft_size, in, b->rows, in_stride, n_frames, b->fft_size, b->bands, d_band, b->max_stft,
+                               0, spec, nullptr, 0.f, st);
 }
 
 static float *band_buf(fvad_batch *b, int par) { return b->d_band + (size_t)par * b->bands.n_bands * b->rows * b->max_stft; }
@@ -471,8 +486,7 @@ static int process_tile(fvad_batch *b, const float *in, size_t in_stride, size_t
         if (!b->use_denoiser) {
             J = F;
             FVAD_TRY(rms_ratio_launch(in, in_stride, b->S, (int)b->C, F, b->fft_size, b->d_ratio_stft, b->max_stft, 0, sD));
-            FVAD_TRY(stft_launch(*b->tabs, in, b->rows, in_stride, F, b->fft_size, b->bands, b->d_band, b->max_stft, 0,
-                                 spec, nullptr, 0.f, b->device, sD));
+            FVAD_TRY(batch_stft(b, in, in_stride, F, b->d_band, spec, sD));
             FVAD_TRY(run_machines(b, 0, false, b->read_count, J, sD));
         } else {
             // ---- wavefront: stage X of this tile follows stage X of the previous tile (stream order) and
@@ -510,8 +524,7 @@ static int process_tile(fvad_batch *b, const float *in, size_t in_stride, size_t
                 FVAD_CUDA_TRY(cudaStreamWaitEvent(sD, b->evE[par], 0));        // the machines of two tiles ago are done with them
                 FVAD_TRY(reframe_launch(b->d_ratio480, b->d_vad480, b->stride480, b->base480, fvad_batch::kHist480, b->S,
                                         b->stft_done, J, b->fft_size, ratio_buf(b, par), vad_buf(b, par), b->max_stft, sD));
-                FVAD_TRY(stft_launch(*b->tabs, b->d_den, b->rows, b->den_cap, J, b->fft_size, b->bands, band_buf(b, par), b->max_stft, 0,
-                                     spec, nullptr, 0.f, b->device, sD));
+                FVAD_TRY(batch_stft(b, b->d_den, b->den_cap, J, band_buf(b, par), spec, sD));
                 FVAD_CUDA_TRY(cudaEventRecord(b->evS[par], sD));
                 FVAD_CUDA_TRY(cudaStreamWaitEvent(b->sE, b->evS[par], 0));
                 FVAD_TRY(run_machines(b, par, true, b->stft_done * (unsigned long long)b->fft_size, J, b->sE));
@@ -556,7 +569,7 @@ static int join_machines(fvad_batch *b) {
 
 static int ensure_trace_buffers(fvad_batch *b) {
     if ((b->trace_flags & FVAD_TRACE_RECORDS) && !b->d_trace) FVAD_TRY(dmalloc(&b->d_trace, b->S * b->max_stft));
-    if ((b->trace_flags & FVAD_TRACE_SPECTRA) && !b->d_spectra) FVAD_TRY(dmalloc(&b->d_spectra, b->rows * b->max_stft * (size_t)kBins));
+    if ((b->trace_flags & FVAD_TRACE_SPECTRA) && !b->d_spectra) FVAD_TRY(dmalloc(&b->d_spectra, b->rows * b->max_stft * ((size_t)b->fft_size / 2 + 1)));
     return FVAD_OK;
 }
 

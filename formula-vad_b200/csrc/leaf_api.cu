@@ -49,14 +49,14 @@ extern "C" int fvad_fft_create(size_t n_fft, size_t sample_rate, fvad_fft **out)
     if (!out) return set_error(FVAD_EINVALID_ARGUMENT, "null out");
     *out = nullptr;
     if (n_fft == 0 || (n_fft % 2) != 0) return set_error(FVAD_EINVALID_FFT_SIZE, "n_fft %zu must be even and non-zero", n_fft);   // FFT.zig:29-31
-    if (n_fft != (size_t)kFft) return set_error(FVAD_EUNSUPPORTED, "this build's FFT kernel covers n_fft 2048 only (got %zu)", n_fft);
+    if (n_fft != (size_t)kFft) FVAD_TRY(stft_generic_supported(n_fft));     // KissFFT's generic plan (stft_generic.cu)
     int device = 0;
     cudaError_t e = cudaGetDevice(&device);
     if (e != cudaSuccess) return set_error(FVAD_ECUDA, "cudaGetDevice: %s (no CPU fallback exists)", cudaGetErrorString(e));
     fvad_fft *f = new (std::nothrow) fvad_fft();
     if (!f) return set_error(FVAD_EOUT_OF_MEMORY, "host allocation failed");
     f->n_fft = n_fft; f->sample_rate = sample_rate; f->device = device;
-    int rc = stft_tables_get(device, &f->tabs);
+    int rc = n_fft == (size_t)kFft ? stft_tables_get(device, &f->tabs) : FVAD_OK;
     if (rc != FVAD_OK) { delete f; return rc; }
     if (cudaMalloc(&f->d_in, sizeof(float) * n_fft) != cudaSuccess || cudaMalloc(&f->d_window, sizeof(float) * n_fft) != cudaSuccess ||
         cudaMalloc(&f->d_out, sizeof(float) * (n_fft / 2 + 1)) != cudaSuccess || cudaMalloc(&f->d_band, sizeof(float) * kMaxBands) != cudaSuccess) {
@@ -107,7 +107,10 @@ extern "C" int fvad_fft_run(fvad_fft *f, const float *first, size_t n_first, con
     FVAD_CUDA_TRY(cudaMemcpyAsync(f->d_in, f->h_in.data(), sizeof(float) * f->n_fft, cudaMemcpyHostToDevice, 0));
     FVAD_CUDA_TRY(cudaMemcpyAsync(f->d_window, window, sizeof(float) * f->n_fft, cudaMemcpyHostToDevice, 0));
     StftBands b{}; b.n_bands = 0;
-    FVAD_TRY(stft_launch(*f->tabs, f->d_in, 1, f->n_fft, 1, f->n_fft, b, f->d_band, 1, 0, f->d_out, f->d_window, norm, f->device, 0));
+    if (f->n_fft == (size_t)kFft)
+        FVAD_TRY(stft_launch(*f->tabs, f->d_in, 1, f->n_fft, 1, f->n_fft, b, f->d_band, 1, 0, f->d_out, f->d_window, norm, f->device, 0));
+    else
+        FVAD_TRY(stft_generic_launch(f->device, f->n_fft, f->d_in, 1, f->n_fft, 1, f->n_fft, b, f->d_band, 1, 0, f->d_out, f->d_window, norm, 0));
     FVAD_CUDA_TRY(cudaMemcpy(result, f->d_out, sizeof(float) * n_result, cudaMemcpyDeviceToHost));
     return FVAD_OK;
 }
@@ -118,6 +121,9 @@ extern "C" int fvad_stft_batch(fvad_fft *f, const float *d_pcm, size_t n_rows, s
     if (!f || !d_pcm || !d_band_sum) return set_error(FVAD_EINVALID_ARGUMENT, "fvad_stft_batch: null argument");
     if (max_bin >= f->n_fft / 2 + 1 || min_bin > max_bin) return set_error(FVAD_EOUT_OF_RANGE, "band %zu..%zu out of range", min_bin, max_bin);
     StftBands b{}; b.n_bands = 1; b.lo[0] = (int)min_bin; b.hi[0] = (int)max_bin;
+    if (f->n_fft != (size_t)kFft)
+        return stft_generic_launch(f->device, f->n_fft, d_pcm, n_rows, row_stride, n_frames, hop, b, d_band_sum, n_frames, 0, d_spectra,
+                                   nullptr, 0.f, (cudaStream_t)cuda_stream);
     return stft_launch(*f->tabs, d_pcm, n_rows, row_stride, n_frames, hop, b, d_band_sum, n_frames, 0, d_spectra, nullptr, 0.f,
                        f->device, (cudaStream_t)cuda_stream);
 }
@@ -152,13 +158,13 @@ extern "C" int fvad_spectrogram_compute(const float *samples, size_t n_samples, 
     if (!samples || !values) return set_error(FVAD_EINVALID_ARGUMENT, "null samples/values");
     if (values_len != info->width * info->height)
         return set_error(FVAD_EINVALID_RESULT_LEN, "values length %zu != width*height %zu", values_len, info->width * info->height);
-    if (fft_size != (size_t)kFft) return set_error(FVAD_EUNSUPPORTED, "this build's FFT kernel covers fft_size 2048 only (got %zu)", fft_size);
-    if (hop_size & 1) return set_error(FVAD_EUNSUPPORTED, "odd hop_size %zu: the kernel loads sample pairs", hop_size);
+    if (fft_size != (size_t)kFft) FVAD_TRY(stft_generic_supported(fft_size));
+    if (fft_size == (size_t)kFft && (hop_size & 1)) return set_error(FVAD_EUNSUPPORTED, "odd hop_size %zu: the 2048-point kernel loads sample pairs", hop_size);
     int device = 0;
     cudaError_t e = cudaGetDevice(&device);
     if (e != cudaSuccess) return set_error(FVAD_ECUDA, "cudaGetDevice: %s (no CPU fallback exists)", cudaGetErrorString(e));
     const StftTables *tabs = nullptr;
-    FVAD_TRY(stft_tables_get(device, &tabs));
+    if (fft_size == (size_t)kFft) FVAD_TRY(stft_tables_get(device, &tabs));
     if (bin_labels)
         for (size_t k = 0; k < info->height; k++) bin_labels[k] = (float)k * info->bin_width;     // FFT.binToFreq, FFT.zig:134-144
     if (info->width == 0) return FVAD_OK;
@@ -172,7 +178,9 @@ extern "C" int fvad_spectrogram_compute(const float *samples, size_t n_samples, 
         StftBands b{}; b.n_bands = 0;
         // one row, `width` overlapping frames `hop_size` apart; the window norm factor FFT.fft recomputes per call
         // (FFT.zig:94) is the table's (same in-order f32 sum over the same Hann values)
-        rc = stft_launch(*tabs, d_in, 1, 0 /* one row: stride unused */, info->width, hop_size, b, nullptr, info->width, 0, d_out, nullptr, 0.f, device, 0);
+        rc = fft_size == (size_t)kFft
+                 ? stft_launch(*tabs, d_in, 1, 0 /* one row: stride unused */, info->width, hop_size, b, nullptr, info->width, 0, d_out, nullptr, 0.f, device, 0)
+                 : stft_generic_launch(device, fft_size, d_in, 1, 0, info->width, hop_size, b, nullptr, info->width, 0, d_out, nullptr, 0.f, 0);
     }
     if (rc == FVAD_OK && cudaMemcpy(values, d_out, sizeof(float) * values_len, cudaMemcpyDeviceToHost) != cudaSuccess)
         rc = set_error(FVAD_ECUDA, "D2H: %s", cudaGetErrorString(cudaGetLastError()));

@@ -46,4 +46,13 @@ int stft_launch(const StftTables &t, const float *d_pcm, size_t n_rows, size_t r
                 size_t band_frame_offset, float *d_spectra, const float *d_window_override,
                 float norm_override, int device, cudaStream_t stream);
 
+// Any other even n_fft whose complex length n_fft/2 is made of the factors 2, 3, 4, 5 (stft_generic.cu): KissFFT's plan
+// executed stage by stage, one CTA per frame.  Same argument meaning as stft_launch; the Hann window / norm factor of the
+// size are built on first use.
+int stft_generic_supported(size_t n_fft);                 // FVAD_OK, FVAD_EINVALID_FFT_SIZE or FVAD_EUNSUPPORTED (message set)
+int stft_generic_norm_factor(int device, size_t n_fft, float *norm);
+int stft_generic_launch(int device, size_t n_fft, const float *d_pcm, size_t n_rows, size_t row_stride, size_t n_frames, size_t hop,
+                        const StftBands &bands, float *d_band, size_t band_frame_stride, size_t band_frame_offset, float *d_spectra,
+                        const float *d_window_override, float norm_override, cudaStream_t stream);
+
 }  // namespace fvad

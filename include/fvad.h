@@ -142,7 +142,10 @@ typedef struct fvad_batch fvad_batch;
 
 /* AudioPipeline.init x n_streams (src/AudioPipeline.zig:39-75, VAD.zig:97-192), all on CUDA
  * device `device` (-1 = current).  Errors as the reference: sample_rate != 48000 ->
- * FVAD_EINVALID_SAMPLE_RATE; odd/zero fft_size -> FVAD_EINVALID_FFT_SIZE. */
+ * FVAD_EINVALID_SAMPLE_RATE; odd/zero fft_size -> FVAD_EINVALID_FFT_SIZE.  fft_size: 2048 runs the specialised
+ * bandwidth kernel; every other even size whose half is made of the factors 2, 3, 4, 5 (256, 512, 960, 1024, 1920, 4096,
+ * ...) runs KissFFT's generic plan; a half with a larger prime factor -> FVAD_EUNSUPPORTED (kf_bfly_generic is not
+ * implemented); with the denoiser fft_size <= 6240 (the 480 -> fft_size re-framing history). */
 int  fvad_batch_create(const fvad_config *cfg, size_t n_streams, int device, fvad_batch **out);
 /* AudioPipeline.deinit */
 void fvad_batch_destroy(fvad_batch *b);
@@ -242,7 +245,7 @@ void fvad_pipeline_destroy(fvad_pipeline *p);                                   
 /* ---- leaf drop-ins ------------------------------------------------------------------ */
 /* FFT.zig: init/fft/binCount/binWidth/nyquistFreq/freqToBin/binToFreq/deinit (src/FFT.zig:28-144) */
 typedef struct fvad_fft fvad_fft;
-int    fvad_fft_create(size_t n_fft, size_t sample_rate, fvad_fft **out);               /* FFT.init */
+int    fvad_fft_create(size_t n_fft, size_t sample_rate, fvad_fft **out);               /* FFT.init; sizes as fvad_batch_create, up to 32768 */
 void   fvad_fft_destroy(fvad_fft *f);                                                   /* FFT.deinit */
 /* FFT.fft on a SplitSlice (first,second) of host memory; result = n_fft/2+1 normalised magnitudes. */
 int    fvad_fft_run(fvad_fft *f, const float *first, size_t n_first, const float *second, size_t n_second,
@@ -272,7 +275,7 @@ int    fvad_stft_batch(fvad_fft *f, const float *d_pcm, size_t n_rows, size_t ro
  * FFT.binToFreq) may be NULL.  fvad_spectrogram_shape does no compute and needs no device.
  * Errors: InsufficientSamples (n_samples < fft_size, :34-36); OutOfRange where the reference's slice
  * samples[from..to] would run past the input (hop_size < fft_size/2: a bounds panic in the reference);
- * Unsupported for fft_size != 2048 or odd hop_size. */
+ * Unsupported for an fft_size whose half has a prime factor above 5, or an odd hop_size with fft_size 2048. */
 typedef struct fvad_spectrogram_info {
     size_t height;          /* bins = fft_size/2 + 1 */
     size_t width;           /* steps */

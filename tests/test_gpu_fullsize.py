@@ -53,6 +53,20 @@ def test_configs1_full_size_properties(fv, checker, knobs):
         total += len(sa)
     assert total > 20 * 100, "two hours of radio traffic per stream must produce hundreds of segments"
 
+    # two WHOLE streams against the reference build of the oracle (tests/golden/fullsize_2h.npz, tools/make_golden_fullsize.py:
+    # four CPU-minutes per stream, run in the build container): every segment and every capture event of two hours, the
+    # long ring wrapped forty times
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fullsize_2h.npz"))
+    assert int(g["seconds"]) == secs
+    for sid in g["ids"]:
+        segs, evs = a[int(sid)]
+        assert segs.tobytes() == g[f"segments_{sid}"].tobytes(), f"stream {sid}: segment list differs from the reference's"
+        want_ev = g[f"events_{sid}"]
+        assert len(evs) == len(want_ev) and np.array_equal(evs["at_index"], want_ev[:, 0])
+        assert np.array_equal(evs["recording_state"].astype(np.uint64), want_ev[:, 1]) and np.array_equal(evs["sample_number"], want_ev[:, 2])
+        assert len(segs) > 250
+
     # prefix exactness against the oracle: decisions taken on STFT frames inside the first `pre` seconds
     pre = 240
     for sid in (3, 17):
