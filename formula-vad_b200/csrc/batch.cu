@@ -8,7 +8,12 @@
 #include "stft.cuh"
 #include "vadm.cuh"
 #include <algorithm>
+#include <atomic>
 #include <cmath>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
 #include <cstdlib>
 #include <cstdio>
 #include <cstring>
@@ -16,6 +21,59 @@
 #include <vector>
 
 using namespace fvad;
+
+// Pageable host input (what a Zig allocator hands over): cudaMemcpyAsync from pageable memory is a staged, synchronous
+// copy at ~10 GB/s -- 0.43 of the device-resident rate at 1184 streams.  The batch therefore owns a small ring of PINNED
+// staging slots and a few copy threads: the rows of a chunk are copied into a slot by the threads while the DMA engine
+// drains the previous slot, and the push returns as soon as its samples have left the caller's memory.
+class HostCopyPool {
+public:
+    explicit HostCopyPool(int n_threads) {
+        for (int i = 0; i < n_threads; i++) workers_.emplace_back([this] { run(); });
+    }
+    ~HostCopyPool() {
+        { std::lock_guard<std::mutex> lk(mu_); stop_ = true; }
+        cv_.notify_all();
+        for (auto &t : workers_) t.join();
+    }
+    // fn(i) for i in [0, n), spread over the threads; returns when all are done
+    void parallel_for(size_t n, const std::function<void(size_t)> &fn) {
+        if (n == 0) return;
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            fn_ = &fn; next_ = 0; n_ = n; pending_ = n; gen_++;
+        }
+        cv_.notify_all();
+        std::unique_lock<std::mutex> lk(mu_);
+        done_cv_.wait(lk, [this] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+private:
+    void run() {
+        unsigned long long seen = 0;
+        for (;;) {
+            std::unique_lock<std::mutex> lk(mu_);
+            cv_.wait(lk, [&] { return stop_ || (gen_ != seen && next_ < n_); });
+            if (stop_) return;
+            while (next_ < n_) {
+                const size_t i = next_++;
+                const std::function<void(size_t)> *fn = fn_;
+                lk.unlock();
+                (*fn)(i);
+                lk.lock();
+                if (--pending_ == 0) done_cv_.notify_all();
+            }
+            seen = gen_;
+        }
+    }
+    std::vector<std::thread> workers_;
+    std::mutex mu_;
+    std::condition_variable cv_, done_cv_;
+    const std::function<void(size_t)> *fn_ = nullptr;
+    size_t next_ = 0, n_ = 0, pending_ = 0;
+    unsigned long long gen_ = 0;
+    bool stop_ = false;
+};
 
 struct fvad_batch {
     fvad_config cfg;
@@ -86,6 +144,13 @@ struct fvad_batch {
     // FVAD_KEEP_FEATURES: the per-STFT-frame features of the whole run stay in HBM for fvad_batch_sweep
     float *d_feat_min = nullptr, *d_feat_ratio = nullptr, *d_feat_vad = nullptr;   // [bands][S][feat_cap], [S][feat_cap] x 2
     size_t feat_cap = 0;
+    // pageable host input: pinned staging slots + copy threads (created at the first pageable push)
+    static constexpr int kStageSlots = 3;
+    float *h_stage[kStageSlots] = {};      // pinned, [rows][stage_samples] each
+    cudaEvent_t evStage[kStageSlots] = {}; // the H2D copy out of the slot has completed
+    size_t stage_samples = 0;
+    int stage_next = 0;
+    HostCopyPool *copy_pool = nullptr;
     // Recorder (fvad_batch_set_recording): history of the original PCM + the host-side capture state per stream
     bool rec_on = false;
     bool hist_fixed = false;               // a ring of hist_cap samples (else: everything pushed, growing)
@@ -189,6 +254,11 @@ extern "C" void fvad_batch_destroy(fvad_batch *b) {
         cudaFree(b->d_hist); cudaFree(b->d_clip_pieces); cudaFree(b->d_clip_stage);
         cudaFree(b->d_sw_params); cudaFree(b->d_sw_rings); cudaFree(b->d_sw_segs); cudaFree(b->d_sw_counts);
         if (b->h_arena_cnt) cudaFreeHost(b->h_arena_cnt);
+        delete b->copy_pool;
+        for (int i = 0; i < fvad_batch::kStageSlots; i++) {
+            if (b->h_stage[i]) cudaFreeHost(b->h_stage[i]);
+            if (b->evStage[i]) cudaEventDestroy(b->evStage[i]);
+        }
         for (cudaStream_t st : {b->sA, b->sB, b->sB2, b->sC, b->sE}) if (st && st != b->stream) cudaStreamDestroy(st);
         if (b->stream) cudaStreamDestroy(b->stream);
     }
@@ -634,6 +704,27 @@ static int history_append(fvad_batch *b, const float *src, size_t src_stride, si
     return FVAD_OK;
 }
 
+static int ensure_staging(fvad_batch *b) {
+    if (b->copy_pool) return FVAD_OK;
+    // ~32 MB per slot, whole samples per row, at least 4096 per row
+    size_t per_row = ((size_t)32 << 20) / sizeof(float) / b->rows;
+    per_row = std::max<size_t>(per_row, 4096);
+    per_row = std::min(per_row, tile_samples(b));
+    for (int i = 0; i < fvad_batch::kStageSlots; i++) {
+        if (cudaHostAlloc((void **)&b->h_stage[i], b->rows * per_row * sizeof(float), cudaHostAllocDefault) != cudaSuccess)
+            return set_error(FVAD_EOUT_OF_MEMORY, "pinned staging slot of %zu bytes: %s", b->rows * per_row * sizeof(float),
+                             cudaGetErrorString(cudaGetLastError()));
+        FVAD_CUDA_TRY(cudaEventCreateWithFlags(&b->evStage[i], cudaEventDisableTiming));
+    }
+    b->stage_samples = per_row;
+    unsigned hw = std::thread::hardware_concurrency();
+    int nt = (int)std::min<unsigned>(hw ? hw : 4, 8);
+    if (const char *e = debug_knob("copy_threads")) nt = std::max(1, atoi(e));
+    b->copy_pool = new (std::nothrow) HostCopyPool(nt);
+    if (!b->copy_pool) return set_error(FVAD_EOUT_OF_MEMORY, "host allocation failed");
+    return FVAD_OK;
+}
+
 // Before the first copy into the filling buffer since it changed hands: its previous tile must have been read.
 static int fill_begin(fvad_batch *b) {
     if (!b->fill_waited) {
@@ -658,11 +749,39 @@ extern "C" int fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n,
         for (size_t r = 2; r < b->rows && strided; r++) strided = (pcm[r] - pcm[r - 1]) == stride;
         strided = strided && stride >= (ptrdiff_t)n && (size_t)stride * sizeof(float) < ((size_t)1 << 31);
     } else if (strided) stride = (ptrdiff_t)n;
+    // pageable rows go through the pinned staging slots (the copy threads move them there); pinned / registered rows are
+    // copied where they lie
+    bool pageable = false;
+    if (n) {
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, pcm[0]) != cudaSuccess) { cudaGetLastError(); pageable = true; }
+        else pageable = at.type == cudaMemoryTypeUnregistered;
+    }
+    if (pageable) FVAD_TRY(ensure_staging(b));
     for (size_t off = 0; off < n;) {
         const size_t m = std::min(tile_samples(b) - b->fill_len, n - off);
         FVAD_TRY(fill_begin(b));
         float *dst = b->d_work_buf[b->work_par] + b->fill_len;
-        if (strided) {
+        if (pageable) {
+            for (size_t sub = 0; sub < m; sub += b->stage_samples) {
+                const size_t len = std::min(b->stage_samples, m - sub);
+                const int slot = b->stage_next;
+                b->stage_next = (slot + 1) % fvad_batch::kStageSlots;
+                FVAD_CUDA_TRY(cudaEventSynchronize(b->evStage[slot]));          // the slot's previous contents are on the device
+                float *stage = b->h_stage[slot];
+                const size_t src_off = off + sub, ss = b->stage_samples;
+                // split long rows so that few-row batches still use every thread
+                const size_t parts = b->rows >= 16 ? 1 : 8;
+                b->copy_pool->parallel_for(b->rows * parts, [&](size_t i) {
+                    const size_t r = i / parts, q = i - r * parts;
+                    const size_t a = len * q / parts, z = len * (q + 1) / parts;
+                    memcpy(stage + r * ss + a, pcm[r] + src_off + a, (z - a) * sizeof(float));
+                });
+                FVAD_CUDA_TRY(cudaMemcpy2DAsync(dst + sub, b->work_cap * sizeof(float), stage, ss * sizeof(float), len * sizeof(float),
+                                                b->rows, cudaMemcpyHostToDevice, b->sH));
+                FVAD_CUDA_TRY(cudaEventRecord(b->evStage[slot], b->sH));
+            }
+        } else if (strided) {
             FVAD_CUDA_TRY(cudaMemcpy2DAsync(dst, b->work_cap * sizeof(float), pcm[0] + off, (size_t)stride * sizeof(float),
                                             m * sizeof(float), b->rows, cudaMemcpyHostToDevice, b->sH));
         } else {
@@ -677,8 +796,9 @@ extern "C" int fvad_batch_push(fvad_batch *b, const float *const *pcm, size_t n,
     }
     b->total_write_count += n;
     // input is borrowed only until return (AudioPipeline.pushSamples copies into its ring): wait for the copies
-    // only; the stages keep running behind the caller's back until fvad_batch_sync
-    FVAD_CUDA_TRY(cudaStreamSynchronize(b->sH));
+    // only; the stages keep running behind the caller's back until fvad_batch_sync.  Pageable input has already left the
+    // caller's memory (it sits in the staging slots).
+    if (!pageable) FVAD_CUDA_TRY(cudaStreamSynchronize(b->sH));
     return FVAD_OK;
 }
 

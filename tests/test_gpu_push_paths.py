@@ -58,6 +58,14 @@ def test_push_cut_invariance(fv, checker, n_channels, tile, knobs):
         del pad
     assert run(separate_rows)[0] == base
 
+    hp = torch.from_numpy(pcm).pin_memory()                                      # pinned host rows: copied where they lie (2-D copies)
+    def pinned_rows(b):
+        base = hp.data_ptr()
+        rows = [base + 4 * n * r for r in range(S * n_channels)]
+        b.push_rows(rows, n // 3)
+        b.push_rows([p + 4 * (n // 3) for p in rows], n - n // 3)
+    assert run(pinned_rows)[0] == base                                           # (numpy arrays above are pageable: staging slots)
+
     x = torch.from_numpy(pcm).cuda()                                             # [S][C][n] on the device
     def device_whole(b):
         b.push_device(x.data_ptr(), n_channels * n, n, n)
