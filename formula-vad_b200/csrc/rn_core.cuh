@@ -289,8 +289,11 @@ RN_HD void load_windowed(const Tables &t, cpx *buf, SRC src) {
 constexpr int kScrFft = 2 * kSlots960;                     // cpx buf[1020]
 constexpr int kScrAna = kScrFft + 96;                      // + misc
 constexpr int kScrSyn = kScrFft + 2 * kFreq + 2 + 96;      // + linear X[481] + misc
-constexpr int kScrPitch = 864 + 296 + 388 + 388 + 64 + 64 + 8;   // xlp, xc, yyl, ip, list, misc, pad: the stride is 24 mod 32 banks,
-                                                                    // so the pooled chains of a CTA's four frames start 8 banks apart
+constexpr int kScrIp = 68;                                 // inner products by LIST POSITION: [0] = xx, [1 + i] = lag list[i] (<= 59 lags)
+constexpr int kScrPitch = 864 + 296 + 388 + kScrIp + 64 + 64 + 8;   // xlp, xc, yyl, ip, list, misc, pad = 1752 floats: the stride is
+                                                                    // 24 mod 32 banks, so the pooled chains of a CTA's four frames
+                                                                    // start 8 banks apart, and four frames take 28 032 B: EIGHT CTAs
+                                                                    // per SM (round 1 indexed ip by lag: 388 floats, 33 KB, six CTAs)
 
 // frame_analysis + the energy half of compute_frame_features (denoise.c:295-308, 349-362, 363-365):
 // X, Ex, E<0.04 silence flag and the cepstrum dct(Ly) with its -12/-4 offsets.
@@ -411,16 +414,16 @@ RN_HD float pitch_gain(float xy, float xx, float yy) {     // compute_pitch_gain
 template <int F>
 RN_HD void pitch_blk(const float *const *xs, PitchCand *const *outs, float *scr0) {
     constexpr int NT = 32 * F;
-    // per frame f (scr = scr0 + f*kScrPitch): xlp 864 | xc 296 | yyl 388 | ip 388 | list 64 ints | misc 16 | imisc 48 ints
+    // per frame f (scr = scr0 + f*kScrPitch): xlp 864 | xc 296 | yyl 388 | ip 68 | list 64 ints | misc 16 | imisc 48 ints
     // misc: [0..4] ac, [8..12] num, [13] Syy of the coarse scan, [14] Syy of the fine scan
     // imisc: [0] best0 [1] best1 [2] T0 [3] nlist [4] ncand; [5..] candT, candTb
 #define RN_SCR(f) (scr0 + (size_t)(f) * kScrPitch)
 #define RN_XC(f) (RN_SCR(f) + 864)
 #define RN_YYL(f) (RN_SCR(f) + 864 + 296)
 #define RN_IP(f) (RN_SCR(f) + 864 + 296 + 388)
-#define RN_LIST(f) (reinterpret_cast<int *>(RN_SCR(f) + 864 + 296 + 388 + 388))
-#define RN_MISC(f) (RN_SCR(f) + 864 + 296 + 388 + 388 + 64)
-#define RN_IMISC(f) (reinterpret_cast<int *>(RN_SCR(f) + 864 + 296 + 388 + 388 + 64 + 16))
+#define RN_LIST(f) (reinterpret_cast<int *>(RN_SCR(f) + 864 + 296 + 388 + kScrIp))
+#define RN_MISC(f) (RN_SCR(f) + 864 + 296 + 388 + kScrIp + 64)
+#define RN_IMISC(f) (reinterpret_cast<int *>(RN_SCR(f) + 864 + 296 + 388 + kScrIp + 64 + 16))
     RN_BLK_PHASE(NT)   // pitch_downsample, pitch.c:171-173 (warp f owns frame f)
         const int f = tid >> 5, lane = tid & 31;
         const float *x = xs[f];                            // pitch_buf of the frame (1728 samples)
@@ -667,31 +670,39 @@ RN_HD void pitch_blk(const float *const *xs, PitchCand *const *outs, float *scr0
 #pragma unroll
                 for (int u = 0; u < 4; u++) s = s + xv[u] * xlp[384 + i + u - lag];
             }
-            RN_IP(f)[lag] = s;
+            RN_IP(f)[1 + idx] = s;                         // by list position; ip_at() finds a lag's position
         }
     RN_BLK_END
     RN_BLK_PHASE(NT)
         if (tid < 16 * F) {
             const int f = tid >> 4, c = tid & 15;
             const int *imisc = RN_IMISC(f);
-            const float *ip = RN_IP(f), *yyl = RN_YYL(f);
+            const float *ipl = RN_IP(f), *yyl = RN_YYL(f);
+            const int *list = RN_LIST(f);
+            const int nl = imisc[3];
+            // the inner product of a lag that the list holds (every lag asked for below was marked; ascending list)
+            auto ip_at = [&](int lag) {
+                int lo = 0, hi = nl - 1;
+                while (lo < hi) { const int mid = (lo + hi) >> 1; if (list[mid] < lag) lo = mid + 1; else hi = mid; }
+                return ipl[1 + lo];
+            };
             PitchCand *out = outs[f];
             const int nc = imisc[4];
             if (out != nullptr && c < nc) {
                 const int T0 = imisc[2];
-                const float xx = ip[0];
+                const float xx = ipl[0];
                 int T; float xy, yy;
-                if (c == 0) { T = T0; xy = ip[T0]; yy = yyl[T0]; }
+                if (c == 0) { T = T0; xy = ip_at(T0); yy = yyl[T0]; }
                 else {
                     const int T1 = imisc[5 + 2 * c], T1b = imisc[6 + 2 * c];
                     T = T1;
-                    xy = .5f * (ip[T1] + ip[T1b]);             // pitch.c:479-480
+                    xy = .5f * (ip_at(T1) + ip_at(T1b));       // pitch.c:479-480
                     yy = .5f * (yyl[T1] + yyl[T1b]);
                 }
                 out->T[c] = (short)T;
                 out->xy[c] = xy; out->yy[c] = yy;
                 out->g[c] = pitch_gain(xy, xx, yy);
-                const float x0 = ip[T - 1], x1 = ip[T], x2 = ip[T + 1];       // pitch.c:509-517
+                const float x0 = ip_at(T - 1), x1 = ip_at(T), x2 = ip_at(T + 1);       // pitch.c:509-517
                 int off;
                 if ((x2 - x0) > .7f * (x1 - x0)) off = 1;
                 else if ((x0 - x2) > .7f * (x1 - x2)) off = -1;
