@@ -1036,6 +1036,20 @@ constexpr int kRnnWeights = 86952, kRnnBiases = 551;
 // vectors of ONE state (floats); state r of a CTA lives at scr + r * kRv_end
 constexpr int kRv_feat = 0, kRv_v1 = 48, kRv_v3 = 96, kRv_v4 = 240, kRv_zr = 456, kRv_hp = 648, kRv_hn = 744, kRv_end = 840;
 
+RN_HD unsigned f2u_early(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(f);
+#else
+    union { float f; unsigned u; } c; c.f = f; return c.u;
+#endif
+}
+RN_HD float u2f_early(unsigned u) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    union { unsigned u; float f; } c; c.u = u; return c.f;
+#endif
+}
 RN_HD float bits_to_f32(unsigned u) {
 #if defined(__CUDA_ARCH__)
     return __uint_as_float(u);
@@ -1048,6 +1062,31 @@ struct RnnF2 { float x, y; };                              // two consecutive ve
 // sum[r] += W[j][col]*v_r[j] for j in [j0,j1), in order, for the R states.  j0 is even and j1-j0 a multiple of 6 (true
 // for every layer): the chain is walked in blocks of three row pairs, and the next block's weight words and vector
 // elements are fetched before the current block is accumulated, so no shared-memory latency sits on the FADD chain.
+// EXPERIMENT ONLY (knob rnn_tolerance_mode, never the default): what a tensor-core formulation of the
+// gate contractions would do to the numbers, without building one.  An MMA does not keep the reference's summation order
+// and takes its activations in reduced precision; the int8 weights are exact in every MMA input type.
+//   0  exact: in-order f32 accumulation of f32 products (the product path)
+//   1  f32 products, accumulated in FOUR interleaved partial sums (any GEMM's freedom to reassociate)
+//   2  as 1, activations rounded to TF32 (10-bit mantissa) before the product
+//   3  as 1, activations rounded to BF16 (7-bit mantissa)
+#if defined(__CUDACC__)
+__constant__ int c_rnn_tolerance_mode;
+#endif
+RN_HD int rnn_tolerance_mode() {
+#if defined(__CUDA_ARCH__)
+    return c_rnn_tolerance_mode;
+#else
+    return 0;
+#endif
+}
+RN_HD float rnn_round_act(float x, int mode) {
+    if (mode < 2) return x;
+    const unsigned u = f2u_early(x);
+    const unsigned drop = mode == 2 ? 13u : 16u;             // tf32 keeps 10 mantissa bits, bf16 7: round to nearest even
+    const unsigned r = u + ((1u << (drop - 1)) - 1u) + ((u >> drop) & 1u);
+    return u2f_early(r & ~((1u << drop) - 1u));
+}
+
 constexpr int kRnnP = 3;
 template <int R> struct RnnBlk { RnnF2 x[R][kRnnP]; };
 struct RnnWBlk { unsigned u[kRnnP]; };
@@ -1063,8 +1102,27 @@ RN_HD void rnn_blk_load(RnnBlk<R> &b, const float *v, int j) {
         for (int r = 0; r < R; r++) b.x[r][p] = *reinterpret_cast<const RnnF2 *>(v + r * kRv_end + j + 2 * p);
     }
 }
+// the experiment's chain: four partial sums, optionally reduced-precision activations (see rnn_tolerance_mode)
+template <int R>
+RN_HD void rnn_chain_tol(const unsigned *W2, int cols, int col, const float *v, const float *rg, int j0, int j1, float (&sum)[R], int mode) {
+    float part[R][4];
+    for (int r = 0; r < R; r++) for (int q = 0; q < 4; q++) part[r][q] = 0.f;
+    for (int j = j0; j < j1; j += 2) {
+        const unsigned u = W2[(j >> 1) * cols + col];
+        const float w0 = bits_to_f32(u << 16), w1 = bits_to_f32(u & 0xffff0000u);
+        for (int r = 0; r < R; r++) {
+            float x0 = v[r * kRv_end + j], x1 = v[r * kRv_end + j + 1];
+            if (rg) { x0 *= rg[r * kRv_end + j]; x1 *= rg[r * kRv_end + j + 1]; }     // the reset gate applied to the state first
+            part[r][(j >> 1) & 1 ? 2 : 0] += w0 * rnn_round_act(x0, mode);
+            part[r][(j >> 1) & 1 ? 3 : 1] += w1 * rnn_round_act(x1, mode);
+        }
+    }
+    for (int r = 0; r < R; r++) sum[r] += (part[r][0] + part[r][1]) + (part[r][2] + part[r][3]);
+}
+
 template <int R>
 RN_HD void rnn_chain(const unsigned *W2, int cols, int col, const float *v, int j0, int j1, float (&sum)[R]) {
+    if (const int mode = rnn_tolerance_mode()) { rnn_chain_tol<R>(W2, cols, col, v, nullptr, j0, j1, sum, mode); return; }
     RnnBlk<R> cur, nxt;
     RnnWBlk wc, wn;
     rnn_w_load(wc, W2, cols, col, j0);
@@ -1088,6 +1146,7 @@ RN_HD void rnn_chain(const unsigned *W2, int cols, int col, const float *v, int 
 // recurrent part of the candidate gate: sum += (W[j][col]*state[j-M])*r[j-M]  (rnn.c:147); same blocking
 template <int R>
 RN_HD void rnn_chain_r(const unsigned *W2, int cols, int col, const float *v, const float *rg, int M, int J, float (&sum)[R]) {
+    if (const int mode = rnn_tolerance_mode()) { rnn_chain_tol<R>(W2, cols, col, v, rg - M, M, J, sum, mode); return; }
     RnnBlk<R> cur, nxt, gcur, gnxt;                         // g*: the reset-gate values
     RnnWBlk wc, wn;
     rnn_w_load(wc, W2, cols, col, M);

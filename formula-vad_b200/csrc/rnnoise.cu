@@ -1059,7 +1059,7 @@ static size_t g_bq2_static[512], g_bq3_static[512];
 #define FVAD_BQ3_VARIANTS(X) X(48) X(96) X(160)
 constexpr size_t kSmemAna = (size_t)kWarpsPerCta * kScrAna * sizeof(float);
 constexpr size_t smem_pitch(int F) { return (size_t)F * kScrPitch * sizeof(float); }
-#define FVAD_PITCH_VARIANTS(X) X(4) X(6) X(8)
+#define FVAD_PITCH_VARIANTS(X) X(2) X(4) X(6) X(8)
 constexpr size_t kSmemSyn = (size_t)kWarpsPerCta * kScrSyn * sizeof(float);
 constexpr size_t smem_rnn(int states) { return ((kRnnWeights * 2 + 15) & ~15) + (560 + 208 + (size_t)states * kRv_end) * sizeof(float); }
 
@@ -1266,7 +1266,7 @@ int rnnoise_stage_b1(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     FVAD_LAUNCH(k_rn_analysis, warp_grid, 32 * kWarpsPerCta, kSmemAna, st, t, s.hp, r->hp_stride(), N, Q, Qcap, s.X, s.Ex, s.ceps, s.sil);
     {
         int F = pitch_frames_per_cta(NQ, r->device);
-        if (const char *e = debug_knob("pitch_f")) { const int v = atoi(e); if (v == 4 || v == 6 || v == 8) F = v; }
+        if (const char *e = debug_knob("pitch_f")) { const int v = atoi(e); if (v == 2 || v == 4 || v == 6 || v == 8) F = v; }
         bool launched = false;
 #define FVAD_PITCH_GO(FF)                                                                                                \
         if (!launched && F == FF) {                                                                                      \
@@ -1309,6 +1309,15 @@ int rnnoise_stage_b(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
 
 // Stage C: the RNN, frame-sequential per state.
 int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
+    {   // experiment hook (knob rnn_tolerance_mode; 0 = the exact path): see rn_core.cuh rnn_tolerance_mode
+        static int set_mode[64] = {};
+        int mode = 0;
+        if (const char *e = debug_knob("rnn_tolerance_mode")) mode = atoi(e);
+        if (r && r->device >= 0 && r->device < 64 && set_mode[r->device] != mode + 1) {
+            FVAD_CUDA_TRY(cudaMemcpyToSymbolAsync(rn::c_rnn_tolerance_mode, &mode, sizeof mode, 0, cudaMemcpyHostToDevice, st));
+            set_mode[r->device] = mode + 1;
+        }
+    }
     FVAD_TRY(rn_check(r, slot, Qs));
     if (Qs == 0) return FVAD_OK;
     RnSlot &s = r->slots[slot];
