@@ -59,6 +59,13 @@ struct RnnoiseBatch {
     std::vector<RnSlot> slots;
     // single-stage arrays (carried in place)
     float *hp_hist = nullptr;      // [N][kPHist]   stage A: pitch/analysis history between tiles
+    // stage A, fourth biquad form: what the chain kernel publishes for the verifying kernel (one tile; stage A of the next
+    // tile follows on the same stream)
+    float *bq_m0 = nullptr;        // [N][bq_m0_stride()]  m0 before every sample of the tile, then the end state's
+    float *bq_m1 = nullptr;        // [N][bq_m1_stride()]  m1 before every 16-sample iteration, then the end state's
+    int *bq_broken = nullptr;      // [N]  first block whose replay disagreed with the chain (kBq4None: none)
+    size_t bq_m0_stride() const { return Qcap * kFrame + 4; }
+    size_t bq_m1_stride() const { return Qcap * (kFrame / 16) + 4; }
     float *cepsc = nullptr;        // [N][8 + Qcap][22]  stage B
     float *head = nullptr;         // [N][Qcap][480]     stage D
     float *tail = nullptr;         // [N][1 + Qcap][480] stage D
@@ -628,6 +635,215 @@ __global__ void __launch_bounds__(bq_threads(BQ)) k_rn_biquad_v3(const float *__
     }
 }
 
+// Fourth form (knob bq_form=4, the default in the latency regime: every chain on an SM of its own): the chain and its
+// verification are SEPARATE KERNELS.  In the chain-per-CTA kernels above the lane's loop costs 41.6-42.6 cycles per sample
+// whatever is switched off beside it; tools/ubench/chain_mix.cu runs the same step alone at 32-33.
+//   k_rn_biquad_chain   one warp per state, lane 0 only: reads its PCM straight from global memory (16-byte loads one
+//                       iteration ahead, L2 prefetch six frames ahead), runs biquad_chain_step, and publishes m0 before every
+//                       sample (one 16-byte store per four samples) and m1 before every 16 samples.  No shared memory, no
+//                       barrier, no hand-shake.  Iterations that start in a denormal tail take the reference's own double step.
+//   k_rn_biquad_verify  frame-parallel, a warp per 32 samples: rebuilds each sample's m1 the way the lane formed it,
+//                       re-evaluates the step with the full hazard analysis (biquad_step_eft_x), compares with the state
+//                       the lane carried on, and stores y = x + m0 (the reference's own float add).  A warp that saw a
+//                       hazard replays its 32 samples on one lane with the reference's double arithmetic from the recorded
+//                       state; the replay ends in the recorded state of the next block unless the fast step was really
+//                       wrong -- then the block's index goes to broken[state] (atomicMin).  0.6 ms per 20 x 60 s tile.
+//   k_rn_biquad_fixup   a warp per state, returns at once unless broken[state] is set: everything from the first wrong
+//                       block to the end of the tile is recomputed with the double step from the recorded (still true)
+//                       state.  On the bench streams the fast step is never wrong outside denormal tails (0 of 86 M
+//                       samples on the host), so this kernel is a launch and a load; knob bq_dbg=32 plants a wrong state
+//                       to exercise it, bq_dbg=64 switches the repair off (tests/test_gpu_denoiser.py).
+// The verdict no longer has to reach the lane while it runs, which is what tied the two together in one CTA.
+// What the lane's loop taught (ncu source pages of four layouts, 20 streams x 60 s):
+//  * ptxas puts all loads of the loop on ONE counting scoreboard: a first use that comes after younger loads were issued
+//    waits for those too.  Loads re-issued quad by quad into the registers just consumed: 7 cycles per sample of
+//    long-scoreboard stall (the full L2 latency every iteration); two register sets taking turns: the same, and plain loads
+//    are sunk to their first use to save registers (volatile ones to the stores that follow them).  What works is the order
+//    "scale the whole set (first use), THEN reload it", which the register dependence itself enforces.
+//  * a taken branch costs the lone warp ~17 cycles (instruction fetch): the fast path closes the loop itself and the
+//    denormal path sits behind it; the not-taken branch between head and body also keeps the head's loads at the head.
+//  * what is left per 32-sample iteration: 32 scalings + 8 loads + pointer arithmetic at the head while the chain idles.
+// 39.8 cycles per sample (233.5 ms per 240 s of 20 streams) against 42.0 for the first form: the loop body runs at 34.2.
+constexpr int kBq4It = 16, kBq4ItPerFrame = kFrame / kBq4It, kBq4Blk = 32, kBq4VerWarps = 8;
+constexpr int kBq4None = 0x7fffffff;
+static_assert(kFrame % kBq4Blk == 0 && kBq4Blk % kBq4It == 0, "verify blocks tile the frame");
+__device__ __forceinline__ bool bq4_tiny(float m0, float m1) {
+    const float a0 = fabsf(m0), a1 = fabsf(m1);
+    return (a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f);
+}
+// IT = samples per iteration of the lane's loop (16 or 32).  At the head of an iteration the raw samples loaded one
+// iteration ago are scaled into a second register set -- their first use, the only place the lane waits for memory -- and
+// the loads of the NEXT iteration are issued at once into the registers just read: a whole iteration of chain time (550 /
+// 1100 cycles) to land.  The order matters: ptxas puts all of a loop's loads on ONE counting scoreboard, so a first use that
+// comes after younger loads were issued waits for those as well (ncu source page of two earlier layouts: 275 cycles of
+// long-scoreboard stall per iteration, the full L2 latency, although the data had been requested 550 cycles earlier).
+__device__ __forceinline__ float4 bq4_ld(const float *p) {
+    float4 v;
+    asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+// MONO: one channel per state, the state's frames are contiguous in its row (no pointer logic in the loop).  The denormal-tail
+// path is marked unlikely so that the fast path falls through: a taken branch costs the lone warp ~17 cycles of instruction
+// fetch, and the not-taken branch behind the head keeps the scaling and the loads in a basic block of their own -- at the head.
+template <int IT, bool MONO>
+__global__ void __launch_bounds__(32) k_rn_biquad_chain(const float *__restrict__ in, size_t in_stride, int C, int Q, size_t Tn,
+                                                        RnPersist *persist, float *__restrict__ pm0, size_t pm0_stride,
+                                                        float *__restrict__ pm1, size_t pm1_stride, int *__restrict__ broken,
+                                                        size_t N, int dbg) {
+    static_assert(kFrame % IT == 0 && IT % kBq4It == 0, "iterations tile the frame");
+    constexpr int kQuads = IT / 4, kItPerFrame = kFrame / IT, kAheadFrames = 6, kAhead = kAheadFrames * kFrame;
+    const size_t n = blockIdx.x;
+    if (n >= N || threadIdx.x != 0) return;
+    float m0 = persist[n].biq[0], m1 = persist[n].biq[1];
+    broken[n] = kBq4None;
+    float *mo = pm0 + n * pm0_stride, *m1o = pm1 + n * pm1_stride;
+    const float *rowbase = in + n * (size_t)C * in_stride;
+    if (Q <= 0) return;
+    for (int c = 0; c < C; c++)                                     // the head of every channel row; the loop prefetches further on
+        for (size_t a = 0; a < (size_t)kAhead && a < Tn * kFrame; a += 32)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(rowbase + (size_t)c * in_stride + a));
+    float4 xr[kQuads];                                              // raw samples of the iteration about to run
+#pragma unroll
+    for (int k = 0; k < kQuads; k++) xr[k] = bq4_ld(rowbase + 4 * k);
+    bool tiny = bq4_tiny(m0, m1);
+    // the iteration being FETCHED: iteration nit of frame (time frame ntf, channel nc) of the state's sequence
+    const float *pnext = rowbase;
+    int nit = 0, nc = 0; size_t ntf = 0;
+    const int H = Q * kItPerFrame;
+    const int row_floats = (int)(Tn * kFrame);
+    const int fault_h = ((dbg & 32) && n == 0) ? 40 * kItPerFrame - 1 : -1;    // test only: a wrong state after this iteration
+    int h = 0;
+    bool more;
+    // scale the iteration's samples (their first use: the lane's only wait for memory), then fetch iteration h + 1 into the
+    // registers just read (after the last iteration: any valid data)
+    auto head = [&](float4 (&xs)[kQuads]) {
+#pragma unroll
+        for (int k = 0; k < kQuads; k++) {
+            xs[k].x = xr[k].x * 32767.0f; xs[k].y = xr[k].y * 32767.0f; xs[k].z = xr[k].z * 32767.0f; xs[k].w = xr[k].w * 32767.0f;
+        }
+        more = h + 1 < H;
+        const float *pl;
+        if (MONO) {
+            pnext += IT;
+            pl = more ? pnext : rowbase;
+            if ((h + 1) * IT + kAhead < row_floats) asm volatile("prefetch.global.L2 [%0];" ::"l"(pnext + kAhead));
+        } else {
+            nit++; pnext += IT;
+            if (nit == kItPerFrame) {
+                nit = 0; nc++;
+                if (nc == C) { nc = 0; ntf++; }
+                pnext = rowbase + (size_t)nc * in_stride + ntf * kFrame;
+                if (ntf + kAheadFrames < Tn) {                      // a frame of this row, six frames ahead, into L2
+                    const float *pf = pnext + kAhead;
+#pragma unroll 1
+                    for (int a = 0; a < kFrame; a += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + a));
+                }
+            }
+            pl = more ? pnext : rowbase;
+        }
+#pragma unroll
+        for (int k = 0; k < kQuads; k++) xr[k] = bq4_ld(pl + 4 * k);
+    };
+    auto foot = [&]() {
+        if (h == fault_h) m0 = __uint_as_float(__float_as_uint(m0) ^ 0x1000u);
+        mo += IT; m1o += IT / kBq4It; h++;
+    };
+#pragma unroll 1
+    for (;;) {
+        float4 xs[kQuads];
+        head(xs);
+        if (__builtin_expect(!tiny, 1)) {                           // (the branch keeps the head a basic block of its own: at the head)
+#pragma unroll
+            for (int k = 0; k < kQuads; k++) {
+                if (k % (kBq4It / 4) == 0) m1o[k / (kBq4It / 4)] = m1;
+                float4 pm;
+                pm.x = m0; biquad_chain_step(xs[k].x, m0, m1);
+                pm.y = m0; biquad_chain_step(xs[k].y, m0, m1);
+                pm.z = m0; biquad_chain_step(xs[k].z, m0, m1);
+                pm.w = m0; biquad_chain_step(xs[k].w, m0, m1);
+                *reinterpret_cast<float4 *>(mo + 4 * k) = pm;
+                // decided four samples before the iteration ends (the state decays by 0.2 % per sample and the threshold
+                // has five decades of margin): the branch behind the next head then never waits for the chain
+                if (k == kQuads - 2) tiny = bq4_tiny(m0, m1);
+            }
+            foot();
+            if (more) continue;                                     // the fast path closes the loop itself: one taken branch per iteration
+            break;
+        }
+        {                                                           // denormal tail of a silence: the reference's own arithmetic
+#pragma unroll
+            for (int k = 0; k < kQuads; k++) {
+                if (k % (kBq4It / 4) == 0) m1o[k / (kBq4It / 4)] = m1;
+                float4 pm;
+                pm.x = m0; biquad_step_x(xs[k].x, m0, m1);
+                pm.y = m0; biquad_step_x(xs[k].y, m0, m1);
+                pm.z = m0; biquad_step_x(xs[k].z, m0, m1);
+                pm.w = m0; biquad_step_x(xs[k].w, m0, m1);
+                *reinterpret_cast<float4 *>(mo + 4 * k) = pm;
+            }
+            tiny = bq4_tiny(m0, m1);
+        }
+        foot();
+        if (!more) break;
+    }
+    mo[0] = m0;                                                     // the end state closes both records
+    m1o[0] = m1;
+    persist[n].biq[0] = m0; persist[n].biq[1] = m1;
+}
+
+// sample t of state n's tile (frame q = t / 480 of the state's frame sequence (t0,c0),(t0,c1),...): scaled as the Denoiser does
+__device__ __forceinline__ float bq4_x(const float *__restrict__ in, size_t in_stride, int C, size_t n, size_t t) {
+    const size_t q = t / kFrame, i = t - q * kFrame;
+    return in[(n * C + (q % C)) * in_stride + (q / C) * kFrame + i] * 32767.0f;
+}
+__global__ void __launch_bounds__(32 * kBq4VerWarps) k_rn_biquad_verify(const float *__restrict__ in, size_t in_stride, int C, int Q,
+                                                                        const float *__restrict__ pm0, size_t pm0_stride,
+                                                                        const float *__restrict__ pm1, size_t pm1_stride,
+                                                                        int *__restrict__ broken, float *__restrict__ hp,
+                                                                        size_t hp_stride, size_t N) {
+    const size_t n = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const size_t vb = (size_t)blockIdx.x * kBq4VerWarps + (threadIdx.x >> 5);
+    const size_t T = (size_t)Q * kFrame;
+    if (n >= N || vb * kBq4Blk >= T) return;
+    const size_t t = vb * kBq4Blk + lane;
+    const float *M0 = pm0 + n * pm0_stride, *M1 = pm1 + n * pm1_stride;
+    float *dst = hp + n * hp_stride + kPHist;
+    const float xv = bq4_x(in, in_stride, C, n, t);
+    const float pre0 = M0[t];
+    const float xp = __shfl_up_sync(0xffffffffu, xv, 1), mp = __shfl_up_sync(0xffffffffu, pre0, 1);
+    float a = pre0, b;
+    if ((lane & (kBq4It - 1)) == 0) b = M1[t / kBq4It];
+    else b = __fmaf_rn(-0.99600f, xp + mp, xp);                     // the lane's own m1' of the previous sample
+    bool hz = false;
+    const float yv = biquad_step_eft_x(xv, a, b, hz);
+    hz |= __float_as_uint(a) != __float_as_uint(M0[t + 1]);
+    const float b_lane = ((lane + 1) & (kBq4It - 1)) == 0 ? M1[(t + 1) / kBq4It] : __fmaf_rn(-0.99600f, yv, xv);
+    hz |= __float_as_uint(b) != __float_as_uint(b_lane);
+    if (!__any_sync(0xffffffffu, hz)) { dst[t] = yv; return; }
+    if (lane == 0) {                                                // replay with the reference's double arithmetic
+        float r0 = M0[t], r1 = M1[t / kBq4It];
+        for (int i = 0; i < kBq4Blk; i++) dst[t + i] = biquad_step_x(bq4_x(in, in_stride, C, n, t + i), r0, r1);
+        if (__float_as_uint(r0) != __float_as_uint(M0[t + kBq4Blk]) || __float_as_uint(r1) != __float_as_uint(M1[(t + kBq4Blk) / kBq4It]))
+            atomicMin(&broken[n], (int)vb);                         // the fast step was wrong somewhere in this block
+    }
+}
+__global__ void __launch_bounds__(32) k_rn_biquad_fixup(const float *__restrict__ in, size_t in_stride, int C, int Q,
+                                                        const float *__restrict__ pm0, size_t pm0_stride,
+                                                        const float *__restrict__ pm1, size_t pm1_stride,
+                                                        const int *__restrict__ broken, RnPersist *persist,
+                                                        float *__restrict__ hp, size_t hp_stride, size_t N) {
+    const size_t n = blockIdx.x;
+    if (n >= N || threadIdx.x != 0) return;
+    const int kb = broken[n];
+    if (kb == kBq4None) return;
+    const size_t T = (size_t)Q * kFrame, t0 = (size_t)kb * kBq4Blk;
+    float m0 = pm0[n * pm0_stride + t0], m1 = pm1[n * pm1_stride + t0 / kBq4It];   // every block before kb verified: this state is true
+    float *dst = hp + n * hp_stride + kPHist;
+    for (size_t t = t0; t < T; t++) dst[t] = biquad_step_x(bq4_x(in, in_stride, C, n, t), m0, m1);
+    persist[n].biq[0] = m0; persist[n].biq[1] = m1;
+}
+
 // Throughput regime (many states): the same protocol with a state per LANE.  Warp 0 walks the chains of 32 states in
 // lock-step (the fast step costs the warp the same instructions for 32 chains as for one -- with one chain per CTA the
 // biquad was a quarter of all instructions the GPU issued at 592 streams), warps 1..7 verify the previous block (state =
@@ -1107,6 +1323,9 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
 #define RN_A(p, n) if (rc == FVAD_OK) rc = rn_alloc(r, &p, (n))
     RN_A(r->persist, r->N);
     RN_A(r->hp_hist, r->N * kPHist);
+    if (r->N < 1000) {                                            // the fourth biquad form's records (from 1000 states on: a state per lane)
+        RN_A(r->bq_m0, r->N * r->bq_m0_stride()); RN_A(r->bq_m1, r->N * r->bq_m1_stride()); RN_A(r->bq_broken, r->N);
+    }
     RN_A(r->cepsc, r->N * (8 + r->Qcap) * kNB);
     RN_A(r->head, NQ * kFrame); RN_A(r->tail, r->N * (1 + r->Qcap) * kFrame);
     for (RnSlot &s : r->slots) {
@@ -1159,6 +1378,10 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
         }
         FVAD_BQ3_VARIANTS(FVAD_BQ3_ATTR)
 #undef FVAD_BQ3_ATTR
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0));
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0));
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0));
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0));
         if (e != cudaSuccess) rc = set_error(FVAD_ECUDA, "cudaFuncSetAttribute: %s (is this an sm_100 device?)", cudaGetErrorString(e));
     }
     if (rc == FVAD_OK) rc = rnnoise_batch_reset(r, 0);
@@ -1215,8 +1438,34 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
         // throttle on low-grid kernels that vanishes from 148 CTAs on
         size_t bq_grid = N;
         if (const char *e = debug_knob("bq_grid_min")) bq_grid = std::max<size_t>(N, (size_t)atoi(e));
-        int form = 1;                                         // knob bq_form: 1 = first form (default: still the fastest, see below), 2 = light chain lane, 3 = named-barrier hand-over
+        // knob bq_form: 4 = chain and verification in separate kernels, 1 = chain lane + verifying warps in one CTA, 2 = light
+        // chain lane, 3 = named-barrier hand-over.  Form 4 where every chain has an SM to itself (latency regime: 233.5 ms against
+        // 246.2 ms per 240 s of 20 streams); with other stages' CTAs on the same SM its lone warp loses more than form 1's CTA
+        // does (x real time, form 4 / form 1: 148 streams 66.8k / 72.2k, 296: 105.4k / 109.6k, 592: 114.5k / 118.3k).
+        int form = lat ? 4 : 1;
         if (const char *e = debug_knob("bq_form")) form = atoi(e);
+        if (form == 4 && !r->bq_m0) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_form=4: not available from 1000 states on");
+        if (form == 4) {
+            launched = true;
+            const size_t T = Qs * kFrame;
+            int it = 32;                                      // knob bq_iter: samples per iteration of the lane's loop (measured, 20 streams x 240 s: 16: 245.6 ms, 32: 233.5 ms; the first form: 246.2 ms)
+            if (const char *e = debug_knob("bq_iter")) it = atoi(e);
+#define FVAD_BQ4_GO(II, MM)                                                                                              \
+            FVAD_LAUNCH_NAMED("k_rn_biquad", (k_rn_biquad_chain<II, MM>), (unsigned)N, 32, hog_on * biquad_smem_hog(0), st, d_in, in_stride, C, \
+                              (int)Qs, Tn, r->persist, r->bq_m0, r->bq_m0_stride(), r->bq_m1, r->bq_m1_stride(), r->bq_broken, N, dbg)
+            if (it == 32 && C == 1) FVAD_BQ4_GO(32, true);
+            else if (it == 32) FVAD_BQ4_GO(32, false);
+            else if (it == 16 && C == 1) FVAD_BQ4_GO(16, true);
+            else if (it == 16) FVAD_BQ4_GO(16, false);
+#undef FVAD_BQ4_GO
+            else return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_iter=%d: 16 or 32", it);
+            FVAD_LAUNCH(k_rn_biquad_verify, dim3((unsigned)ceil_div(T / kBq4Blk, (size_t)kBq4VerWarps), (unsigned)N), 32 * kBq4VerWarps, 0, st,
+                        d_in, in_stride, C, (int)Qs, r->bq_m0, r->bq_m0_stride(), r->bq_m1, r->bq_m1_stride(), r->bq_broken, s.hp,
+                        r->hp_stride(), N);
+            if (!(dbg & 64))                                   // (test only: bq_dbg=64 leaves a planted fault unrepaired)
+            FVAD_LAUNCH(k_rn_biquad_fixup, (unsigned)N, 32, 0, st, d_in, in_stride, C, (int)Qs, r->bq_m0, r->bq_m0_stride(), r->bq_m1,
+                        r->bq_m1_stride(), r->bq_broken, r->persist, s.hp, r->hp_stride(), N);
+        }
         const bool v2 = form == 2;
 #define FVAD_BQ3_GO(BB)                                                                                                  \
         if (form == 3 && !launched && BQ == BB) {                                                                        \

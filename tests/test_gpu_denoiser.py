@@ -39,9 +39,9 @@ def test_denoiser_batch_bit_exact(fv, checker, rnn_rg, knobs):
                                           (240, 1, 2), (48, 1, 3), (160, 1, 3)])
 def test_denoiser_biquad_block_sizes(fv, checker, bq, roll, form, knobs):
     """The biquad kernel's block length (samples between two verdicts of the verifying warps; 96 by default), the form
-    of the chain lane's loop (unrolled / rolled) and the kernel's form (3, the default: chain warp and verifying warps
-    hand blocks over through named barriers without waiting for each other; 2: lock-step, the lane publishes only m0;
-    1: the first form) change how the chain is cut into verified pieces and who stores what, never the result."""
+    of the chain lane's loop (unrolled / rolled) and the kernel's form (1: chain lane and verifying warps of one CTA in
+    lock-step; 2: the lane publishes only m0; 3: hand-over through named barriers) change how the chain is cut into
+    verified pieces and who stores what, never the result.  (Form 4, the default, has its own test below.)"""
     knobs(bq_block=str(bq), bq_roll=str(roll), bq_form=str(form))
     S, secs = 3, 6
     pcm = np.stack([synth(fv, 40 + s, secs) for s in range(S)])
@@ -51,6 +51,30 @@ def test_denoiser_biquad_block_sizes(fv, checker, bq, roll, form, knobs):
         wo, wv = checker.denoise_stream(pcm[s])
         assert np.array_equal(vad[s], wv), (s, np.nonzero(vad[s] != wv)[0][:5])
         assert np.array_equal(out[s], wo), (s, np.abs(out[s] - wo).max())
+
+
+@pytest.mark.parametrize("it,dbg,exact", [(16, 0, True), (32, 0, True), (16, 32, True), (32, 32, True), (16, 96, False)])
+def test_denoiser_biquad_separate_kernels(fv, checker, it, dbg, exact, knobs):
+    """The default form of the biquad below 1000 states (bq_form=4): the chain lane alone in one kernel (16 or 32 samples per
+    loop iteration), verification + replay in a second, a fix-up in a third.  bq_dbg=32 plants a WRONG state in the chain of
+    state 0 at frame 40 of every call: the verifying kernel must find it and the fix-up kernel recompute the rest of the
+    call, so the result stays the reference's; with the fix-up switched off as well (bq_dbg=96) it must NOT be -- which
+    shows that the fix-up path is what was exercised.  A second call continues from the (repaired) carried state."""
+    knobs(bq_form="4", bq_iter=str(it), bq_dbg=str(dbg))
+    S, secs = 3, 6
+    pcm = np.stack([synth(fv, 40 + s, secs) for s in range(S)])
+    d = fv.DenoiserBatch(S)
+    out, vad = d.run(pcm)
+    pcm2 = np.stack([synth(fv, 40 + s, 1, first=secs * 48000) for s in range(S)])
+    out2, vad2 = d.run(pcm2)
+    for s in range(S):
+        wo, wv = checker.denoise_stream(np.concatenate([pcm[s], pcm2[s]]))
+        go, gv = np.concatenate([out[s], out2[s]]), np.concatenate([vad[s], vad2[s]])
+        if exact or s != 0:
+            assert np.array_equal(gv, wv), (s, np.nonzero(gv != wv)[0][:5])
+            assert np.array_equal(go, wo), (s, np.abs(go - wo).max())
+        else:
+            assert not np.array_equal(go, wo), "the planted fault must matter when nothing repairs it"
 
 
 def test_denoiser_biquad_state_per_lane(fv, checker, knobs):
