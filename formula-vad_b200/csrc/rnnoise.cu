@@ -62,10 +62,10 @@ struct RnnoiseBatch {
     // stage A, fourth biquad form: what the chain kernel publishes for the verifying kernel (one tile; stage A of the next
     // tile follows on the same stream)
     float *bq_m0 = nullptr;        // [N][bq_m0_stride()]  m0 before every sample of the tile, then the end state's
-    float *bq_m1 = nullptr;        // [N][bq_m1_stride()]  m1 before every 16-sample iteration, then the end state's
+    float *bq_m1 = nullptr;        // [N][bq_m1_stride()]  m1 before every 8th sample, then the end state's
     int *bq_broken = nullptr;      // [N]  first block whose replay disagreed with the chain (kBq4None: none)
     size_t bq_m0_stride() const { return Qcap * kFrame + 4; }
-    size_t bq_m1_stride() const { return Qcap * (kFrame / 16) + 4; }
+    size_t bq_m1_stride() const { return Qcap * (kFrame / 8) + 4; }
     float *cepsc = nullptr;        // [N][8 + Qcap][22]  stage B
     float *head = nullptr;         // [N][Qcap][480]     stage D
     float *tail = nullptr;         // [N][1 + Qcap][480] stage D
@@ -662,9 +662,11 @@ __global__ void __launch_bounds__(bq_threads(BQ)) k_rn_biquad_v3(const float *__
 //    "scale the whole set (first use), THEN reload it", which the register dependence itself enforces.
 //  * a taken branch costs the lone warp ~17 cycles (instruction fetch): the fast path closes the loop itself and the
 //    denormal path sits behind it; the not-taken branch between head and body also keeps the head's loads at the head.
-//  * what is left per 32-sample iteration: 32 scalings + 8 loads + pointer arithmetic at the head while the chain idles.
-// 39.8 cycles per sample (233.5 ms per 240 s of 20 streams) against 42.0 for the first form: the loop body runs at 34.2.
-constexpr int kBq4It = 16, kBq4ItPerFrame = kFrame / kBq4It, kBq4Blk = 32, kBq4VerWarps = 8;
+//  * what is left at the head while the chain idles: the scalings (packed, FMUL2: two samples per instruction), the 16-byte
+//    loads (the LSU takes one every 4 cycles) and the pointer arithmetic.
+// 39.4 cycles per sample (230.9 ms per 240 s of 20 streams, 24-sample iterations) against 42.0 for the first form; the loop
+// body itself runs at 34.2.
+constexpr int kBq4It = 8, kBq4ItPerFrame = kFrame / kBq4It, kBq4Blk = 32, kBq4VerWarps = 8;   // kBq4It: samples between two records of m1
 constexpr int kBq4None = 0x7fffffff;
 static_assert(kFrame % kBq4Blk == 0 && kBq4Blk % kBq4It == 0, "verify blocks tile the frame");
 __device__ __forceinline__ bool bq4_tiny(float m0, float m1) {
@@ -719,7 +721,10 @@ __global__ void __launch_bounds__(32) k_rn_biquad_chain(const float *__restrict_
     auto head = [&](float4 (&xs)[kQuads]) {
 #pragma unroll
         for (int k = 0; k < kQuads; k++) {
-            xs[k].x = xr[k].x * 32767.0f; xs[k].y = xr[k].y * 32767.0f; xs[k].z = xr[k].z * 32767.0f; xs[k].w = xr[k].w * 32767.0f;
+            // two packed multiplies per quad (FMUL2: each half rounded like the scalar product): half the head's issue slots
+            const float2 lo = __fmul2_rn(make_float2(xr[k].x, xr[k].y), make_float2(32767.0f, 32767.0f));
+            const float2 hi = __fmul2_rn(make_float2(xr[k].z, xr[k].w), make_float2(32767.0f, 32767.0f));
+            xs[k] = make_float4(lo.x, lo.y, hi.x, hi.y);
         }
         more = h + 1 < H;
         const float *pl;
@@ -1271,6 +1276,7 @@ static size_t biquad_smem_hog(size_t static_bytes) {
 }
 static size_t g_bq_static[512];                              // static shared memory per BQ variant (cudaFuncGetAttributes)
 static size_t g_bq2_static[512], g_bq3_static[512];
+#define FVAD_BQ4_ITERS(X) X(16) X(24) X(32) X(48)
 #define FVAD_BQ2_VARIANTS(X) X(48) X(96) X(160) X(240)
 #define FVAD_BQ3_VARIANTS(X) X(48) X(96) X(160)
 constexpr size_t kSmemAna = (size_t)kWarpsPerCta * kScrAna * sizeof(float);
@@ -1378,10 +1384,11 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
         }
         FVAD_BQ3_VARIANTS(FVAD_BQ3_ATTR)
 #undef FVAD_BQ3_ATTR
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0));
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0));
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0));
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0));
+#define FVAD_BQ4_ATTR(II)                                                                                                 \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<II, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0)); \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<II, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0));
+        FVAD_BQ4_ITERS(FVAD_BQ4_ATTR)
+#undef FVAD_BQ4_ATTR
         if (e != cudaSuccess) rc = set_error(FVAD_ECUDA, "cudaFuncSetAttribute: %s (is this an sm_100 device?)", cudaGetErrorString(e));
     }
     if (rc == FVAD_OK) rc = rnnoise_batch_reset(r, 0);
@@ -1448,17 +1455,18 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
         if (form == 4) {
             launched = true;
             const size_t T = Qs * kFrame;
-            int it = 32;                                      // knob bq_iter: samples per iteration of the lane's loop (measured, 20 streams x 240 s: 16: 245.6 ms, 32: 233.5 ms; the first form: 246.2 ms)
+            int it = 24;                                      // knob bq_iter: samples per iteration of the lane's loop (measured, ms per 240 s of 20 streams: 16: 241.7, 24: 230.9, 32: 243.0, 48: 230.5; the first form: 246.6 -- beyond the head's amortisation the differences are ptxas' scheduling of the body)
             if (const char *e = debug_knob("bq_iter")) it = atoi(e);
 #define FVAD_BQ4_GO(II, MM)                                                                                              \
             FVAD_LAUNCH_NAMED("k_rn_biquad", (k_rn_biquad_chain<II, MM>), (unsigned)N, 32, hog_on * biquad_smem_hog(0), st, d_in, in_stride, C, \
                               (int)Qs, Tn, r->persist, r->bq_m0, r->bq_m0_stride(), r->bq_m1, r->bq_m1_stride(), r->bq_broken, N, dbg)
-            if (it == 32 && C == 1) FVAD_BQ4_GO(32, true);
-            else if (it == 32) FVAD_BQ4_GO(32, false);
-            else if (it == 16 && C == 1) FVAD_BQ4_GO(16, true);
-            else if (it == 16) FVAD_BQ4_GO(16, false);
+            bool go4 = false;
+#define FVAD_BQ4_PICK(II)                                                                                                 \
+            if (!go4 && it == II) { go4 = true; if (C == 1) FVAD_BQ4_GO(II, true); else FVAD_BQ4_GO(II, false); }
+            FVAD_BQ4_ITERS(FVAD_BQ4_PICK)
+#undef FVAD_BQ4_PICK
+            if (!go4) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_iter=%d: 16, 24, 32 or 48", it);
 #undef FVAD_BQ4_GO
-            else return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_iter=%d: 16 or 32", it);
             FVAD_LAUNCH(k_rn_biquad_verify, dim3((unsigned)ceil_div(T / kBq4Blk, (size_t)kBq4VerWarps), (unsigned)N), 32 * kBq4VerWarps, 0, st,
                         d_in, in_stride, C, (int)Qs, r->bq_m0, r->bq_m0_stride(), r->bq_m1, r->bq_m1_stride(), r->bq_broken, s.hp,
                         r->hp_stride(), N);

@@ -53,9 +53,9 @@ def test_denoiser_biquad_block_sizes(fv, checker, bq, roll, form, knobs):
         assert np.array_equal(out[s], wo), (s, np.abs(out[s] - wo).max())
 
 
-@pytest.mark.parametrize("it,dbg,exact", [(16, 0, True), (32, 0, True), (16, 32, True), (32, 32, True), (16, 96, False)])
+@pytest.mark.parametrize("it,dbg,exact", [(16, 0, True), (24, 0, True), (32, 0, True), (48, 0, True), (16, 32, True), (24, 32, True), (48, 32, True), (24, 96, False)])
 def test_denoiser_biquad_separate_kernels(fv, checker, it, dbg, exact, knobs):
-    """The default form of the biquad below 1000 states (bq_form=4): the chain lane alone in one kernel (16 or 32 samples per
+    """The default form of the biquad in the latency regime (bq_form=4): the chain lane alone in one kernel (16 to 48 samples per
     loop iteration), verification + replay in a second, a fix-up in a third.  bq_dbg=32 plants a WRONG state in the chain of
     state 0 at frame 40 of every call: the verifying kernel must find it and the fix-up kernel recompute the rest of the
     call, so the result stays the reference's; with the fix-up switched off as well (bq_dbg=96) it must NOT be -- which
