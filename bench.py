@@ -65,7 +65,7 @@ ALGO_BYTES = {
     "k_rn_out": (3 * 1920, "frame"),
     "k_vadm": (12, "stft_frame"),
 }
-BIQUAD_CHAIN_OPS = 7        # dependent f32 operations per sample on the chain lane (rn_core.cuh biquad_step_fast)
+BIQUAD_CHAIN_OPS = 7        # dependent f32 operations per sample on the chain lane (rn_core.cuh biquad_chain_step)
 F32_OP_CYCLES = 4           # dependent-issue latency of FADD / FMUL / FFMA on sm_100 (B300_MICROARCH.md)
 
 
@@ -379,7 +379,7 @@ def b200_arm(args):
             bound = BIQUAD_CHAIN_OPS * F32_OP_CYCLES
             roofline = {"kernel": name, "bound": "latency", "achieved": cyc, "peak": bound, "unit": "cycles/sample (lower is better)",
                         "frac": bound / cyc, "cycles_per_sample": cyc, "chain_cycles": bound,
-                        "chain": f"{BIQUAD_CHAIN_OPS} dependent f32 operations x {F32_OP_CYCLES} cycles (rn_core.cuh biquad_step_fast)",
+                        "chain": f"{BIQUAD_CHAIN_OPS} dependent f32 operations x {F32_OP_CYCLES} cycles (rn_core.cuh biquad_chain_step)",
                         "sm_mhz": mhz, "avg_launch_ms": 1e3 * dur_s, "launches": info["launches"], "share_of_step": shares[name],
                         "critical_path_share": info["total_ms"] / prof_ms, "traffic": traffic, "hbm": hbm,
                         "note": "sample-sequential IIR per stream: the binding limit is the dependent chain, not HBM or FLOPs "
