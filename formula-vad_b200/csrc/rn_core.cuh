@@ -1065,7 +1065,8 @@ struct RnnF2 { float x, y; };                              // two consecutive ve
 // EXPERIMENT ONLY (knob rnn_tolerance_mode, never the default): what a tensor-core formulation of the
 // gate contractions would do to the numbers, without building one.  An MMA does not keep the reference's summation order
 // and takes its activations in reduced precision; the int8 weights are exact in every MMA input type.
-//   0  exact: in-order f32 accumulation of f32 products (the product path)
+//   0  exact: in-order f32 accumulation of f32 products (the product path; modes 1-3 live in an instantiation of their own,
+//      k_rn_rnn<1, 1, true>: a run-time switch inside the product kernel's chains cost it 24 % at 592 streams)
 //   1  f32 products, accumulated in FOUR interleaved partial sums (any GEMM's freedom to reassociate)
 //   2  as 1, activations rounded to TF32 (10-bit mantissa) before the product
 //   3  as 1, activations rounded to BF16 (7-bit mantissa)
@@ -1120,9 +1121,9 @@ RN_HD void rnn_chain_tol(const unsigned *W2, int cols, int col, const float *v, 
     for (int r = 0; r < R; r++) sum[r] += (part[r][0] + part[r][1]) + (part[r][2] + part[r][3]);
 }
 
-template <int R>
+template <int R, bool TOL = false>
 RN_HD void rnn_chain(const unsigned *W2, int cols, int col, const float *v, int j0, int j1, float (&sum)[R]) {
-    if (const int mode = rnn_tolerance_mode()) { rnn_chain_tol<R>(W2, cols, col, v, nullptr, j0, j1, sum, mode); return; }
+    if (TOL) { rnn_chain_tol<R>(W2, cols, col, v, nullptr, j0, j1, sum, rnn_tolerance_mode()); return; }   // the experiment's instantiation only
     RnnBlk<R> cur, nxt;
     RnnWBlk wc, wn;
     rnn_w_load(wc, W2, cols, col, j0);
@@ -1144,9 +1145,9 @@ RN_HD void rnn_chain(const unsigned *W2, int cols, int col, const float *v, int 
     }
 }
 // recurrent part of the candidate gate: sum += (W[j][col]*state[j-M])*r[j-M]  (rnn.c:147); same blocking
-template <int R>
+template <int R, bool TOL = false>
 RN_HD void rnn_chain_r(const unsigned *W2, int cols, int col, const float *v, const float *rg, int M, int J, float (&sum)[R]) {
-    if (const int mode = rnn_tolerance_mode()) { rnn_chain_tol<R>(W2, cols, col, v, rg - M, M, J, sum, mode); return; }
+    if (TOL) { rnn_chain_tol<R>(W2, cols, col, v, rg - M, M, J, sum, rnn_tolerance_mode()); return; }
     RnnBlk<R> cur, nxt, gcur, gnxt;                         // g*: the reset-gate values
     RnnWBlk wc, wn;
     rnn_w_load(wc, W2, cols, col, M);
@@ -1173,7 +1174,7 @@ RN_HD void rnn_chain_r(const unsigned *W2, int cols, int col, const float *v, co
 constexpr float kWScale = 1.f / 256;
 
 // One GRU layer: v = [inputs(M) | state(N)], zr/hp/hn scratch (all of state 0; state r at + r*kRv_end).  Two CTA phases.
-template <int R>
+template <int R, bool TOL = false>
 RN_HD void rnn_gru_cta(const unsigned *W2, const float *bias, const float *tansig, int layer, float *v, float *zr, float *hp,
                        float *hn) {
     const RnnLayer L = rnn_layer(layer);
@@ -1186,11 +1187,11 @@ RN_HD void rnn_gru_cta(const unsigned *W2, const float *bias, const float *tansi
 #pragma unroll
             for (int r = 0; r < R; r++) s[r] = bl[tid];
             if (tid < 2 * N) {                               // update and reset gates (rnn.c:119-139)
-                rnn_chain<R>(Wl, L.cols, tid, v, 0, L.J, s);
+                rnn_chain<R, TOL>(Wl, L.cols, tid, v, 0, L.J, s);
 #pragma unroll
                 for (int r = 0; r < R; r++) zr[r * kRv_end + tid] = sigmoid_approx(tansig, kWScale * s[r]);
             } else {                                         // candidate: input part (rnn.c:143-145)
-                rnn_chain<R>(Wl, L.cols, tid, v, 0, L.M, s);
+                rnn_chain<R, TOL>(Wl, L.cols, tid, v, 0, L.M, s);
 #pragma unroll
                 for (int r = 0; r < R; r++) hp[r * kRv_end + tid - 2 * N] = s[r];
             }
@@ -1201,7 +1202,7 @@ RN_HD void rnn_gru_cta(const unsigned *W2, const float *bias, const float *tansi
             float s[R];
 #pragma unroll
             for (int r = 0; r < R; r++) s[r] = hp[r * kRv_end + tid];
-            rnn_chain_r<R>(Wl, L.cols, 2 * N + tid, v, zr + N, L.M, L.J, s);
+            rnn_chain_r<R, TOL>(Wl, L.cols, 2 * N + tid, v, zr + N, L.M, L.J, s);
 #pragma unroll
             for (int r = 0; r < R; r++) {
                 float x = kWScale * s[r];
@@ -1218,7 +1219,7 @@ template <int R> struct RnnOut { float *gains[R]; float *vad[R]; };
 // Whole network for one frame of each of the R states.  scr = vectors (kRv_* offsets) of state 0, state r at
 // + r*kRv_end; the frame's features are already at kRv_feat..+42.  Bit r of `act` says state r has a frame this
 // round: an inactive state is computed on stale inputs (harmless) but neither its GRU states nor any output is written.
-template <int R>
+template <int R, bool TOL = false>
 RN_HD void rnn_frame_cta(const unsigned *W2, const float *bias, const float *tansig, float *scr, unsigned act, const RnnOut<R> &out) {
     float *feat = scr + kRv_feat, *v1 = scr + kRv_v1, *v3 = scr + kRv_v3, *v4 = scr + kRv_v4;
     float *zr = scr + kRv_zr, *hp = scr + kRv_hp, *hn = scr + kRv_hn;
@@ -1228,12 +1229,12 @@ RN_HD void rnn_frame_cta(const unsigned *W2, const float *bias, const float *tan
             float s[R];
 #pragma unroll
             for (int r = 0; r < R; r++) s[r] = bias[L.b_off + tid];
-            rnn_chain<R>(W2 + L.w_off / 2, L.cols, tid, feat, 0, L.J, s);
+            rnn_chain<R, TOL>(W2 + L.w_off / 2, L.cols, tid, feat, 0, L.J, s);
 #pragma unroll
             for (int r = 0; r < R; r++) v1[r * kRv_end + tid] = tansig_approx(tansig, kWScale * s[r]);
         }
     RN_CTA_END
-    rnn_gru_cta<R>(W2, bias, tansig, kL_vad, v1, zr, hp, hn);
+    rnn_gru_cta<R, TOL>(W2, bias, tansig, kL_vad, v1, zr, hp, hn);
     RN_CTA_PHASE
 #pragma unroll
         for (int r = 0; r < R; r++) {
@@ -1250,13 +1251,13 @@ RN_HD void rnn_frame_cta(const unsigned *W2, const float *bias, const float *tan
 #pragma unroll
             for (int r = 0; r < R; r++) s[r] = bias[L.b_off];
             // its input is the NEW vad state, read from hn (v1[24..] is being written by warp 0)
-            rnn_chain<R>(W2 + L.w_off / 2, L.cols, 0, hn, 0, L.J, s);
+            rnn_chain<R, TOL>(W2 + L.w_off / 2, L.cols, 0, hn, 0, L.J, s);
 #pragma unroll
             for (int r = 0; r < R; r++)
                 if ((act >> r) & 1) *out.vad[r] = sigmoid_approx(tansig, kWScale * s[r]);
         }
     RN_CTA_END
-    rnn_gru_cta<R>(W2, bias, tansig, kL_noise, v3, zr, hp, hn);
+    rnn_gru_cta<R, TOL>(W2, bias, tansig, kL_noise, v3, zr, hp, hn);
     RN_CTA_PHASE
         if (tid < 48) {                                                                      // noise_gru_state
 #pragma unroll
@@ -1267,14 +1268,14 @@ RN_HD void rnn_frame_cta(const unsigned *W2, const float *bias, const float *tan
             }
         }
     RN_CTA_END
-    rnn_gru_cta<R>(W2, bias, tansig, kL_den, v4, zr, hp, hn);
+    rnn_gru_cta<R, TOL>(W2, bias, tansig, kL_den, v4, zr, hp, hn);
     RN_CTA_PHASE
         if (tid < 22) {                                      // denoise_output, sigmoid (rnn.c:177) on the NEW denoise state (hn)
             const RnnLayer L = rnn_layer(kL_out);
             float s[R];
 #pragma unroll
             for (int r = 0; r < R; r++) s[r] = bias[L.b_off + tid];
-            rnn_chain<R>(W2 + L.w_off / 2, L.cols, tid, hn, 0, L.J, s);
+            rnn_chain<R, TOL>(W2 + L.w_off / 2, L.cols, tid, hn, 0, L.J, s);
 #pragma unroll
             for (int r = 0; r < R; r++)
                 if ((act >> r) & 1) out.gains[r][tid] = sigmoid_approx(tansig, kWScale * s[r]);

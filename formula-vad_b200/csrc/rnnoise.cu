@@ -635,8 +635,8 @@ __global__ void __launch_bounds__(bq_threads(BQ)) k_rn_biquad_v3(const float *__
     }
 }
 
-// Fourth form (knob bq_form=4, the default in the latency regime: every chain on an SM of its own): the chain and its
-// verification are SEPARATE KERNELS.  In the chain-per-CTA kernels above the lane's loop costs 41.6-42.6 cycles per sample
+// Fourth form (knob bq_form=4; the fifth form below, the default in the latency regime, is this one with a staging warp): the
+// chain and its verification are SEPARATE KERNELS.  In the chain-per-CTA kernels above the lane's loop costs 41.6-42.6 cycles per sample
 // whatever is switched off beside it; tools/ubench/chain_mix.cu runs the same step alone at 32-33.
 //   k_rn_biquad_chain   one warp per state, lane 0 only: reads its PCM straight from global memory (16-byte loads one
 //                       iteration ahead, L2 prefetch six frames ahead), runs biquad_chain_step, and publishes m0 before every
@@ -790,6 +790,132 @@ __global__ void __launch_bounds__(32) k_rn_biquad_chain(const float *__restrict_
         }
         foot();
         if (!more) break;
+    }
+    mo[0] = m0;                                                     // the end state closes both records
+    m1o[0] = m1;
+    persist[n].biq[0] = m0; persist[n].biq[1] = m1;
+}
+
+// Fifth form (knob bq_form=5): form 4 with a STAGING WARP.  Warp 1 copies the state's frames from global memory into a ring
+// of four frames in shared memory, already scaled by 32767 (coalesced loads, 15 samples per lane and frame), up to three
+// frames ahead of the chain; lane 0 of warp 0 reads its samples from the ring.  A shared-memory load lands in ~30 cycles, so
+// the registers of a quad can be reloaded right after the quad has been consumed -- younger loads on the shared scoreboard
+// are done long before the next first use -- and the loop has NO head: no scaling, no global loads, no pointer arithmetic on
+// the chain's warp.  The two warps meet at no barrier: two counters in shared memory (frames staged / frames consumed), read
+// once per frame.  Records, verification and fix-up are form 4's.  36.3 cycles per sample with 48-sample iterations (form 4:
+// 39.4, form 1: 42.0); the body's asymptote is 35.7 -- what is left against the 28-cycle chain is ptxas' order of the lane's
+// off-chain instructions.
+constexpr int kBq5Ring = 4;
+// a shared-memory load by its 32-bit shared address (formed ONCE: from a generic pointer the compiler re-derives the shared
+// window with S2UR SR_CgaCtaId in every iteration, ~30 cycles the lane waits for)
+__device__ __forceinline__ float4 bq5_lds(unsigned a) {
+    float4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+template <int IT>
+__global__ void __launch_bounds__(64) k_rn_biquad_chain_s(const float *__restrict__ in, size_t in_stride, int C, int Q,
+                                                          RnPersist *persist, float *__restrict__ pm0, size_t pm0_stride,
+                                                          float *__restrict__ pm1, size_t pm1_stride, int *__restrict__ broken,
+                                                          size_t N, int dbg) {
+    static_assert(kFrame % IT == 0 && IT % kBq4It == 0, "iterations tile the frame");
+    constexpr int kQuads = IT / 4, kItPerFrame = kFrame / IT, kRingFloats = kBq5Ring * kFrame;
+    __shared__ __align__(16) float ring[kRingFloats];
+    __shared__ int s_ready, s_done;                                 // frames staged / frames consumed so far
+    const size_t n = blockIdx.x;
+    if (n >= N) return;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) { s_ready = 0; s_done = 0; broken[n] = kBq4None; }
+    __syncthreads();
+    volatile int *v_ready = &s_ready, *v_done = &s_done;
+    if (warp == 1) {                                                // ---- the staging warp
+        for (int q = 0; q < Q; q++) {
+            const float *src = in + (n * C + (q % C)) * in_stride + (size_t)(q / C) * kFrame;
+            float v[kFrame / 32];
+#pragma unroll
+            for (int i = 0; i < kFrame / 32; i++) v[i] = __ldg(src + lane + 32 * i);
+            while (q - *v_done >= kBq5Ring) __nanosleep(100);      // the slot is free once its frame has been consumed
+            float *dst = ring + (q % kBq5Ring) * kFrame;
+#pragma unroll
+            for (int i = 0; i < kFrame / 32; i++) dst[lane + 32 * i] = v[i];
+            __threadfence_block();
+            __syncwarp();
+            if (lane == 0) *v_ready = q + 1;
+        }
+        return;
+    }
+    if (lane != 0 || Q <= 0) return;
+    // ---- the chain lane
+    float m0 = persist[n].biq[0], m1 = persist[n].biq[1];
+    float *mo = pm0 + n * pm0_stride, *m1o = pm1 + n * pm1_stride;
+    while (*v_ready < 1) __nanosleep(20);
+    __threadfence_block();
+    auto scale = [](float4 v) {                                     // two packed multiplies per quad (each half rounded like the scalar product)
+        const float2 lo = __fmul2_rn(make_float2(v.x, v.y), make_float2(32767.0f, 32767.0f));
+        const float2 hi = __fmul2_rn(make_float2(v.z, v.w), make_float2(32767.0f, 32767.0f));
+        return make_float4(lo.x, lo.y, hi.x, hi.y);
+    };
+    float4 xq[kQuads], xn[kQuads];                                  // scaled samples of the iteration about to run; raw samples of the next
+#pragma unroll
+    for (int k = 0; k < kQuads; k++) xq[k] = scale(*reinterpret_cast<const float4 *>(ring + 4 * k));
+    bool tiny = bq4_tiny(m0, m1);
+    unsigned ring_s;                                                // (opaque: the compiler would re-derive it inside the loop)
+    asm volatile("mov.u32 %0, %1;" : "=r"(ring_s) : "r"((unsigned)__cvta_generic_to_shared(ring)));
+    int off = 0;                                                    // ring offset of the iteration about to run
+#pragma unroll 1
+    for (int q = 0; q < Q; q++) {
+        const int need = q + 2 < Q ? q + 2 : Q;                     // the frame's last iteration already reads the next frame
+        while (*v_ready < need) __nanosleep(20);
+        __threadfence_block();
+        if ((dbg & 32) && n == 0 && q == 40) m0 = __uint_as_float(__float_as_uint(m0) ^ 0x1000u);   // test only: a wrong state
+        int it = 0;
+#pragma unroll 1
+        for (;;) {
+            off += IT;
+            if (off == kRingFloats) off = 0;
+            const unsigned nx = ring_s + 4u * (unsigned)off;        // after the very last iteration: stale data, never used
+            it++;
+#pragma unroll
+            for (int k = 0; k < kQuads; k++) xn[k] = bq5_lds(nx + 16u * k);
+            if (__builtin_expect(!tiny, 1)) {
+#pragma unroll
+                for (int k = 0; k < kQuads; k++) {
+                    if (k % (kBq4It / 4) == 0) m1o[k / (kBq4It / 4)] = m1;
+                    const float4 xs = xq[k];
+                    float4 pm;
+                    pm.x = m0; biquad_chain_step(xs.x, m0, m1);
+                    pm.y = m0; biquad_chain_step(xs.y, m0, m1);
+                    pm.z = m0; biquad_chain_step(xs.z, m0, m1);
+                    pm.w = m0; biquad_chain_step(xs.w, m0, m1);
+                    *reinterpret_cast<float4 *>(mo + 4 * k) = pm;
+                    if (k == kQuads - 2) tiny = bq4_tiny(m0, m1);   // four samples early: the branch never waits for the chain
+                }
+#pragma unroll
+                for (int k = 0; k < kQuads; k++) xq[k] = scale(xn[k]);
+                mo += IT; m1o += IT / kBq4It;
+                if (it < kItPerFrame) continue;                     // the fast path closes the loop itself
+                break;
+            }
+            {                                                       // denormal tail of a silence: the reference's own arithmetic
+#pragma unroll
+                for (int k = 0; k < kQuads; k++) {
+                    if (k % (kBq4It / 4) == 0) m1o[k / (kBq4It / 4)] = m1;
+                    const float4 xs = xq[k];
+                    float4 pm;
+                    pm.x = m0; biquad_step_x(xs.x, m0, m1);
+                    pm.y = m0; biquad_step_x(xs.y, m0, m1);
+                    pm.z = m0; biquad_step_x(xs.z, m0, m1);
+                    pm.w = m0; biquad_step_x(xs.w, m0, m1);
+                    *reinterpret_cast<float4 *>(mo + 4 * k) = pm;
+                }
+                tiny = bq4_tiny(m0, m1);
+#pragma unroll
+                for (int k = 0; k < kQuads; k++) xq[k] = scale(xn[k]);
+            }
+            mo += IT; m1o += IT / kBq4It;
+            if (it >= kItPerFrame) break;
+        }
+        *v_done = q + 1;
     }
     mo[0] = m0;                                                     // the end state closes both records
     m1o[0] = m1;
@@ -1112,7 +1238,7 @@ __global__ void __launch_bounds__(32 * kWarpsPerCta) k_rn_cepsfeat(const float *
 // the weights and meet at no barrier after the start, so the narrow layers of one group (24..96 of its 288 threads busy)
 // overlap the wide layers of another.  The frame index and the 42 features of the NEXT round are fetched while this
 // round computes.
-template <int R, int G>
+template <int R, int G, bool TOL = false>
 __global__ void __launch_bounds__(kRnnThreads * G) k_rn_rnn(const unsigned *__restrict__ weights2, const float *__restrict__ bias,
                                                             const float *__restrict__ tansig, const float *__restrict__ feat,
                                                             const int *__restrict__ nzlist, const int *__restrict__ nz_tile,
@@ -1164,7 +1290,7 @@ __global__ void __launch_bounds__(kRnnThreads * G) k_rn_rnn(const unsigned *__re
             qa[r] = qb[r];
             qb[r] = j + 2 < nz[r] ? nzlist[(n0 + r) * Qcap + j + 2] : 0;
         }
-        rnn_frame_cta<R>(W2, b, ts, scr, act, out);
+        rnn_frame_cta<R, TOL>(W2, b, ts, scr, act, out);
     }
 #pragma unroll
     for (int r = 0; r < R; r++)
@@ -1276,7 +1402,7 @@ static size_t biquad_smem_hog(size_t static_bytes) {
 }
 static size_t g_bq_static[512];                              // static shared memory per BQ variant (cudaFuncGetAttributes)
 static size_t g_bq2_static[512], g_bq3_static[512];
-#define FVAD_BQ4_ITERS(X) X(16) X(24) X(32) X(48)
+#define FVAD_BQ4_ITERS(X) X(16) X(24) X(32) X(48) X(80)
 #define FVAD_BQ2_VARIANTS(X) X(48) X(96) X(160) X(240)
 #define FVAD_BQ3_VARIANTS(X) X(48) X(96) X(160)
 constexpr size_t kSmemAna = (size_t)kWarpsPerCta * kScrAna * sizeof(float);
@@ -1354,6 +1480,7 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<RR, GG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(RR * GG));
         FVAD_RNN_VARIANTS(FVAD_RNN_ATTR)
 #undef FVAD_RNN_ATTR
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_rnn<1, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rnn(1));
 #define FVAD_BQ_ATTR(BB, RL)                                                                                             \
         if (e == cudaSuccess) {                                                                                          \
             cudaFuncAttributes fa{};                                                                                     \
@@ -1389,6 +1516,10 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
         if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain<II, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(0));
         FVAD_BQ4_ITERS(FVAD_BQ4_ATTR)
 #undef FVAD_BQ4_ATTR
+#define FVAD_BQ5_ATTR(II)                                                                                                 \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain_s<II>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(kBq5Ring * kFrame * 4 + 64));
+        FVAD_BQ4_ITERS(FVAD_BQ5_ATTR)
+#undef FVAD_BQ5_ATTR
         if (e != cudaSuccess) rc = set_error(FVAD_ECUDA, "cudaFuncSetAttribute: %s (is this an sm_100 device?)", cudaGetErrorString(e));
     }
     if (rc == FVAD_OK) rc = rnnoise_batch_reset(r, 0);
@@ -1445,12 +1576,37 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
         // throttle on low-grid kernels that vanishes from 148 CTAs on
         size_t bq_grid = N;
         if (const char *e = debug_knob("bq_grid_min")) bq_grid = std::max<size_t>(N, (size_t)atoi(e));
-        // knob bq_form: 4 = chain and verification in separate kernels, 1 = chain lane + verifying warps in one CTA, 2 = light
-        // chain lane, 3 = named-barrier hand-over.  Form 4 where every chain has an SM to itself (latency regime: 233.5 ms against
-        // 246.2 ms per 240 s of 20 streams); with other stages' CTAs on the same SM its lone warp loses more than form 1's CTA
-        // does (x real time, form 4 / form 1: 148 streams 66.8k / 72.2k, 296: 105.4k / 109.6k, 592: 114.5k / 118.3k).
-        int form = lat ? 4 : 1;
+        // knob bq_form: 5 = the chain lane fed by a staging warp, verification and fix-up in kernels of their own; 4 = the same
+        // with the lane reading global memory itself; 1 = chain lane + verifying warps in one CTA; 2 = light chain lane; 3 =
+        // named-barrier hand-over.  Form 5 where every chain has an SM to itself (latency regime; ms per 240 s of 20 streams:
+        // form 5 212.9, form 4 230.9, form 1 246.6); with other stages' CTAs on the same SM a lone chain warp loses more than
+        // form 1's CTA does (x real time, form 4 / form 1: 148 streams 66.8k / 72.2k, 296: 105.4k / 109.6k, 592: 114.5k / 118.3k).
+        int form = lat ? 5 : 1;
         if (const char *e = debug_knob("bq_form")) form = atoi(e);
+        if (form == 5 && !r->bq_m0) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_form=5: not available from 1000 states on");
+        if (form == 5) {
+            launched = true;
+            const size_t T = Qs * kFrame;
+            int it = 48;                                      // samples per loop iteration (ms per 240 s of 20 streams: 16: 220.5, 24: 251.6, 32: 218.2, 48: 212.9, 80: 253.5 -- 255 registers; the spread is ptxas' scheduling of the body)
+            if (const char *e = debug_knob("bq_iter")) it = atoi(e);
+            bool go5 = false;
+#define FVAD_BQ5_PICK(II)                                                                                                 \
+            if (!go5 && it == II) {                                                                                      \
+                go5 = true;                                                                                              \
+                FVAD_LAUNCH_NAMED("k_rn_biquad", (k_rn_biquad_chain_s<II>), (unsigned)N, 64, hog_on * biquad_smem_hog(kBq5Ring * kFrame * 4 + 64), st, \
+                                  d_in, in_stride, C, (int)Qs, r->persist, r->bq_m0, r->bq_m0_stride(), r->bq_m1, r->bq_m1_stride(),       \
+                                  r->bq_broken, N, dbg);                                                                 \
+            }
+            FVAD_BQ4_ITERS(FVAD_BQ5_PICK)
+#undef FVAD_BQ5_PICK
+            if (!go5) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_iter=%d: 16, 24, 32, 48 or 80", it);
+            FVAD_LAUNCH(k_rn_biquad_verify, dim3((unsigned)ceil_div(T / kBq4Blk, (size_t)kBq4VerWarps), (unsigned)N), 32 * kBq4VerWarps, 0, st,
+                        d_in, in_stride, C, (int)Qs, r->bq_m0, r->bq_m0_stride(), r->bq_m1, r->bq_m1_stride(), r->bq_broken, s.hp,
+                        r->hp_stride(), N);
+            if (!(dbg & 64))
+            FVAD_LAUNCH(k_rn_biquad_fixup, (unsigned)N, 32, 0, st, d_in, in_stride, C, (int)Qs, r->bq_m0, r->bq_m0_stride(), r->bq_m1,
+                        r->bq_m1_stride(), r->bq_broken, r->persist, s.hp, r->hp_stride(), N);
+        }
         if (form == 4 && !r->bq_m0) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_form=4: not available from 1000 states on");
         if (form == 4) {
             launched = true;
@@ -1465,7 +1621,7 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
             if (!go4 && it == II) { go4 = true; if (C == 1) FVAD_BQ4_GO(II, true); else FVAD_BQ4_GO(II, false); }
             FVAD_BQ4_ITERS(FVAD_BQ4_PICK)
 #undef FVAD_BQ4_PICK
-            if (!go4) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_iter=%d: 16, 24, 32 or 48", it);
+            if (!go4) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_iter=%d: 16, 24, 32, 48 or 80", it);
 #undef FVAD_BQ4_GO
             FVAD_LAUNCH(k_rn_biquad_verify, dim3((unsigned)ceil_div(T / kBq4Blk, (size_t)kBq4VerWarps), (unsigned)N), 32 * kBq4VerWarps, 0, st,
                         d_in, in_stride, C, (int)Qs, r->bq_m0, r->bq_m0_stride(), r->bq_m1, r->bq_m1_stride(), r->bq_broken, s.hp,
@@ -1566,13 +1722,13 @@ int rnnoise_stage_b(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
 
 // Stage C: the RNN, frame-sequential per state.
 int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
-    {   // experiment hook (knob rnn_tolerance_mode; 0 = the exact path): see rn_core.cuh rnn_tolerance_mode
+    int tol_mode = 0;                                           // experiment (knob rnn_tolerance_mode; 0 = the product path): rn_core.cuh
+    if (const char *e = debug_knob("rnn_tolerance_mode")) tol_mode = atoi(e);
+    if (tol_mode) {
         static int set_mode[64] = {};
-        int mode = 0;
-        if (const char *e = debug_knob("rnn_tolerance_mode")) mode = atoi(e);
-        if (r && r->device >= 0 && r->device < 64 && set_mode[r->device] != mode + 1) {
-            FVAD_CUDA_TRY(cudaMemcpyToSymbolAsync(rn::c_rnn_tolerance_mode, &mode, sizeof mode, 0, cudaMemcpyHostToDevice, st));
-            set_mode[r->device] = mode + 1;
+        if (r && r->device >= 0 && r->device < 64 && set_mode[r->device] != tol_mode) {
+            FVAD_CUDA_TRY(cudaMemcpyToSymbolAsync(rn::c_rnn_tolerance_mode, &tol_mode, sizeof tol_mode, 0, cudaMemcpyHostToDevice, st));
+            set_mode[r->device] = tol_mode;
         }
     }
     FVAD_TRY(rn_check(r, slot, Qs));
@@ -1593,8 +1749,14 @@ int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     }
     if (const char *e = debug_knob("rnn_r")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) R = v; }
     if (const char *e = debug_knob("rnn_g")) { const int v = atoi(e); if (v >= 1 && v <= 3) G = v; }
+    if (tol_mode) { R = 1; G = 1; }                             // the experiment's kernel exists in one shape
     const unsigned grid = (unsigned)ceil_div(r->N, (size_t)R * G);
     bool launched = false;
+    if (tol_mode) {
+        launched = true;
+        FVAD_LAUNCH_NAMED("k_rn_rnn", (k_rn_rnn<1, 1, true>), grid, kRnnThreads, smem_rnn(1), st, r->tab.weights2, r->tab.bias, r->tab.t.tansig,
+                          s.feat, s.nzlist, s.nz_tile, r->persist, r->Qcap, r->N, s.gains, s.vad);
+    }
 #define FVAD_RNN_GO(RR, GG)                                                                                              \
     if (!launched && R == RR && G == GG) {                                                                               \
         launched = true;                                                                                                 \

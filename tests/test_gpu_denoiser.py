@@ -53,14 +53,16 @@ def test_denoiser_biquad_block_sizes(fv, checker, bq, roll, form, knobs):
         assert np.array_equal(out[s], wo), (s, np.abs(out[s] - wo).max())
 
 
-@pytest.mark.parametrize("it,dbg,exact", [(16, 0, True), (24, 0, True), (32, 0, True), (48, 0, True), (16, 32, True), (24, 32, True), (48, 32, True), (24, 96, False)])
-def test_denoiser_biquad_separate_kernels(fv, checker, it, dbg, exact, knobs):
-    """The default form of the biquad in the latency regime (bq_form=4): the chain lane alone in one kernel (16 to 48 samples per
-    loop iteration), verification + replay in a second, a fix-up in a third.  bq_dbg=32 plants a WRONG state in the chain of
+@pytest.mark.parametrize("form", [4, 5])
+@pytest.mark.parametrize("it,dbg,exact", [(16, 0, True), (24, 0, True), (32, 0, True), (48, 0, True), (80, 0, True), (16, 32, True), (24, 32, True), (48, 32, True), (24, 96, False)])
+def test_denoiser_biquad_separate_kernels(fv, checker, form, it, dbg, exact, knobs):
+    """The forms of the biquad with the chain in a kernel of its own (bq_form=5, the default in the latency regime, and 4): the chain lane alone in one kernel (16 to 48 samples per
+    loop iteration; form 5: fed by a staging warp through a ring in shared memory), verification + replay in a second, a
+    fix-up in a third.  bq_dbg=32 plants a WRONG state in the chain of
     state 0 at frame 40 of every call: the verifying kernel must find it and the fix-up kernel recompute the rest of the
     call, so the result stays the reference's; with the fix-up switched off as well (bq_dbg=96) it must NOT be -- which
     shows that the fix-up path is what was exercised.  A second call continues from the (repaired) carried state."""
-    knobs(bq_form="4", bq_iter=str(it), bq_dbg=str(dbg))
+    knobs(bq_form=str(form), bq_iter=str(it), bq_dbg=str(dbg))
     S, secs = 3, 6
     pcm = np.stack([synth(fv, 40 + s, secs) for s in range(S)])
     d = fv.DenoiserBatch(S)
