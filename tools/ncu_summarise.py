@@ -71,7 +71,7 @@ with open(os.path.join(out, f"{tag}_ncu_full_metrics.txt"), "w") as f:
                     k = "k_stft2048<true>" if re.match(r"k_stft2048<(?:\(bool\))?(1|true)", k) else "k_stft2048<false>"
                 else:
                     k = re.sub(r"<.*", "", k)              # the library's profile names carry no template arguments
-                    if k == "k_rn_biquad_chain":
+                    if k in ("k_rn_biquad_chain", "k_rn_biquad_chain_s"):
                         k = "k_rn_biquad"                  # the name the library's profile (and bench.py) uses for the chain kernel
                 tb = nbytes("dram__bytes_read.sum") + nbytes("dram__bytes_write.sum")
                 if k.startswith("k_stft2048") and tb > 1e10:
