@@ -640,7 +640,7 @@ __global__ void __launch_bounds__(bq_threads(BQ)) k_rn_biquad_v3(const float *__
 // whatever is switched off beside it; tools/ubench/chain_mix.cu runs the same step alone at 32-33.
 //   k_rn_biquad_chain   one warp per state, lane 0 only: reads its PCM straight from global memory (16-byte loads one
 //                       iteration ahead, L2 prefetch six frames ahead), runs biquad_chain_step, and publishes m0 before every
-//                       sample (one 16-byte store per four samples) and m1 before every 16 samples.  No shared memory, no
+//                       sample (one 16-byte store per four samples) and m1 before every 8 samples.  No shared memory, no
 //                       barrier, no hand-shake.  Iterations that start in a denormal tail take the reference's own double step.
 //   k_rn_biquad_verify  frame-parallel, a warp per 32 samples: rebuilds each sample's m1 the way the lane formed it,
 //                       re-evaluates the step with the full hazard analysis (biquad_step_eft_x), compares with the state
@@ -673,10 +673,9 @@ __device__ __forceinline__ bool bq4_tiny(float m0, float m1) {
     const float a0 = fabsf(m0), a1 = fabsf(m1);
     return (a0 != 0.0f && a0 < 1.0e-25f) || (a1 != 0.0f && a1 < 1.0e-25f);
 }
-// IT = samples per iteration of the lane's loop (16 or 32).  At the head of an iteration the raw samples loaded one
+// IT = samples per iteration of the lane's loop (16 ... 80).  At the head of an iteration the raw samples loaded one
 // iteration ago are scaled into a second register set -- their first use, the only place the lane waits for memory -- and
-// the loads of the NEXT iteration are issued at once into the registers just read: a whole iteration of chain time (550 /
-// 1100 cycles) to land.  The order matters: ptxas puts all of a loop's loads on ONE counting scoreboard, so a first use that
+// the loads of the NEXT iteration are issued at once into the registers just read: a whole iteration of chain time to land.  The order matters: ptxas puts all of a loop's loads on ONE counting scoreboard, so a first use that
 // comes after younger loads were issued waits for those as well (ncu source page of two earlier layouts: 275 cycles of
 // long-scoreboard stall per iteration, the full L2 latency, although the data had been requested 550 cycles earlier).
 __device__ __forceinline__ float4 bq4_ld(const float *p) {
