@@ -1743,8 +1743,7 @@ int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     int R = 1, G = 1;
     if (!latency_regime(r->N, r->device)) {
         if (per_sm <= 6) { R = 2; G = 3; }
-        else if (per_sm <= 8) { R = 4; G = 2; }
-        else { R = 4; G = 3; }
+        else { R = 4; G = 3; }                                  // 1184 streams, ms per 120 s: (4,3) 953.7, (2,3) 962.2, (4,2) 987.8, (2,2) 1008.5, (1,3) 1008.6, (4,1) 1140.3
     }
     if (const char *e = debug_knob("rnn_r")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) R = v; }
     if (const char *e = debug_knob("rnn_g")) { const int v = atoi(e); if (v >= 1 && v <= 3) G = v; }
