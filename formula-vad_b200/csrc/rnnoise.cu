@@ -1551,13 +1551,13 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
     // stages share its scheduler.  Many chains (throughput regime): no reservation, so several chains and the
     // other stages' CTAs share an SM; reserving it there serialises the biquad against everything else.
     const bool lat = latency_regime(N, r->device);
-    // A state per lane (k_rn_biquad_lanes: 8 x fewer instructions per sample, 32 chains per warp) from 1000 states on.  Its
+    // A state per lane (k_rn_biquad_lanes: 8 x fewer instructions per sample, 32 chains per warp) from 700 states on.  Its
     // warp advances at the pace of its slowest lane (~230 cycles per sample with the synthetic streams' overlapping
     // silences: the whole warp takes the double path while any state is in a denormal tail), and stage A of tile t+1 follows
     // stage A of tile t, so it only pays where the tile is short enough for that chain not to set the pace.  Measured,
     // x real time, lanes / chain-per-CTA: 296 streams 70.1k / 103.2k, 592: 104.4k / 116.5k, 1184: 130.4k / 113.0k,
     // 2368: 134.2k / 113.8k.
-    bool lanes = !lat && N >= 1000;
+    bool lanes = !lat && N >= 700;                                 // round 2, ms per 120 s, lanes / chain-per-CTA: 592 streams 616.6 / 565.3, 800: 709.2 / 788.3, 900: 812.9 / 886.7, 1184: 953.6 / 1143.6
     if (const char *e = debug_knob("biquad_lanes")) lanes = atoi(e) != 0;
     if (lanes) {
         FVAD_LAUNCH_NAMED("k_rn_biquad", k_rn_biquad_lanes, (unsigned)ceil_div(N, (size_t)kBqlStates), 32 * kBqlWarps, 0, st, d_in,

@@ -80,7 +80,7 @@ def test_denoiser_biquad_separate_kernels(fv, checker, form, it, dbg, exact, kno
 
 
 def test_denoiser_biquad_state_per_lane(fv, checker, knobs):
-    """The many-stream biquad (a state per lane, 32 states per CTA; chosen by itself only from 1000 states on)
+    """The many-stream biquad (a state per lane, 32 states per CTA; chosen by itself only from 700 states on)
     forced on 37 states: the second CTA has 5 live lanes, the streams' digital silences exercise the denormal path and the
     hazard replays are lane-divergent.  A second call continues from the carried filter state."""
     knobs(biquad_lanes="1")
