@@ -1744,6 +1744,11 @@ int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     if (!latency_regime(r->N, r->device)) {
         if (per_sm <= 6) { R = 2; G = 3; }
         else { R = 4; G = 3; }                                  // 1184 streams, ms per 120 s: (4,3) 953.7, (2,3) 962.2, (4,2) 987.8, (2,2) 1008.5, (1,3) 1008.6, (4,1) 1140.3
+    } else if (2 * r->N > sms) {
+        // Upper latency regime: the biquad chains hold an SM each, and an RNN CTA takes an SM of the rest for its weights --
+        // more states than free SMs would run the RNN in two waves.  Two states per CTA (independent groups): ms per 240 s,
+        // (1,2) / (1,1): 80 streams 307.9 / 344.0, 96: 335.9 / 356.8, 112: 394.0 / 412.0; 60 streams 271.8 / 271.2.
+        G = 2;
     }
     if (const char *e = debug_knob("rnn_r")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) R = v; }
     if (const char *e = debug_knob("rnn_g")) { const int v = atoi(e); if (v >= 1 && v <= 3) G = v; }
