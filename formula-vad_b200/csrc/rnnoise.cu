@@ -1582,6 +1582,7 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
         // form 1's CTA does (x real time, form 4 / form 1: 148 streams 66.8k / 72.2k, 296: 105.4k / 109.6k, 592: 114.5k / 118.3k).
         int form = lat ? 5 : 1;
         if (const char *e = debug_knob("bq_form")) form = atoi(e);
+        if (form == 4 && ((reinterpret_cast<uintptr_t>(d_in) & 15) || (in_stride & 3))) form = 5;   // form 4's lane loads 16 bytes at a time
         if (form == 5 && !r->bq_m0) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_form=5: not available from 1000 states on");
         if (form == 5) {
             launched = true;
