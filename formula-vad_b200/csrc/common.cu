@@ -55,9 +55,11 @@ const char *debug_knob(const char *key) {
 
 bool latency_regime(size_t n_chains, int device) {
     if (const char *e = debug_knob("latency_mode")) return atoi(e) != 0;
-    // measured on B200 (148 SMs), x real-time latency / throughput rule: 40 chains 28.0k / 22.0k, 80: 47.5k / 37.7k,
-    // 110: 48.9k / 47.7k, 148: 49.8k / 54.5k -- the crossover sits near three quarters of the SM count
-    return 4 * n_chains <= 3 * (size_t)device_sm_count(device);
+    // Round 1 (one chain per reserved SM), x real-time latency / throughput rule: 40 chains 28.0k / 22.0k, 80: 47.5k / 37.7k,
+    // 110: 48.9k / 47.7k, 148: 49.8k / 54.5k -- the crossover sat near three quarters of the SM count.  Round 2 packs up to
+    // four chains on a reserved SM (rnnoise.cu, form 5), ms per 240 s latency / throughput rule: 128 chains 321.9 / 372.7,
+    // 148: 370.7 / 384.4, 160: 385.7 / 398.0 -- the rule now holds up to one chain per SM.
+    return n_chains <= (size_t)device_sm_count(device);
 }
 
 int device_sm_count(int device) {

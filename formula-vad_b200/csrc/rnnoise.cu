@@ -812,22 +812,29 @@ __device__ __forceinline__ float4 bq5_lds(unsigned a) {
     asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
     return v;
 }
-template <int IT>
-__global__ void __launch_bounds__(64) k_rn_biquad_chain_s(const float *__restrict__ in, size_t in_stride, int C, int Q,
-                                                          RnPersist *persist, float *__restrict__ pm0, size_t pm0_stride,
-                                                          float *__restrict__ pm1, size_t pm1_stride, int *__restrict__ broken,
-                                                          size_t N, int dbg) {
+// CH = chains per CTA (1, 2 or 4): chain warps 0..CH-1 (one per SM sub-partition), staging warps CH..2CH-1, a ring and a pair
+// of counters per chain.  One chain per SM is the fastest chain; two or four per SM leave more SMs to the other stages.
+template <int IT, int CH>
+__global__ void __launch_bounds__(64 * CH) k_rn_biquad_chain_s(const float *__restrict__ in, size_t in_stride, int C, int Q,
+                                                               RnPersist *persist, float *__restrict__ pm0, size_t pm0_stride,
+                                                               float *__restrict__ pm1, size_t pm1_stride, int *__restrict__ broken,
+                                                               size_t N, int dbg) {
     static_assert(kFrame % IT == 0 && IT % kBq4It == 0, "iterations tile the frame");
     constexpr int kQuads = IT / 4, kItPerFrame = kFrame / IT, kRingFloats = kBq5Ring * kFrame;
-    __shared__ __align__(16) float ring[kRingFloats];
-    __shared__ int s_ready, s_done;                                 // frames staged / frames consumed so far
-    const size_t n = blockIdx.x;
-    if (n >= N) return;
+    __shared__ __align__(16) float rings[CH][kRingFloats];
+    __shared__ int s_ready[CH], s_done[CH];                         // frames staged / frames consumed so far, per chain
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (threadIdx.x == 0) { s_ready = 0; s_done = 0; broken[n] = kBq4None; }
+    const int ch = warp < CH ? warp : warp - CH;
+    const size_t n = (size_t)blockIdx.x * CH + ch;
+    if (threadIdx.x < CH) {
+        s_ready[threadIdx.x] = 0; s_done[threadIdx.x] = 0;
+        if ((size_t)blockIdx.x * CH + threadIdx.x < N) broken[(size_t)blockIdx.x * CH + threadIdx.x] = kBq4None;
+    }
     __syncthreads();
-    volatile int *v_ready = &s_ready, *v_done = &s_done;
-    if (warp == 1) {                                                // ---- the staging warp
+    if (n >= N) return;
+    float *ring = rings[ch];
+    volatile int *v_ready = &s_ready[ch], *v_done = &s_done[ch];
+    if (warp >= CH) {                                               // ---- a staging warp
         for (int q = 0; q < Q; q++) {
             const float *src = in + (n * C + (q % C)) * in_stride + (size_t)(q / C) * kFrame;
             float v[kFrame / 32];
@@ -1402,6 +1409,8 @@ static size_t biquad_smem_hog(size_t static_bytes) {
 static size_t g_bq_static[512];                              // static shared memory per BQ variant (cudaFuncGetAttributes)
 static size_t g_bq2_static[512], g_bq3_static[512];
 #define FVAD_BQ4_ITERS(X) X(16) X(24) X(32) X(48) X(80)
+static int bq5_chains_per_sm(size_t N, size_t sms) { return 4 * N <= sms ? 1 : 2 * N <= sms ? 2 : 4; }   // latency regime: chains per reserved SM
+static size_t bq5_static(int ch) { return (size_t)ch * (kBq5Ring * kFrame * 4 + 8) + 64; }   // upper bound of form 5's static shared memory
 #define FVAD_BQ2_VARIANTS(X) X(48) X(96) X(160) X(240)
 #define FVAD_BQ3_VARIANTS(X) X(48) X(96) X(160)
 constexpr size_t kSmemAna = (size_t)kWarpsPerCta * kScrAna * sizeof(float);
@@ -1516,7 +1525,9 @@ int rnnoise_batch_create(size_t n_states, size_t max_frames, int n_slots, int de
         FVAD_BQ4_ITERS(FVAD_BQ4_ATTR)
 #undef FVAD_BQ4_ATTR
 #define FVAD_BQ5_ATTR(II)                                                                                                 \
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain_s<II>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(kBq5Ring * kFrame * 4 + 64));
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain_s<II, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(bq5_static(1))); \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain_s<II, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(bq5_static(2))); \
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k_rn_biquad_chain_s<II, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)biquad_smem_hog(bq5_static(4)));
         FVAD_BQ4_ITERS(FVAD_BQ5_ATTR)
 #undef FVAD_BQ5_ATTR
         if (e != cudaSuccess) rc = set_error(FVAD_ECUDA, "cudaFuncSetAttribute: %s (is this an sm_100 device?)", cudaGetErrorString(e));
@@ -1589,15 +1600,24 @@ int rnnoise_stage_a(RnnoiseBatch *r, int slot, const float *d_in, size_t in_stri
             const size_t T = Qs * kFrame;
             int it = 48;                                      // samples per loop iteration (ms per 240 s of 20 streams: 16: 220.5, 24: 251.6, 32: 218.2, 48: 212.9, 80: 253.5 -- 255 registers; the spread is ptxas' scheduling of the body)
             if (const char *e = debug_knob("bq_iter")) it = atoi(e);
+            // chains per CTA = per reserved SM (knob bq_chains: 1, 2, 4).  A second chain on the SM costs the first nothing (its
+            // warp has a sub-partition of its own), four cost 1.5 %; every SM not reserved goes to the other stages.  ms per
+            // 240 s, 1 / 2 / 4 chains: 20 streams 289.6 / 289.4 / 293.9, 60: 290.1 / 281.3 / 288.7, 80: 316.7 / 290.3 / 290.8,
+            // 96: 354.1 / 303.6 / 300.3, 112: 409.5 / 335.5 / 311.3.
+            int chains = bq5_chains_per_sm(N, (size_t)device_sm_count(r->device));
+            if (const char *e = debug_knob("bq_chains")) chains = atoi(e);
             bool go5 = false;
+#define FVAD_BQ5_GO(II, CC)                                                                                              \
+                FVAD_LAUNCH_NAMED("k_rn_biquad", (k_rn_biquad_chain_s<II, CC>), (unsigned)ceil_div(N, (size_t)CC), 64 * CC,     \
+                                  hog_on * biquad_smem_hog(bq5_static(CC)), st, d_in, in_stride, C, (int)Qs, r->persist, r->bq_m0, \
+                                  r->bq_m0_stride(), r->bq_m1, r->bq_m1_stride(), r->bq_broken, N, dbg)
 #define FVAD_BQ5_PICK(II)                                                                                                 \
             if (!go5 && it == II) {                                                                                      \
                 go5 = true;                                                                                              \
-                FVAD_LAUNCH_NAMED("k_rn_biquad", (k_rn_biquad_chain_s<II>), (unsigned)N, 64, hog_on * biquad_smem_hog(kBq5Ring * kFrame * 4 + 64), st, \
-                                  d_in, in_stride, C, (int)Qs, r->persist, r->bq_m0, r->bq_m0_stride(), r->bq_m1, r->bq_m1_stride(),       \
-                                  r->bq_broken, N, dbg);                                                                 \
+                if (chains == 4) FVAD_BQ5_GO(II, 4); else if (chains == 2) FVAD_BQ5_GO(II, 2); else FVAD_BQ5_GO(II, 1);      \
             }
             FVAD_BQ4_ITERS(FVAD_BQ5_PICK)
+#undef FVAD_BQ5_GO
 #undef FVAD_BQ5_PICK
             if (!go5) return set_error(FVAD_EINVALID_ARGUMENT, "knob bq_iter=%d: 16, 24, 32, 48 or 80", it);
             FVAD_LAUNCH(k_rn_biquad_verify, dim3((unsigned)ceil_div(T / kBq4Blk, (size_t)kBq4VerWarps), (unsigned)N), 32 * kBq4VerWarps, 0, st,
@@ -1745,10 +1765,11 @@ int rnnoise_stage_c(RnnoiseBatch *r, int slot, size_t Qs, cudaStream_t st) {
     if (!latency_regime(r->N, r->device)) {
         if (per_sm <= 6) { R = 2; G = 3; }
         else { R = 4; G = 3; }                                  // 1184 streams, ms per 120 s: (4,3) 953.7, (2,3) 962.2, (4,2) 987.8, (2,2) 1008.5, (1,3) 1008.6, (4,1) 1140.3
-    } else if (2 * r->N > sms) {
-        // Upper latency regime: the biquad chains hold an SM each, and an RNN CTA takes an SM of the rest for its weights --
-        // more states than free SMs would run the RNN in two waves.  Two states per CTA (independent groups): ms per 240 s,
-        // (1,2) / (1,1): 80 streams 307.9 / 344.0, 96: 335.9 / 356.8, 112: 394.0 / 412.0; 60 streams 271.8 / 271.2.
+    } else if (5 * r->N > 3 * sms) {
+        // Upper latency regime: the biquad chains hold reserved SMs (four chains each up here), and an RNN CTA takes an SM of
+        // the rest for its weights.  Two states per CTA (independent groups) from 0.6 states per SM on; ms per 240 s, G = 1 /
+        // 2 / 3: 80 streams 285.9 / 290.7 / 292.2, 112: 334.0 / 312.4 / 312.9, 128: 369.3 / 328.1 / 320.8, 148: 411.5 / 370.2 /
+        // 363.0.
         G = 2;
     }
     if (const char *e = debug_knob("rnn_r")) { const int v = atoi(e); if (v == 1 || v == 2 || v == 4) R = v; }

@@ -79,6 +79,21 @@ def test_denoiser_biquad_separate_kernels(fv, checker, form, it, dbg, exact, kno
             assert not np.array_equal(go, wo), "the planted fault must matter when nothing repairs it"
 
 
+@pytest.mark.parametrize("chains,dbg", [(2, 0), (4, 0), (2, 32), (4, 32)])
+def test_denoiser_biquad_chains_per_cta(fv, checker, chains, dbg, knobs):
+    """Form 5 with two or four chains per CTA (a chain warp, a staging warp and a ring each): five states leave the last CTA
+    partly empty; a planted wrong state (bq_dbg=32) is repaired as with one chain per CTA."""
+    knobs(bq_form="5", bq_chains=str(chains), bq_dbg=str(dbg))
+    S, secs = 5, 4
+    pcm = np.stack([synth(fv, 70 + s, secs) for s in range(S)])
+    d = fv.DenoiserBatch(S)
+    out, vad = d.run(pcm)
+    for s in range(S):
+        wo, wv = checker.denoise_stream(pcm[s])
+        assert np.array_equal(vad[s], wv), (s, np.nonzero(vad[s] != wv)[0][:5])
+        assert np.array_equal(out[s], wo), (s, np.abs(out[s] - wo).max())
+
+
 def test_denoiser_biquad_state_per_lane(fv, checker, knobs):
     """The many-stream biquad (a state per lane, 32 states per CTA; chosen by itself only from 700 states on)
     forced on 37 states: the second CTA has 5 live lanes, the streams' digital silences exercise the denormal path and the
