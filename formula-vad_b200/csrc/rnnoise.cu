@@ -935,7 +935,7 @@ __global__ void __launch_bounds__(64 * CH) k_rn_biquad_chain_s(const float *__re
     constexpr int kQuads = IT / 4, kItPerFrame = kFrame / IT, kRingFloats = kBq5Ring * kFrame;
     __shared__ __align__(16) float rings[CH][kRingFloats];
     __shared__ int s_ready[CH], s_done[CH];                         // frames staged / frames consumed so far, per chain
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // (the shuffle tells ptxas the value is warp-uniform)
     const int ch = warp < CH ? warp : warp - CH;
     const size_t n = (size_t)blockIdx.x * CH + ch;
     if (threadIdx.x < CH) {
