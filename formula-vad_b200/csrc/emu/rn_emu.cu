@@ -147,4 +147,72 @@ int rn_emu_tile(void *h, const float *in, size_t in_stride, int Tn, float *out, 
     }
     return 0;
 }
+
+// The protocol of the biquad's chain / verify / fix-up kernels (rnnoise.cu, forms 4 and 5) on the host, one state, n samples
+// (a multiple of 32): the lane's fast step in iterations of `it` samples with the denormal test taken four samples before the
+// end of the previous iteration, the record (m0 before every sample, m1 before every eighth), then per 32-sample block the
+// hazard analysis, the replay of hazardous blocks from the recorded state and the comparison of its end state.  `plant` >= 0
+// flips a bit of m0 after that iteration (what knob bq_dbg=32 does).  y = the result after verification and fix-up.
+// counts[0] = samples flagged, [1] = blocks replayed, [2] = first block whose replay disagreed (-1: none), [3] = iterations
+// that took the double path.
+int rn_emu_biquad_protocol(const float *in, size_t n, int it, long plant, float *y, float *state, long *counts) {
+    if (n % 32 || it % 8 || it <= 0) return -1;
+    std::vector<float> M0(n + 1), M1(n / 8 + 1), xs(n);
+    for (size_t i = 0; i < n; i++) xs[i] = in[i] * 32767.0f;
+    float m0 = state[0], m1 = state[1];
+    const float s0 = m0, s1 = m1;
+    auto is_tiny = [](float a, float b) {
+        a = a < 0 ? -a : a; b = b < 0 ? -b : b;
+        return (a != 0.0f && a < 1.0e-25f) || (b != 0.0f && b < 1.0e-25f);
+    };
+    bool tiny = is_tiny(m0, m1);
+    long n_tiny_it = 0, h = 0;
+    for (size_t i0 = 0; i0 < n; i0 += it, h++) {
+        const size_t len = i0 + it <= n ? it : n - i0;
+        bool next_tiny = tiny;
+        if (tiny) n_tiny_it++;
+        for (size_t i = 0; i < len; i++) {
+            if ((i0 + i) % 8 == 0) M1[(i0 + i) / 8] = m1;
+            M0[i0 + i] = m0;
+            if (tiny) biquad_step_x(xs[i0 + i], m0, m1);
+            else biquad_chain_step(xs[i0 + i], m0, m1);
+            if (!tiny && i + 1 == len - 4) next_tiny = is_tiny(m0, m1);
+        }
+        tiny = tiny ? is_tiny(m0, m1) : next_tiny;
+        if (h == plant) m0 = u2f(f2u(m0) ^ 0x1000u);
+    }
+    M0[n] = m0; M1[n / 8] = m1;
+    (void)s0; (void)s1;
+    long flagged = 0, replayed = 0, broken = -1;
+    for (size_t b0 = 0; b0 < n; b0 += 32) {
+        bool any = false;
+        for (int l = 0; l < 32; l++) {
+            const size_t t = b0 + l;
+            float a = M0[t], b;
+            if (t % 8 == 0) b = M1[t / 8];
+            else b = fma_rn(-0.99600f, xs[t - 1] + M0[t - 1], xs[t - 1]);
+            bool hz = false;
+            const float yv = biquad_step_eft_x(xs[t], a, b, hz);
+            hz |= f2u(a) != f2u(M0[t + 1]);
+            const float bl = (t + 1) % 8 == 0 ? M1[(t + 1) / 8] : fma_rn(-0.99600f, yv, xs[t]);
+            hz |= f2u(b) != f2u(bl);
+            y[t] = yv;
+            if (hz) { flagged++; any = true; }
+        }
+        if (any) {
+            replayed++;
+            float r0 = M0[b0], r1 = M1[b0 / 8];
+            for (int l = 0; l < 32; l++) y[b0 + l] = biquad_step_x(xs[b0 + l], r0, r1);
+            if ((f2u(r0) != f2u(M0[b0 + 32]) || f2u(r1) != f2u(M1[(b0 + 32) / 8])) && broken < 0) broken = (long)(b0 / 32);
+        }
+    }
+    if (broken >= 0) {                                         // k_rn_biquad_fixup
+        size_t t0 = (size_t)broken * 32;
+        m0 = M0[t0]; m1 = M1[t0 / 8];
+        for (size_t t = t0; t < n; t++) y[t] = biquad_step_x(xs[t], m0, m1);
+    }
+    state[0] = m0; state[1] = m1;
+    counts[0] = flagged; counts[1] = replayed; counts[2] = broken; counts[3] = n_tiny_it;
+    return 0;
+}
 }

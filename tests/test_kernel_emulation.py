@@ -81,3 +81,39 @@ def test_port_trace_internals_against_emulation(fv, port, emu):
     assert np.array_equal(sil, np.array([t.silence for t in tr]))
     assert np.array_equal(pitch, np.array([t.pitch_index for t in tr]))
     assert np.array_equal(vad, wv)
+
+
+@pytest.mark.parametrize("it", [16, 48])
+def test_biquad_chain_protocol_on_host(fv, emu, it):
+    """The biquad's chain / verify / fix-up protocol (rnnoise.cu forms 4 and 5) replayed on the host with the same step
+    functions: on the synthetic streams the fast step is never WRONG (hazards are raised and replayed, every replay confirms
+    the recorded state: the fix-up kernel has nothing to do), the verified output equals the first form's (which the port's
+    trace pins), and a planted wrong state is found by the verification and repaired by the fix-up."""
+    emu.rn_emu_biquad_protocol.argtypes = [_fp, C.c_size_t, C.c_int, C.c_long, _fp, _fp, C.POINTER(C.c_long)]
+    secs = 40
+    for sid in (3, 17):
+        x = np.ascontiguousarray(synth(fv, sid, secs), np.float32)
+        n = x.size
+        # reference: the first form's block protocol through the tile emulation (hp trace)
+        h = emu.rn_emu_create(1)
+        hp = np.zeros(n, np.float32)
+        out = np.zeros(n, np.float32)
+        emu.rn_emu_tile(h, x.ctypes.data_as(_fp), n, n // 480, out.ctypes.data_as(_fp), n, None, None, None, None, None,
+                        hp.ctypes.data_as(_fp))
+        emu.rn_emu_destroy(h)
+        y = np.zeros(n, np.float32)
+        st = np.zeros(2, np.float32)
+        cnt = (C.c_long * 4)()
+        assert emu.rn_emu_biquad_protocol(x.ctypes.data_as(_fp), n, it, -1, y.ctypes.data_as(_fp), st.ctypes.data_as(_fp), cnt) == 0
+        assert cnt[2] == -1, "the fast step was wrong in block %d" % cnt[2]
+        assert cnt[1] > 0 and cnt[3] > 0, "the stream must exercise hazard replays and the denormal path"
+        assert np.array_equal(y.view(np.uint32), hp.view(np.uint32))
+        # a planted wrong state: found, repaired, same output and same end state
+        y2 = np.zeros(n, np.float32)
+        st2 = np.zeros(2, np.float32)
+        cnt2 = (C.c_long * 4)()
+        plant = (n // it) // 3
+        assert emu.rn_emu_biquad_protocol(x.ctypes.data_as(_fp), n, it, plant, y2.ctypes.data_as(_fp), st2.ctypes.data_as(_fp), cnt2) == 0
+        assert cnt2[2] >= 0 and abs(cnt2[2] - ((plant + 1) * it - 1) // 32) <= 1
+        assert np.array_equal(y2.view(np.uint32), hp.view(np.uint32))
+        assert np.array_equal(st2.view(np.uint32), st.view(np.uint32))
